@@ -1,0 +1,155 @@
+/*
+ * zflacb200.h — C ABI of the B200-native FLAC decode path (libzflacb200.so).
+ *
+ * This is the drop-in boundary for Senryoku/zflac's one public entry point,
+ *
+ *     pub fn decode(allocator: std.mem.Allocator, reader: anytype) !DecodedFLAC
+ *                                                   (reference src/zflac.zig:217)
+ *
+ * and its result type DecodedFLAC { channels, sample_rate, bits_per_sample,
+ * samples: union{s8,s16,s32}, _samples_backing } (src/zflac.zig:12-28). A Zig
+ * shim (zig/zflac.zig) keeps that signature and calls the
+ * functions below; nothing in the signatures is a CUDA or torch type.
+ *
+ * Everything behind these calls runs on the GPU (sm_100a kernels). There is no
+ * CPU decode fallback: if CUDA is unavailable the calls fail with
+ * ZFLACB200_CUDA_ERROR.
+ *
+ * Ownership follows the reference ("Caller owns the returned memory",
+ * src/zflac.zig:216; buffer from the caller's allocator, 32-byte aligned,
+ * :331): decoding is two-phase so the CALLER allocates the PCM buffer:
+ *
+ *     zflacb200_open()   parse + upload + all kernels; PCM stays on the device;
+ *                        returns the DecodedFLAC header fields and sizes
+ *     (caller allocates info.pcm_bytes with its own allocator, align 32)
+ *     zflacb200_read()   device -> caller buffer
+ *     zflacb200_close()
+ */
+#ifndef ZFLACB200_H
+#define ZFLACB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZFLACB200_ABI_VERSION 1
+
+/* One value per Zig error name decode() can return; the shim maps
+ * them 1:1 onto the Zig error set. */
+typedef enum zflacb200_status {
+    ZFLACB200_OK = 0,
+    ZFLACB200_INVALID_SIGNATURE = 1,               /* error.InvalidSignature            src/zflac.zig:220 */
+    ZFLACB200_INVALID_METADATA_HEADER = 2,         /* error.InvalidMetadataHeader       :248 */
+    ZFLACB200_UNIMPLEMENTED = 3,                   /* error.Unimplemented               :263 */
+    ZFLACB200_INVALID_CHECKSUM = 4,                /* error.InvalidChecksum             :280 */
+    ZFLACB200_MISSING_STREAMINFO = 5,              /* error.MissingStreaminfo           :309 */
+    ZFLACB200_INVALID_FRAME_HEADER = 6,            /* error.InvalidFrameHeader          :352,357,361,372,405 */
+    ZFLACB200_INVALID_CODED_NUMBER = 7,            /* error.InvalidCodedNumber          :206 */
+    ZFLACB200_INCONSISTENT_PARAMETERS = 8,         /* error.InconsistentParameters      :386,391 */
+    ZFLACB200_INVALID_SUBFRAME_HEADER = 9,         /* error.InvalidSubframeHeader       :431,471,542 */
+    ZFLACB200_INVALID_RESIDUAL_CODING_METHOD = 10, /* error.InvalidResidualCodingMethod :618 */
+    ZFLACB200_END_OF_STREAM = 11,                  /* error.EndOfStream (reader)        e.g. :344 */
+    ZFLACB200_OUT_OF_MEMORY = 12,                  /* error.OutOfMemory */
+    /* input on which the reference itself is undefined (unreachable / @intCast
+     * out of range / slice out of bounds: panic in Debug, UB in ReleaseFast) */
+    ZFLACB200_UNDEFINED_IN_REFERENCE = 90,
+    /* not Zig errors: */
+    ZFLACB200_CUDA_ERROR = 100,      /* no device, kernel launch or copy failed; see zflacb200_last_error() */
+    ZFLACB200_INVALID_ARGUMENT = 101
+} zflacb200_status;
+
+/* zflacb200_options.flags */
+#define ZFLACB200_VERIFY_MD5 0x1u      /* default: reproduce the reference's MD5 gate (src/zflac.zig:267-280) */
+#define ZFLACB200_SKIP_MD5 0x2u        /* additive: do not hash; never returns InvalidChecksum */
+#define ZFLACB200_INPUT_ON_DEVICE 0x4u /* `data` is a device pointer (bench: inputs resident in HBM) */
+#define ZFLACB200_NO_CRC_ACCEL 0x8u    /* diagnostics: ignore CRC-16 links, probe every frame end (slow path) */
+
+typedef struct zflacb200_options {
+    uint32_t struct_size; /* sizeof(zflacb200_options) */
+    uint32_t flags;       /* 0 = defaults (VERIFY_MD5) */
+    int32_t device;       /* CUDA device ordinal, -1 = current */
+    void *stream;         /* cudaStream_t to launch on (NULL = the context's own stream) */
+} zflacb200_options;
+
+/* What DecodedFLAC carries (src/zflac.zig:18-24) plus sizes and diagnostics. */
+typedef struct zflacb200_info {
+    uint8_t channels;        /* DecodedFLAC.channels */
+    uint8_t bits_per_sample; /* DecodedFLAC.bits_per_sample: from the first frame header (:381-384) */
+    uint8_t container_bytes; /* union tag: 1 = .s8, 2 = .s16, 4 = .s32 (from STREAMINFO, :256-264) */
+    uint8_t md5_checked;     /* 1 if the MD5 gate ran */
+    uint32_t sample_rate;    /* DecodedFLAC.sample_rate (u24) */
+    uint64_t n_samples;      /* samples.len: interleaved sample count */
+    uint64_t pcm_bytes;      /* n_samples * container_bytes == _samples_backing.len */
+    /* diagnostics (not part of the reference's result) */
+    uint64_t n_frames;
+    uint64_t audio_offset;       /* byte offset of the first frame */
+    uint64_t audio_bytes;        /* bytes of the frames decoded */
+    uint64_t n_candidates;       /* frame-index entries the sync scan emitted */
+    uint64_t n_probed_frames;    /* frames whose end had to be found by decoding (no CRC-16 link) */
+    uint64_t n_crc16_mismatch;   /* decoded frames whose CRC-16 does not match (reference ignores it, Q1) */
+    uint8_t md5_computed[16];
+    uint8_t md5_streaminfo[16];
+    /* device time of the last open(), ms, CUDA events on the launch stream */
+    float ms_scan, ms_link, ms_decode, ms_epilogue, ms_md5, ms_total;
+} zflacb200_info;
+
+typedef struct zflacb200_stream zflacb200_stream; /* opaque handle of one decoded stream */
+
+/* Library / device lifecycle. zflacb200_init is optional (open() does it lazily). */
+int zflacb200_abi_version(void);
+int zflacb200_init(int device);
+int zflacb200_device_count(void);
+void zflacb200_shutdown(void);
+const char *zflacb200_status_name(int status); /* the Zig error name, e.g. "InvalidFrameHeader" */
+const char *zflacb200_last_error(void);        /* thread-local detail for CUDA_ERROR / INVALID_ARGUMENT */
+
+/* Replaces the body of decode() (src/zflac.zig:217-310): signature + metadata walk,
+ * frame index, subframe decode, decorrelation, MD5 gate, MSB-align shift.
+ * `data`/`len` is the whole stream the reader would yield. On success *out is a
+ * handle holding the PCM on the device and *info is filled; on any error no
+ * handle is returned (the reference returns no data on error, errdefer :265,:332). */
+int zflacb200_open(const uint8_t *data, size_t len, const zflacb200_options *opt,
+                   zflacb200_stream **out, zflacb200_info *info);
+
+/* Copies the PCM (interleaved, container_bytes each, post MSB-align shift —
+ * exactly DecodedFLAC._samples_backing) into `dst` (host memory, >= info.pcm_bytes). */
+int zflacb200_read(zflacb200_stream *s, void *dst, size_t dst_bytes);
+
+/* Device pointer of the PCM (valid until close); for callers that keep audio on the GPU. */
+int zflacb200_device_pcm(zflacb200_stream *s, void **dev_ptr, size_t *bytes);
+
+void zflacb200_close(zflacb200_stream *s);
+
+/* One-call convenience used by hosts that own a plain malloc-style allocator:
+ * open + read into `dst` if it is large enough (else returns pcm_bytes needed in info and
+ * ZFLACB200_OUT_OF_MEMORY) + close. */
+int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *opt,
+                     void *dst, size_t dst_capacity, zflacb200_info *info);
+
+/* File-parallel batch (BASELINE config 5): n independent streams decoded in one
+ * pipeline pass on one device. statuses[i]/infos[i]/outs[i] are per stream. Returns
+ * ZFLACB200_OK if the batch ran (individual streams may still carry errors). */
+int zflacb200_open_batch(const uint8_t *const *datas, const size_t *lens, size_t n,
+                         const zflacb200_options *opt, zflacb200_stream **outs,
+                         zflacb200_info *infos, int *statuses);
+
+/* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
+typedef struct zflacb200_frame {
+    uint64_t offset;        /* byte offset of the sync code */
+    uint64_t end_offset;    /* just past the CRC-16 */
+    uint64_t sample_offset; /* interleaved-sample offset */
+    uint32_t block_size;
+    uint8_t header_len;
+    uint8_t channel_code;
+    uint8_t crc16_ok;
+    uint8_t probed;
+} zflacb200_frame;
+int zflacb200_frames(zflacb200_stream *s, zflacb200_frame *dst, size_t capacity, size_t *n_frames);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZFLACB200_H */

@@ -1,0 +1,191 @@
+"""zflac_b200 — B200-native FLAC decode path behind Senryoku/zflac's public API.
+
+Host-side mirror of the reference interface (the reference is Zig; there is no Zig toolchain
+in this image, so the host side above the C ABI is Python, see INTEGRATION.md for the Zig shim):
+
+    reference                                   here
+    ---------                                   ----
+    zflac.decode(allocator, reader)             zflac_b200.decode(data)            (src/zflac.zig:217)
+    DecodedFLAC{channels, sample_rate,          DecodedFLAC(channels, sample_rate, (src/zflac.zig:18-24)
+      bits_per_sample, samples: s8|s16|s32}       bits_per_sample, samples: ndarray int8|int16|int32)
+    error.InvalidSignature, ...                 zflac_b200.InvalidSignature, ...   (one class per Zig error)
+
+All decoding runs in libzflacb200.so (hand-written sm_100a kernels, include/zflacb200.h). If the
+library or a CUDA device is missing, decode() raises; nothing falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _native
+from ._native import INPUT_ON_DEVICE, NO_CRC_ACCEL, SKIP_MD5, VERIFY_MD5  # noqa: F401
+
+__all__ = ["decode", "decode_into", "DecodedFLAC", "ZflacError", "CudaError", "open_device", "DeviceStream"]
+
+
+class ZflacError(Exception):
+    """Base of the Zig error set decode() can return."""
+    status = -1
+
+
+def _mk(name, status):
+    cls = type(name, (ZflacError,), {"status": status, "__doc__": f"error.{name}"})
+    globals()[name] = cls
+    __all__.append(name)
+    return cls
+
+
+_ERRORS = {
+    1: _mk("InvalidSignature", 1), 2: _mk("InvalidMetadataHeader", 2), 3: _mk("Unimplemented", 3),
+    4: _mk("InvalidChecksum", 4), 5: _mk("MissingStreaminfo", 5), 6: _mk("InvalidFrameHeader", 6),
+    7: _mk("InvalidCodedNumber", 7), 8: _mk("InconsistentParameters", 8), 9: _mk("InvalidSubframeHeader", 9),
+    10: _mk("InvalidResidualCodingMethod", 10), 11: _mk("EndOfStream", 11), 12: _mk("OutOfMemory", 12),
+    90: _mk("UndefinedInReference", 90), 100: _mk("CudaError", 100), 101: _mk("InvalidArgument", 101),
+}
+
+
+def _raise(status: int):
+    lib = _native.load()
+    detail = (lib.zflacb200_last_error() or b"").decode()
+    cls = _ERRORS.get(status, ZflacError)
+    raise cls(f"{lib.zflacb200_status_name(status).decode()}" + (f": {detail}" if detail else ""))
+
+
+@dataclass
+class DecodedFLAC:
+    """Mirror of `pub const DecodedFLAC` (src/zflac.zig:18-28). `samples` plays the role of the
+    s8/s16/s32 union: its dtype is the union tag; values are interleaved, frame-major /
+    channel-minor, MSB-aligned for 9-15 and 17-31 bit streams (zflac.zig:287-306)."""
+    channels: int
+    sample_rate: int
+    bits_per_sample: int
+    samples: np.ndarray
+    info: dict = field(default_factory=dict)
+
+    @property
+    def tag(self) -> str:
+        return {1: "s8", 2: "s16", 4: "s32"}[self.samples.dtype.itemsize]
+
+    def deinit(self):  # the reference frees _samples_backing here; numpy owns the buffer
+        self.samples = None
+
+
+def _info_dict(info: _native.Info) -> dict:
+    d = {k: getattr(info, k) for k, _ in _native.Info._fields_ if not k.startswith("md5_")}
+    d["md5_computed"] = bytes(info.md5_computed)
+    d["md5_streaminfo"] = bytes(info.md5_streaminfo)
+    return d
+
+
+def _options(flags=0, device=-1, stream=None) -> _native.Options:
+    return _native.Options(C.sizeof(_native.Options), flags, device, stream)
+
+
+def _as_u8(data) -> np.ndarray:
+    if isinstance(data, np.ndarray):
+        return np.ascontiguousarray(data, dtype=np.uint8)
+    if hasattr(data, "read"):
+        data = data.read()  # the reference takes a reader; slurp it
+    return np.frombuffer(data, dtype=np.uint8)
+
+
+_DTYPES = {1: np.int8, 2: np.int16, 4: np.int32}
+
+
+def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bool = True) -> DecodedFLAC:
+    """Drop-in for `zflac.decode(allocator, reader)`: `data` is bytes / ndarray / a readable object
+    holding the whole stream. Raises the ZflacError subclass named like the Zig error."""
+    lib = _native.load()
+    arr = _as_u8(data)
+    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL)
+    opt = _options(flags, device)
+    handle = C.c_void_p()
+    info = _native.Info()
+    st = lib.zflacb200_open(arr.ctypes.data, arr.size, C.byref(opt), C.byref(handle), C.byref(info))
+    if st != 0:
+        _raise(st)
+    try:
+        # the caller-side allocation of the reference (allocator.allocWithOptions(u8, n, 32), zflac.zig:331)
+        out = np.empty(int(info.n_samples), dtype=_DTYPES[info.container_bytes])
+        st = lib.zflacb200_read(handle, out.ctypes.data, out.nbytes)
+        if st != 0:
+            _raise(st)
+    finally:
+        lib.zflacb200_close(handle)
+    return DecodedFLAC(info.channels, info.sample_rate, info.bits_per_sample, out, _info_dict(info))
+
+
+def decode_into(data, dst: np.ndarray, *, device: int = -1, verify_md5: bool = True) -> dict:
+    """One-call variant (zflacb200_decode): decodes into a caller-owned buffer."""
+    lib = _native.load()
+    arr = _as_u8(data)
+    opt = _options(0 if verify_md5 else SKIP_MD5, device)
+    info = _native.Info()
+    st = lib.zflacb200_decode(arr.ctypes.data, arr.size, C.byref(opt), dst.ctypes.data, dst.nbytes, C.byref(info))
+    if st != 0:
+        _raise(st)
+    return _info_dict(info)
+
+
+class DeviceStream:
+    """A decoded stream whose PCM stays in HBM (zflacb200_open with ZFLACB200_INPUT_ON_DEVICE)."""
+
+    def __init__(self, handle, info):
+        self._h = handle
+        self.info = _info_dict(info)
+        self.channels, self.sample_rate, self.bits_per_sample = info.channels, info.sample_rate, info.bits_per_sample
+        self.container_bytes, self.n_samples, self.pcm_bytes = info.container_bytes, int(info.n_samples), int(info.pcm_bytes)
+
+    def device_ptr(self) -> int:
+        p, n = C.c_void_p(), C.c_size_t()
+        _native.load().zflacb200_device_pcm(self._h, C.byref(p), C.byref(n))
+        return p.value or 0
+
+    def to_host(self) -> np.ndarray:
+        out = np.empty(self.n_samples, dtype=_DTYPES[self.container_bytes])
+        st = _native.load().zflacb200_read(self._h, out.ctypes.data, out.nbytes)
+        if st != 0:
+            _raise(st)
+        return out
+
+    def frames(self) -> np.ndarray:
+        lib = _native.load()
+        n = C.c_size_t()
+        lib.zflacb200_frames(self._h, None, 0, C.byref(n))
+        buf = (_native.Frame * max(n.value, 1))()
+        lib.zflacb200_frames(self._h, buf, n.value, C.byref(n))
+        dt = np.dtype([("offset", "<u8"), ("end_offset", "<u8"), ("sample_offset", "<u8"), ("block_size", "<u4"),
+                       ("header_len", "u1"), ("channel_code", "u1"), ("crc16_ok", "u1"), ("probed", "u1")])
+        return np.frombuffer(bytes(buf), dtype=dt)[: n.value].copy()
+
+    def close(self):
+        if self._h:
+            _native.load().zflacb200_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+
+def open_device(dev_ptr: int, nbytes: int, *, device: int = -1, stream: int | None = None, verify_md5: bool = True,
+                use_crc_links: bool = True, host_data=None) -> DeviceStream:
+    """Decode a stream that already sits in device memory (or, with host_data, upload it first)
+    and keep the PCM on the device."""
+    lib = _native.load()
+    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL)
+    if host_data is not None:
+        arr = _as_u8(host_data)
+        ptr, n = arr.ctypes.data, arr.size
+    else:
+        flags |= INPUT_ON_DEVICE
+        ptr, n = dev_ptr, nbytes
+    opt = _options(flags, device, stream)
+    handle = C.c_void_p()
+    info = _native.Info()
+    st = lib.zflacb200_open(ptr, n, C.byref(opt), C.byref(handle), C.byref(info))
+    if st != 0:
+        _raise(st)
+    return DeviceStream(handle, info)

@@ -1,0 +1,81 @@
+"""ctypes binding of libzflacb200.so (include/zflacb200.h). Fails loudly when the library is
+missing or cannot be loaded: there is no Python or CPU decode fallback."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "_lib", "libzflacb200.so")
+
+# zflacb200_options.flags
+VERIFY_MD5 = 0x1
+SKIP_MD5 = 0x2
+INPUT_ON_DEVICE = 0x4
+NO_CRC_ACCEL = 0x8
+
+EXPORTS = [
+    "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown",
+    "zflacb200_status_name", "zflacb200_last_error", "zflacb200_open", "zflacb200_read",
+    "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_open_batch", "zflacb200_frames",
+]
+
+
+class Options(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("flags", C.c_uint32), ("device", C.c_int32), ("stream", C.c_void_p)]
+
+
+class Info(C.Structure):
+    _fields_ = [("channels", C.c_uint8), ("bits_per_sample", C.c_uint8), ("container_bytes", C.c_uint8),
+                ("md5_checked", C.c_uint8), ("sample_rate", C.c_uint32), ("n_samples", C.c_uint64),
+                ("pcm_bytes", C.c_uint64), ("n_frames", C.c_uint64), ("audio_offset", C.c_uint64),
+                ("audio_bytes", C.c_uint64), ("n_candidates", C.c_uint64), ("n_probed_frames", C.c_uint64),
+                ("n_crc16_mismatch", C.c_uint64), ("md5_computed", C.c_uint8 * 16),
+                ("md5_streaminfo", C.c_uint8 * 16), ("ms_scan", C.c_float), ("ms_link", C.c_float),
+                ("ms_decode", C.c_float), ("ms_epilogue", C.c_float), ("ms_md5", C.c_float), ("ms_total", C.c_float)]
+
+
+class Frame(C.Structure):
+    _fields_ = [("offset", C.c_uint64), ("end_offset", C.c_uint64), ("sample_offset", C.c_uint64),
+                ("block_size", C.c_uint32), ("header_len", C.c_uint8), ("channel_code", C.c_uint8),
+                ("crc16_ok", C.c_uint8), ("probed", C.c_uint8)]
+
+
+_lib = None
+
+
+def load():
+    """Load libzflacb200.so. Raises if it has not been built (run __graft_entry__.build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: the CUDA library has not been built. Run "
+            "`python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). zflac_b200 has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.zflacb200_abi_version.restype = C.c_int
+    lib.zflacb200_init.argtypes = [C.c_int]
+    lib.zflacb200_init.restype = C.c_int
+    lib.zflacb200_device_count.restype = C.c_int
+    lib.zflacb200_shutdown.restype = None
+    lib.zflacb200_status_name.argtypes = [C.c_int]
+    lib.zflacb200_status_name.restype = C.c_char_p
+    lib.zflacb200_last_error.restype = C.c_char_p
+    lib.zflacb200_open.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.POINTER(C.c_void_p), C.POINTER(Info)]
+    lib.zflacb200_open.restype = C.c_int
+    lib.zflacb200_read.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    lib.zflacb200_read.restype = C.c_int
+    lib.zflacb200_device_pcm.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+    lib.zflacb200_device_pcm.restype = C.c_int
+    lib.zflacb200_close.argtypes = [C.c_void_p]
+    lib.zflacb200_close.restype = None
+    lib.zflacb200_decode.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.c_void_p, C.c_size_t, C.POINTER(Info)]
+    lib.zflacb200_decode.restype = C.c_int
+    lib.zflacb200_open_batch.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, C.POINTER(Options),
+                                         C.POINTER(C.c_void_p), C.POINTER(Info), C.POINTER(C.c_int)]
+    lib.zflacb200_open_batch.restype = C.c_int
+    lib.zflacb200_frames.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.zflacb200_frames.restype = C.c_int
+    _lib = lib
+    return lib

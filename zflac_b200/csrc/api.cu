@@ -1,0 +1,783 @@
+// api.cu — host side of libzflacb200.so: the C ABI of include/zflacb200.h.
+//
+// Host work is what the reference does once per stream and never per sample: the signature
+// and metadata walk (src/zflac.zig:217-253), container choice (:256-264), the stream-level
+// frame-loop rules (first-frame latch :376-392, buffer growth / "stop trusting the total"
+// :394-402, block-size-1 rule :405, termination :341-350, trim :583-588), error precedence
+// ("first error in stream order wins") and the MD5 comparison (:279-280). Everything per byte
+// or per sample runs in the kernels of scan.cu / decode.cu / epilogue.cu. There is no CPU
+// decode path: without a CUDA device every entry point returns ZFLACB200_CUDA_ERROR.
+#include "../../include/zflacb200.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+using namespace zf;
+
+namespace {
+
+thread_local std::string g_last_error;
+std::mutex g_mutex;
+
+struct DeviceCtx {
+    bool ready = false;
+    cudaStream_t stream = nullptr;
+};
+DeviceCtx g_ctx[64];
+
+#define CU_CHECK(expr)                                                                          \
+    do {                                                                                        \
+        cudaError_t _e = (expr);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            char _b[512];                                                                       \
+            snprintf(_b, sizeof(_b), "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            g_last_error = _b;                                                                  \
+            return ZFLACB200_CUDA_ERROR;                                                        \
+        }                                                                                       \
+    } while (0)
+
+int ensure_device(int device, int *resolved) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        g_last_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (there is no CPU fallback)";
+        return ZFLACB200_CUDA_ERROR;
+    }
+    if (device < 0) CU_CHECK(cudaGetDevice(&device));
+    if (device >= count || device >= 64) {
+        g_last_error = "device ordinal out of range";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    CU_CHECK(cudaSetDevice(device));
+    DeviceCtx &c = g_ctx[device];
+    if (!c.ready) {
+        cudaDeviceProp prop;
+        CU_CHECK(cudaGetDeviceProperties(&prop, device));
+        if (prop.major < 10) {
+            g_last_error = "libzflacb200 is built for sm_100a (B200) only; device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor);
+            return ZFLACB200_CUDA_ERROR;
+        }
+        CU_CHECK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+        CU_CHECK(scan_init_constants());
+        cudaMemPool_t pool;
+        CU_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
+        uint64_t thresh = ~0ull;  // keep freed blocks cached: open() allocates the same sizes again and again
+        CU_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+        c.ready = true;
+    }
+    *resolved = device;
+    return ZFLACB200_OK;
+}
+
+// ------------------------------------------------------------------ byte access for host logic
+struct ByteSource {
+    const uint8_t *host = nullptr;
+    const uint8_t *dev = nullptr;
+    uint64_t len = 0;
+    // copies [off, off+n) into dst; bytes past len are not written. Returns bytes available.
+    uint64_t get(uint64_t off, uint64_t n, uint8_t *dst) const {
+        if (off >= len) return 0;
+        const uint64_t m = std::min<uint64_t>(n, len - off);
+        if (host) memcpy(dst, host + off, m);
+        else if (cudaMemcpy(dst, dev + off, m, cudaMemcpyDeviceToHost) != cudaSuccess) return 0;
+        return m;
+    }
+};
+
+struct Streaminfo {
+    uint32_t min_block = 0, max_block = 0, min_frame = 0, max_frame = 0;
+    uint32_t sample_rate = 0, channels_m1 = 0, depth_m1 = 0;
+    uint64_t total = 0;
+    uint8_t md5[16] = {0};
+};
+
+// src/zflac.zig:217-253 + :309: signature, metadata blocks, STREAMINFO.
+int parse_metadata(const ByteSource &src, Streaminfo &si, uint64_t &audio_offset) {
+    uint8_t b[40];
+    if (src.get(0, 4, b) < 4) return ZFLACB200_END_OF_STREAM;
+    if (!(b[0] == 0x66 && b[1] == 0x4C && b[2] == 0x61 && b[3] == 0x43)) return ZFLACB200_INVALID_SIGNATURE;
+    uint64_t pos = 4;
+    bool have = false;
+    for (;;) {
+        if (src.get(pos, 4, b) < 4) return ZFLACB200_END_OF_STREAM;
+        pos += 4;
+        const unsigned type = b[0] & 0x7F;
+        const bool last = (b[0] & 0x80) != 0;
+        const uint32_t length = ((uint32_t)b[1] << 16) | ((uint32_t)b[2] << 8) | b[3];
+        if (type == 0) {  // STREAMINFO: always 34 bytes, the length field is not consulted (Q13)
+            if (src.get(pos, 34, b) < 34) return ZFLACB200_END_OF_STREAM;
+            pos += 34;
+            si.min_block = ((uint32_t)b[0] << 8) | b[1];
+            si.max_block = ((uint32_t)b[2] << 8) | b[3];
+            si.min_frame = ((uint32_t)b[4] << 16) | ((uint32_t)b[5] << 8) | b[6];
+            si.max_frame = ((uint32_t)b[7] << 16) | ((uint32_t)b[8] << 8) | b[9];
+            si.sample_rate = ((uint32_t)b[10] << 12) | ((uint32_t)b[11] << 4) | (b[12] >> 4);
+            si.channels_m1 = (b[12] >> 1) & 7;
+            si.depth_m1 = ((b[12] & 1u) << 4) | (b[13] >> 4);
+            si.total = ((uint64_t)(b[13] & 15) << 32) | ((uint64_t)b[14] << 24) | ((uint64_t)b[15] << 16) | ((uint64_t)b[16] << 8) | b[17];
+            memcpy(si.md5, b + 18, 16);
+            have = true;
+        } else if (type >= 1 && type <= 6) {
+            if (src.len - pos < length) return ZFLACB200_END_OF_STREAM;
+            pos += length;
+        } else {
+            return ZFLACB200_INVALID_METADATA_HEADER;
+        }
+        if (last) break;
+    }
+    if (!have) return ZFLACB200_MISSING_STREAMINFO;
+    audio_offset = pos;
+    return ZFLACB200_OK;
+}
+
+const uint32_t kRate[16] = {0, 88200, 176400, 192000, 8000, 16000, 22050, 24000, 32000, 44100, 48000, 96000, 0, 0, 0, 0};
+const uint8_t kChCount[16] = {1, 2, 3, 4, 5, 6, 7, 8, 2, 2, 2, 0, 0, 0, 0, 0};
+const uint8_t kBps[8] = {0, 8, 12, 0, 16, 20, 24, 32};
+
+struct Hdr {
+    uint32_t block_size = 0, sr_value = 0;
+    uint8_t n_before_crc = 0, ch_code = 0, bd_code = 0, sr_code = 0;
+};
+
+// Frame header at a position the scan did not emit: same checks in the same order as the
+// reference (:343-374). `n_before_crc` excludes the CRC-8 byte (read later, :407).
+int host_parse_header(const ByteSource &src, uint64_t pos, Hdr &h) {
+    uint8_t b[16] = {0};
+    const uint64_t avail = src.get(pos, 16, b);
+    if (avail < 4) return ZFLACB200_END_OF_STREAM;
+    if (!(b[0] == 0xFF && (b[1] & 0xFE) == 0xF8)) return ZFLACB200_INVALID_FRAME_HEADER;
+    const unsigned bs_code = b[2] >> 4, sr_code = b[2] & 15;
+    h.ch_code = b[3] >> 4;
+    h.bd_code = (b[3] >> 1) & 7;
+    h.sr_code = (uint8_t)sr_code;
+    if (avail < 5) return ZFLACB200_END_OF_STREAM;
+    const unsigned c0 = b[4];
+    unsigned ones = 0;
+    while (ones < 8 && (c0 & (0x80u >> ones))) ++ones;
+    if (c0 == 0xFF || ones == 1) return ZFLACB200_INVALID_CODED_NUMBER;
+    unsigned n = 4 + (ones == 0 ? 1 : ones);
+    if (n > avail) return ZFLACB200_END_OF_STREAM;
+    if (bs_code == 0) return ZFLACB200_INVALID_FRAME_HEADER;
+    if (bs_code == 6) {
+        if (n + 1 > avail) return ZFLACB200_END_OF_STREAM;
+        h.block_size = (uint32_t)b[n] + 1;
+        n += 1;
+    } else if (bs_code == 7) {
+        if (n + 2 > avail) return ZFLACB200_END_OF_STREAM;
+        const uint32_t v = ((uint32_t)b[n] << 8) | b[n + 1];
+        if (v == 0xFFFF) return ZFLACB200_INVALID_FRAME_HEADER;
+        h.block_size = v + 1;
+        n += 2;
+    } else if (bs_code == 1) h.block_size = 192;
+    else if (bs_code <= 5) h.block_size = 144u << bs_code;
+    else h.block_size = 1u << bs_code;
+    h.sr_value = kRate[sr_code];
+    if (sr_code == 12) {
+        if (n + 1 > avail) return ZFLACB200_END_OF_STREAM;
+        h.sr_value = b[n];
+        n += 1;
+    } else if (sr_code == 13 || sr_code == 14) {
+        if (n + 2 > avail) return ZFLACB200_END_OF_STREAM;
+        h.sr_value = (((uint32_t)b[n] << 8) | b[n + 1]) * (sr_code == 14 ? 10u : 1u);
+        n += 2;
+    } else if (sr_code == 15) return ZFLACB200_INVALID_FRAME_HEADER;
+    h.n_before_crc = (uint8_t)n;
+    return ZFLACB200_OK;
+}
+
+struct ChainFrame {
+    FrameRec rec;
+    uint64_t expect_end;
+    bool probed;
+};
+
+struct Chain {
+    std::vector<ChainFrame> frames;
+    int status = ZFLACB200_OK;  // error that ends the stream, reported unless an earlier frame fails in K2
+    uint64_t n_samples = 0;
+    uint64_t scratch_elems = 0;
+    uint32_t max_block = 0;
+    uint8_t channels = 0, bps = 0;
+    uint32_t sample_rate = 0;
+    uint64_t n_probed = 0;
+};
+
+struct Pipeline {
+    const uint8_t *d_stream = nullptr;
+    uint64_t len = 0;
+    cudaStream_t st = nullptr;
+    ByteSource src;
+    Streaminfo si;
+    uint64_t audio_offset = 0;
+    std::vector<Cand> cands;
+    std::vector<uint32_t> link;
+    std::unordered_map<uint64_t, FrameOut> known;  // frame offset -> end/status found by decoding it
+    bool use_links = true;
+    bool wide = false;  // 32 bps stream: int64 scratch
+    // one-frame probe buffers
+    FrameRec *d_probe_rec = nullptr;
+    FrameOut *d_probe_out = nullptr;
+
+    int probe(const FrameRec &rec, FrameOut &out) {
+        CU_CHECK(cudaMemcpyAsync(d_probe_rec, &rec, sizeof(rec), cudaMemcpyHostToDevice, st));
+        CU_CHECK(launch_decode_frames(d_stream, len, d_probe_rec, 1, nullptr, wide, d_probe_out, false, st));
+        CU_CHECK(cudaMemcpyAsync(&out, d_probe_out, sizeof(out), cudaMemcpyDeviceToHost, st));
+        CU_CHECK(cudaStreamSynchronize(st));
+        return ZFLACB200_OK;
+    }
+
+    // The reference's frame loop (:340-581) minus the per-sample work. Returns a CUDA-level
+    // status; the stream-level outcome is chain.status.
+    int build_chain(Chain &ch) {
+        ch = Chain();
+        bool first = true;
+        uint32_t sample_rate = 0, channel_count = 0, bd_code = 0, bps = 0;
+        bool valid_total = si.total > 0;
+        const uint64_t expected_channels = (uint64_t)si.channels_m1 + 1;
+        const uint64_t total = expected_channels * (valid_total ? si.total : 4096);
+        uint64_t samples_len = total;
+        uint64_t pos = audio_offset, off = 0;
+        size_t ci = 0;  // moving index into cands (sorted by offset)
+        for (;;) {
+            if (valid_total && off >= total) break;  // :341
+            if (len - std::min(pos, len) < 4) {        // readInt(u32) fails (:343-350)
+                if (valid_total) ch.status = ZFLACB200_END_OF_STREAM;
+                break;
+            }
+            while (ci < cands.size() && cands[ci].offset < pos) ++ci;
+            const bool is_cand = ci < cands.size() && cands[ci].offset == pos;
+            Hdr h;
+            if (is_cand) {
+                const Cand &c = cands[ci];
+                h.block_size = c.block_size;
+                h.sr_value = c.sr_value;
+                h.n_before_crc = c.header_len - 1;
+                h.ch_code = c.ch_code;
+                h.bd_code = c.bd_code;
+                h.sr_code = c.sr_code;
+            } else {
+                const int e = host_parse_header(src, pos, h);
+                if (e != ZFLACB200_OK) {
+                    ch.status = e;
+                    break;
+                }
+            }
+            const uint32_t frame_rate = (h.sr_code == 0) ? si.sample_rate : h.sr_value;
+            if (first) {  // :376-388
+                sample_rate = frame_rate;
+                channel_count = kChCount[h.ch_code];
+                bd_code = h.bd_code;
+                if (bd_code == 0) bps = si.depth_m1 + 1;
+                else if (bd_code == 3) { ch.status = ZFLACB200_UNDEFINED_IN_REFERENCE; break; }
+                else bps = kBps[bd_code];
+                if (channel_count != expected_channels) { ch.status = ZFLACB200_INCONSISTENT_PARAMETERS; break; }
+                first = false;
+                ch.channels = (uint8_t)channel_count;
+                ch.bps = (uint8_t)bps;
+                ch.sample_rate = sample_rate & 0xFFFFFF;
+            } else if (sample_rate != frame_rate || channel_count != kChCount[h.ch_code] || bd_code != h.bd_code) {
+                ch.status = ZFLACB200_INCONSISTENT_PARAMETERS;  // :391
+                break;
+            }
+            const uint64_t expected = off + (uint64_t)h.block_size * channel_count;  // :394-402
+            if (samples_len < expected) {
+                samples_len = std::max(2 * samples_len, expected);
+                valid_total = false;
+            }
+            if (h.block_size == 1 && valid_total && off + channel_count < total) {  // :405
+                ch.status = ZFLACB200_INVALID_FRAME_HEADER;
+                break;
+            }
+            if (pos + h.n_before_crc + 1 > len) {  // CRC-8 byte (:407)
+                ch.status = ZFLACB200_END_OF_STREAM;
+                break;
+            }
+            ChainFrame cf;
+            cf.rec.offset = pos;
+            cf.rec.sample_base = off;
+            cf.rec.scratch_base = ch.scratch_elems;
+            cf.rec.block_size = h.block_size;
+            cf.rec.scratch_pitch = round_up_u32(h.block_size, 8);
+            cf.rec.header_len = h.n_before_crc + 1;
+            cf.rec.ch_code = h.ch_code;
+            cf.rec.channels = (uint8_t)channel_count;
+            cf.rec.bps = (uint8_t)bps;
+            cf.rec.stream_id = 0;
+            cf.probed = false;
+            // where does this frame end?
+            FrameOut fo;
+            auto it = known.find(pos);
+            if (it != known.end()) {
+                fo = it->second;
+                cf.probed = true;
+            } else if (use_links && is_cand && link[ci] != kNoLink) {
+                fo.status = ST_OK;
+                fo.end_offset = link[ci] < cands.size() ? cands[link[ci]].offset : len;
+                fo.stored_crc16 = 0;
+            } else {
+                const int e = probe(cf.rec, fo);
+                if (e != ZFLACB200_OK) return e;
+                known[pos] = fo;
+                cf.probed = true;
+                ++ch.n_probed;
+            }
+            if (fo.status != ST_OK) {
+                ch.status = (int)fo.status;
+                break;
+            }
+            cf.expect_end = fo.end_offset;
+            ch.frames.push_back(cf);
+            ch.scratch_elems += (uint64_t)cf.rec.scratch_pitch * channel_count;
+            ch.max_block = std::max(ch.max_block, h.block_size);
+            off += (uint64_t)h.block_size * channel_count;  // :580
+            pos = fo.end_offset;
+        }
+        ch.n_samples = off;
+        return ZFLACB200_OK;
+    }
+};
+
+struct Events {
+    cudaEvent_t e[8];
+    bool made = false;
+    int init() {
+        for (auto &x : e) CU_CHECK(cudaEventCreate(&x));
+        made = true;
+        return ZFLACB200_OK;
+    }
+    ~Events() {
+        if (made)
+            for (auto &x : e) cudaEventDestroy(x);
+    }
+};
+
+float ev_ms(cudaEvent_t a, cudaEvent_t b) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+}
+
+}  // namespace
+
+struct zflacb200_stream {
+    int device = 0;
+    void *d_pcm = nullptr;
+    uint64_t pcm_bytes = 0;
+    zflacb200_info info;
+    std::vector<zflacb200_frame> frames;
+};
+
+namespace {
+
+struct DevBuf {  // stream-ordered allocation released on scope exit
+    void *p = nullptr;
+    cudaStream_t st = nullptr;
+    int alloc(size_t bytes, cudaStream_t s) {
+        st = s;
+        CU_CHECK(cudaMallocAsync(&p, bytes ? bytes : 16, s));
+        return ZFLACB200_OK;
+    }
+    void *release() {
+        void *r = p;
+        p = nullptr;
+        return r;
+    }
+    ~DevBuf() {
+        if (p) cudaFreeAsync(p, st);
+    }
+};
+
+int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info) {
+    if (!data || !out || !info) {
+        g_last_error = "null argument";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    *out = nullptr;
+    memset(info, 0, sizeof(*info));
+    const uint32_t flags = opt ? opt->flags : 0;
+    int device = -1;
+    {
+        const int e = ensure_device(opt ? opt->device : -1, &device);
+        if (e != ZFLACB200_OK) return e;
+    }
+    cudaStream_t st = (opt && opt->stream) ? (cudaStream_t)opt->stream : g_ctx[device].stream;
+    const bool on_device = (flags & ZFLACB200_INPUT_ON_DEVICE) != 0;
+
+    Pipeline pl;
+    pl.len = len;
+    pl.st = st;
+    pl.src.len = len;
+    if (on_device) pl.src.dev = data;
+    else pl.src.host = data;
+    pl.use_links = (flags & ZFLACB200_NO_CRC_ACCEL) == 0;
+
+    // ---- signature + metadata (host, a few dozen bytes)
+    {
+        const int e = parse_metadata(pl.src, pl.si, pl.audio_offset);
+        if (e != ZFLACB200_OK) return e;
+    }
+    const uint32_t depth = pl.si.depth_m1 + 1;            // :256
+    const uint32_t aligned = (depth + 7u) & ~7u;          // :257
+    const uint32_t container_bytes = aligned == 8 ? 1 : aligned == 16 ? 2 : 4;  // :259-264
+    memcpy(info->md5_streaminfo, pl.si.md5, 16);
+    info->audio_offset = pl.audio_offset;
+    info->container_bytes = (uint8_t)container_bytes;
+
+    Events ev;
+    if (ev.init() != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(cudaEventRecord(ev.e[0], st));
+
+    // ---- stream bytes in HBM
+    DevBuf b_stream;
+    if (on_device) {
+        pl.d_stream = data;
+    } else {
+        if (b_stream.alloc(((len + 15) & ~15ull) + 64, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+        CU_CHECK(cudaMemcpyAsync(b_stream.p, data, len, cudaMemcpyHostToDevice, st));
+        pl.d_stream = (const uint8_t *)b_stream.p;
+    }
+
+    DevBuf b_probe_rec, b_probe_out;
+    if (b_probe_rec.alloc(sizeof(FrameRec), st) || b_probe_out.alloc(sizeof(FrameOut), st)) return ZFLACB200_CUDA_ERROR;
+    pl.d_probe_rec = (FrameRec *)b_probe_rec.p;
+    pl.d_probe_out = (FrameOut *)b_probe_out.p;
+
+    // ---- K1: sync scan -> candidates in stream order
+    CU_CHECK(cudaEventRecord(ev.e[1], st));
+    uint32_t n_cand = 0;
+    DevBuf b_cands, b_total, b_tiles, b_ticket, b_link;
+    {
+        const uint32_t n_tiles = scan_tile_count(pl.audio_offset, len);
+        uint32_t cap = (uint32_t)std::min<uint64_t>(len / 256 + 4096, 0x7FFFFFFFull);
+        if (b_total.alloc(sizeof(uint32_t), st) || b_ticket.alloc(sizeof(uint32_t), st) ||
+            b_tiles.alloc(sizeof(unsigned long long) * std::max<uint32_t>(n_tiles, 1), st))
+            return ZFLACB200_CUDA_ERROR;
+        for (int attempt = 0; attempt < 2; ++attempt) {
+            if (b_cands.p) { cudaFreeAsync(b_cands.p, st); b_cands.p = nullptr; }
+            if (b_cands.alloc(sizeof(Cand) * (size_t)cap, st)) return ZFLACB200_CUDA_ERROR;
+            CU_CHECK(launch_sync_scan(pl.d_stream, pl.audio_offset, len, (Cand *)b_cands.p, cap, (uint32_t *)b_total.p,
+                                      (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
+            CU_CHECK(cudaMemcpyAsync(&n_cand, b_total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CU_CHECK(cudaStreamSynchronize(st));
+            if (n_cand <= cap) break;
+            cap = n_cand;  // pathological density of valid headers: rerun with room for all of them
+        }
+    }
+    CU_CHECK(cudaEventRecord(ev.e[2], st));
+
+    // ---- K1b: CRC-16 links between neighbouring candidates
+    if (b_link.alloc(sizeof(uint32_t) * std::max<uint32_t>(n_cand, 1), st)) return ZFLACB200_CUDA_ERROR;
+    pl.cands.resize(n_cand);
+    pl.link.assign(n_cand, kNoLink);
+    if (n_cand) {
+        if (pl.use_links)
+            CU_CHECK(launch_frame_link(pl.d_stream, len, (const Cand *)b_cands.p, n_cand, (uint32_t *)b_link.p, 4, 16ull << 20, st));
+        CU_CHECK(cudaMemcpyAsync(pl.cands.data(), b_cands.p, sizeof(Cand) * n_cand, cudaMemcpyDeviceToHost, st));
+        if (pl.use_links)
+            CU_CHECK(cudaMemcpyAsync(pl.link.data(), b_link.p, sizeof(uint32_t) * n_cand, cudaMemcpyDeviceToHost, st));
+    }
+    CU_CHECK(cudaEventRecord(ev.e[3], st));
+    CU_CHECK(cudaStreamSynchronize(st));
+    info->n_candidates = n_cand;
+
+    // ---- chain + K2, repeated only if a decoded frame end contradicts a CRC-16 link
+    Chain chain;
+    DevBuf b_frames, b_outs, b_scratch, b_pcm;
+    std::vector<FrameOut> outs;
+    int final_status = ZFLACB200_OK;
+    bool decoded_ok = false;
+    {   // a 32 bps stream (side channel: 33 bits) runs on the int64 scratch; bps is latched by the first frame
+        Hdr h0;
+        if (host_parse_header(pl.src, pl.audio_offset, h0) == ZFLACB200_OK)
+            pl.wide = (h0.bd_code == 0 ? depth : kBps[h0.bd_code]) == 32;
+    }
+    for (int round = 0; round < 64 && !decoded_ok; ++round) {
+        if (round == 63) pl.use_links = false;  // give up on links: probe everything (always consistent)
+        {
+            const int e = pl.build_chain(chain);
+            if (e != ZFLACB200_OK) return e;
+        }
+        const uint32_t nf = (uint32_t)chain.frames.size();
+        const bool write = chain.status == ZFLACB200_OK;
+        std::vector<FrameRec> recs(nf);
+        for (uint32_t i = 0; i < nf; ++i) recs[i] = chain.frames[i].rec;
+        if (b_frames.p) { cudaFreeAsync(b_frames.p, st); b_frames.p = nullptr; }
+        if (b_outs.p) { cudaFreeAsync(b_outs.p, st); b_outs.p = nullptr; }
+        if (b_scratch.p) { cudaFreeAsync(b_scratch.p, st); b_scratch.p = nullptr; }
+        if (b_frames.alloc(sizeof(FrameRec) * std::max<uint32_t>(nf, 1), st) || b_outs.alloc(sizeof(FrameOut) * std::max<uint32_t>(nf, 1), st))
+            return ZFLACB200_CUDA_ERROR;
+        if (write && b_scratch.alloc(chain.scratch_elems * (pl.wide ? 8 : 4), st)) return ZFLACB200_CUDA_ERROR;
+        outs.resize(nf);
+        if (nf) {
+            CU_CHECK(cudaMemcpyAsync(b_frames.p, recs.data(), sizeof(FrameRec) * nf, cudaMemcpyHostToDevice, st));
+            CU_CHECK(cudaEventRecord(ev.e[4], st));
+            CU_CHECK(launch_decode_frames(pl.d_stream, len, (const FrameRec *)b_frames.p, nf, b_scratch.p, pl.wide,
+                                          (FrameOut *)b_outs.p, write, st));
+            CU_CHECK(cudaEventRecord(ev.e[5], st));
+            CU_CHECK(cudaMemcpyAsync(outs.data(), b_outs.p, sizeof(FrameOut) * nf, cudaMemcpyDeviceToHost, st));
+            CU_CHECK(cudaStreamSynchronize(st));
+        } else {
+            CU_CHECK(cudaEventRecord(ev.e[4], st));
+            CU_CHECK(cudaEventRecord(ev.e[5], st));
+        }
+        decoded_ok = true;
+        for (uint32_t i = 0; i < nf; ++i) {
+            if (outs[i].status != ST_OK) {  // first failing frame in stream order wins
+                final_status = (int)outs[i].status;
+                break;
+            }
+            if (outs[i].end_offset != chain.frames[i].expect_end) {  // link disagreed with the decode: decode is the truth
+                pl.known[chain.frames[i].rec.offset] = outs[i];
+                decoded_ok = false;
+                break;
+            }
+        }
+        if (final_status != ZFLACB200_OK) return final_status;
+    }
+    if (!decoded_ok) {
+        g_last_error = "frame chain did not converge";
+        return ZFLACB200_CUDA_ERROR;
+    }
+    if (chain.status != ZFLACB200_OK) return chain.status;
+
+    const uint32_t nf = (uint32_t)chain.frames.size();
+    const uint64_t pcm_bytes = chain.n_samples * container_bytes;
+    if (b_pcm.alloc(pcm_bytes + 64, st)) return ZFLACB200_CUDA_ERROR;
+
+    // ---- K3: decorrelate + shift + interleave
+    uint32_t msb_shift = 0;  // :287-306, keyed on the STREAMINFO depth
+    if (depth >= 9 && depth <= 15) msb_shift = 16 - depth;
+    else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
+    DevBuf b_flag, b_jobs, b_digest;
+    if (b_flag.alloc(sizeof(uint32_t), st) || b_jobs.alloc(sizeof(Md5Job), st) || b_digest.alloc(16, st)) return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(cudaMemsetAsync(b_flag.p, 0, sizeof(uint32_t), st));
+    EpilogueParams ep;
+    ep.frames = (const FrameRec *)b_frames.p;
+    ep.n_frames = nf;
+    ep.max_block_size = chain.max_block;
+    ep.scratch = b_scratch.p;
+    ep.wide_scratch = pl.wide;
+    ep.pcm = b_pcm.p;
+    ep.container_bytes = container_bytes;
+    ep.msb_shift = msb_shift;
+    ep.lossy_flag = (uint32_t *)b_flag.p;
+    CU_CHECK(launch_epilogue(ep, st));
+    CU_CHECK(cudaEventRecord(ev.e[6], st));
+
+    // ---- K4: MD5 gate
+    const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0;
+    uint32_t lossy = 0;
+    if (do_md5) {
+        if (msb_shift) {
+            CU_CHECK(cudaMemcpyAsync(&lossy, b_flag.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CU_CHECK(cudaStreamSynchronize(st));
+            if (lossy) {  // a sample exceeds the STREAMINFO depth (Q5): hash the unshifted values, shift afterwards
+                ep.msb_shift = 0;
+                CU_CHECK(launch_epilogue(ep, st));
+            }
+        }
+        Md5Job job;
+        job.pcm = b_pcm.p;
+        job.n_samples = chain.n_samples;
+        job.container_bytes = container_bytes;
+        job.hash_bytes = aligned == 24 ? 3 : container_bytes;  // :268-277
+        job.unshift = lossy ? 0 : msb_shift;
+        job.pad = 0;
+        CU_CHECK(cudaMemcpyAsync(b_jobs.p, &job, sizeof(job), cudaMemcpyHostToDevice, st));
+        CU_CHECK(launch_md5((const Md5Job *)b_jobs.p, 1, (uint8_t *)b_digest.p, st));
+        if (lossy) CU_CHECK(launch_shift_inplace(b_pcm.p, chain.n_samples, container_bytes, msb_shift, st));
+        CU_CHECK(cudaMemcpyAsync(info->md5_computed, b_digest.p, 16, cudaMemcpyDeviceToHost, st));
+    }
+    CU_CHECK(cudaEventRecord(ev.e[7], st));
+    CU_CHECK(cudaStreamSynchronize(st));
+
+    info->ms_scan = ev_ms(ev.e[1], ev.e[2]);
+    info->ms_link = ev_ms(ev.e[2], ev.e[3]);
+    info->ms_decode = ev_ms(ev.e[4], ev.e[5]);
+    info->ms_epilogue = ev_ms(ev.e[5], ev.e[6]);
+    info->ms_md5 = ev_ms(ev.e[6], ev.e[7]);
+    info->ms_total = ev_ms(ev.e[0], ev.e[7]);
+    info->md5_checked = do_md5 ? 1 : 0;
+    if (do_md5 && memcmp(info->md5_computed, pl.si.md5, 16) != 0) return ZFLACB200_INVALID_CHECKSUM;  // :279-280
+
+    info->channels = chain.channels;
+    info->bits_per_sample = chain.bps;
+    info->sample_rate = chain.sample_rate;
+    info->n_samples = chain.n_samples;
+    info->pcm_bytes = pcm_bytes;
+    info->n_frames = nf;
+    info->n_probed_frames = chain.n_probed;
+    info->audio_bytes = nf ? chain.frames.back().expect_end - pl.audio_offset : 0;
+
+    zflacb200_stream *h = new zflacb200_stream();
+    h->device = device;
+    h->pcm_bytes = pcm_bytes;
+    h->frames.resize(nf);
+    for (uint32_t i = 0; i < nf; ++i) {
+        zflacb200_frame &f = h->frames[i];
+        const ChainFrame &cf = chain.frames[i];
+        f.offset = cf.rec.offset;
+        f.end_offset = cf.expect_end;
+        f.sample_offset = cf.rec.sample_base;
+        f.block_size = cf.rec.block_size;
+        f.header_len = cf.rec.header_len;
+        f.channel_code = cf.rec.ch_code;
+        f.crc16_ok = cf.probed ? 2 : 1;  // 2 = not verified by a link (see n_crc16_mismatch)
+        f.probed = cf.probed ? 1 : 0;
+    }
+    // CRC-16 diagnostic for frames that were not linked (the reference ignores the CRC, Q1)
+    {
+        std::vector<uint64_t> rb, re;
+        std::vector<uint32_t> idx;
+        for (uint32_t i = 0; i < nf; ++i)
+            if (chain.frames[i].probed) {
+                rb.push_back(chain.frames[i].rec.offset);
+                re.push_back(chain.frames[i].expect_end - 2);
+                idx.push_back(i);
+            }
+        if (!rb.empty()) {
+            DevBuf b_rb, b_re, b_crc;
+            const size_t m = rb.size();
+            if (b_rb.alloc(8 * m, st) || b_re.alloc(8 * m, st) || b_crc.alloc(2 * m, st)) return ZFLACB200_CUDA_ERROR;
+            std::vector<uint16_t> crc(m);
+            CU_CHECK(cudaMemcpyAsync(b_rb.p, rb.data(), 8 * m, cudaMemcpyHostToDevice, st));
+            CU_CHECK(cudaMemcpyAsync(b_re.p, re.data(), 8 * m, cudaMemcpyHostToDevice, st));
+            CU_CHECK(launch_crc16_ranges(pl.d_stream, (const uint64_t *)b_rb.p, (const uint64_t *)b_re.p, (uint32_t)m, (uint16_t *)b_crc.p, st));
+            CU_CHECK(cudaMemcpyAsync(crc.data(), b_crc.p, 2 * m, cudaMemcpyDeviceToHost, st));
+            CU_CHECK(cudaStreamSynchronize(st));
+            for (size_t k = 0; k < m; ++k) {
+                const bool ok = crc[k] == (uint16_t)outs[idx[k]].stored_crc16;
+                h->frames[idx[k]].crc16_ok = ok ? 1 : 0;
+                if (!ok) ++info->n_crc16_mismatch;
+            }
+        }
+    }
+    h->d_pcm = b_pcm.release();
+    h->info = *info;
+    *out = h;
+    return ZFLACB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int zflacb200_abi_version(void) { return ZFLACB200_ABI_VERSION; }
+
+int zflacb200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int zflacb200_init(int device) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    int d;
+    return ensure_device(device, &d);
+}
+
+void zflacb200_shutdown(void) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    for (int d = 0; d < 64; ++d)
+        if (g_ctx[d].ready) {
+            cudaSetDevice(d);
+            cudaStreamDestroy(g_ctx[d].stream);
+            g_ctx[d] = DeviceCtx();
+        }
+}
+
+const char *zflacb200_status_name(int status) {
+    switch (status) {
+        case ZFLACB200_OK: return "OK";
+        case ZFLACB200_INVALID_SIGNATURE: return "InvalidSignature";
+        case ZFLACB200_INVALID_METADATA_HEADER: return "InvalidMetadataHeader";
+        case ZFLACB200_UNIMPLEMENTED: return "Unimplemented";
+        case ZFLACB200_INVALID_CHECKSUM: return "InvalidChecksum";
+        case ZFLACB200_MISSING_STREAMINFO: return "MissingStreaminfo";
+        case ZFLACB200_INVALID_FRAME_HEADER: return "InvalidFrameHeader";
+        case ZFLACB200_INVALID_CODED_NUMBER: return "InvalidCodedNumber";
+        case ZFLACB200_INCONSISTENT_PARAMETERS: return "InconsistentParameters";
+        case ZFLACB200_INVALID_SUBFRAME_HEADER: return "InvalidSubframeHeader";
+        case ZFLACB200_INVALID_RESIDUAL_CODING_METHOD: return "InvalidResidualCodingMethod";
+        case ZFLACB200_END_OF_STREAM: return "EndOfStream";
+        case ZFLACB200_OUT_OF_MEMORY: return "OutOfMemory";
+        case ZFLACB200_UNDEFINED_IN_REFERENCE: return "UndefinedInReference";
+        case ZFLACB200_CUDA_ERROR: return "CudaError";
+        case ZFLACB200_INVALID_ARGUMENT: return "InvalidArgument";
+        default: return "Unknown";
+    }
+}
+
+const char *zflacb200_last_error(void) { return g_last_error.c_str(); }
+
+int zflacb200_open(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    g_last_error.clear();
+    return open_impl(data, len, opt, out, info);
+}
+
+int zflacb200_read(zflacb200_stream *s, void *dst, size_t dst_bytes) {
+    if (!s || (!dst && s->pcm_bytes)) return ZFLACB200_INVALID_ARGUMENT;
+    if (dst_bytes < s->pcm_bytes) {
+        g_last_error = "destination smaller than pcm_bytes";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    std::lock_guard<std::mutex> lock(g_mutex);
+    CU_CHECK(cudaSetDevice(s->device));
+    if (s->pcm_bytes) CU_CHECK(cudaMemcpy(dst, s->d_pcm, s->pcm_bytes, cudaMemcpyDeviceToHost));
+    return ZFLACB200_OK;
+}
+
+int zflacb200_device_pcm(zflacb200_stream *s, void **dev_ptr, size_t *bytes) {
+    if (!s || !dev_ptr || !bytes) return ZFLACB200_INVALID_ARGUMENT;
+    *dev_ptr = s->d_pcm;
+    *bytes = s->pcm_bytes;
+    return ZFLACB200_OK;
+}
+
+void zflacb200_close(zflacb200_stream *s) {
+    if (!s) return;
+    std::lock_guard<std::mutex> lock(g_mutex);
+    cudaSetDevice(s->device);
+    if (s->d_pcm) cudaFreeAsync(s->d_pcm, g_ctx[s->device].stream);
+    delete s;
+}
+
+int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *opt, void *dst, size_t dst_capacity, zflacb200_info *info) {
+    zflacb200_stream *h = nullptr;
+    const int e = zflacb200_open(data, len, opt, &h, info);
+    if (e != ZFLACB200_OK) return e;
+    int r = ZFLACB200_OK;
+    if (dst_capacity < info->pcm_bytes) r = ZFLACB200_OUT_OF_MEMORY;
+    else r = zflacb200_read(h, dst, dst_capacity);
+    zflacb200_close(h);
+    return r;
+}
+
+int zflacb200_open_batch(const uint8_t *const *datas, const size_t *lens, size_t n, const zflacb200_options *opt,
+                         zflacb200_stream **outs, zflacb200_info *infos, int *statuses) {
+    if (!datas || !lens || !outs || !infos || !statuses) return ZFLACB200_INVALID_ARGUMENT;
+    int worst = ZFLACB200_OK;
+    for (size_t i = 0; i < n; ++i) {
+        statuses[i] = zflacb200_open(datas[i], lens[i], opt, &outs[i], &infos[i]);
+        if (statuses[i] == ZFLACB200_CUDA_ERROR) worst = ZFLACB200_CUDA_ERROR;
+    }
+    return worst;
+}
+
+int zflacb200_frames(zflacb200_stream *s, zflacb200_frame *dst, size_t capacity, size_t *n_frames) {
+    if (!s || !n_frames) return ZFLACB200_INVALID_ARGUMENT;
+    *n_frames = s->frames.size();
+    if (dst) memcpy(dst, s->frames.data(), sizeof(zflacb200_frame) * std::min(capacity, s->frames.size()));
+    return ZFLACB200_OK;
+}
+
+}  // extern "C"

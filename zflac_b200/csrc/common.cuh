@@ -1,0 +1,70 @@
+// common.cuh — records shared by the host pipeline and the sm_100a kernels.
+//
+// Pipeline:
+//   K1  sync_scan      coalesced scan of the compressed stream -> frame candidates
+//                      (header grammar + CRC-8), ordered compaction (ballot + decoupled look-back)
+//   K1b frame_link     CRC-16 over the bytes between neighbouring candidates -> verified frame
+//                      ends without entropy decoding (the reference ignores the CRCs, Q1; here they
+//                      are accelerators, the chain stays the truth)
+//   K2  decode_frames  one thread per frame: Rice + CONSTANT/VERBATIM/FIXED/LPC -> planar scratch
+//   K3  epilogue       decorrelation + MSB-align shift + narrow + interleave -> PCM
+//   K4  md5            STREAMINFO MD5 gate over the PCM
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace zf {
+
+// --- status codes: numerically identical to include/zflacb200.h ---
+enum : uint32_t {
+    ST_OK = 0,
+    ST_INVALID_FRAME_HEADER = 6,
+    ST_INVALID_CODED_NUMBER = 7,
+    ST_INCONSISTENT_PARAMETERS = 8,
+    ST_INVALID_SUBFRAME_HEADER = 9,
+    ST_INVALID_RESIDUAL_CODING_METHOD = 10,
+    ST_END_OF_STREAM = 11,
+    ST_UNDEFINED_IN_REFERENCE = 90,
+};
+
+constexpr uint32_t kNoLink = 0xFFFFFFFFu;
+
+// K1 output: one grammar- and CRC-8-valid frame header found in the stream.
+struct Cand {
+    uint64_t offset;      // byte offset of the sync code
+    uint32_t block_size;  // decoded block size (1..65535)
+    uint32_t sr_value;    // frame sample rate as the reference computes it (0 = "from STREAMINFO")
+    uint8_t header_len;   // bytes including the CRC-8
+    uint8_t ch_code;      // 4-bit channel assignment
+    uint8_t bd_code;      // 3-bit bit depth code
+    uint8_t sr_code;      // 4-bit sample rate code
+    uint32_t pad;
+};
+static_assert(sizeof(Cand) == 24, "Cand layout");
+
+// K2 input: one frame of the chain.
+struct FrameRec {
+    uint64_t offset;        // byte offset of the sync code
+    uint64_t sample_base;   // interleaved-sample offset of the frame in the PCM buffer
+    uint64_t scratch_base;  // element offset of the frame in the planar scratch
+    uint32_t block_size;
+    uint32_t scratch_pitch; // elements per channel plane (block_size rounded up to 8)
+    uint8_t header_len;
+    uint8_t ch_code;
+    uint8_t channels;
+    uint8_t bps;            // bits per sample latched from the first frame (zflac.zig:381-384)
+    uint32_t stream_id;     // batch mode: which stream the frame belongs to
+};
+static_assert(sizeof(FrameRec) == 40, "FrameRec layout");
+
+// K2 output.
+struct FrameOut {
+    uint64_t end_offset;  // byte offset just past the CRC-16 (valid when status == ST_OK)
+    uint32_t status;
+    uint32_t stored_crc16;
+};
+static_assert(sizeof(FrameOut) == 16, "FrameOut layout");
+
+__host__ __device__ inline uint32_t round_up_u32(uint32_t v, uint32_t m) { return (v + m - 1) / m * m; }
+
+}  // namespace zf

@@ -1,0 +1,261 @@
+// epilogue.cu — K3 epilogue and K4 md5 (sm_100a).
+//
+// K3 restates, per time step of a frame, the reference's stereo decorrelation
+// (src/zflac.zig:553-578), the narrowing store into the container type (:494, :537 — the
+// wasted-bit shift was already applied by K2) and the MSB-align shift (:287-306), and writes
+// the interleaved, frame-major/channel-minor PCM layout DecodedFLAC returns (:443). It reads
+// the planar scratch coalesced and writes whole interleaved time steps per thread.
+//
+// K4 restates the MD5 gate (:267-280): RFC 1321 over the little-endian container bytes of the
+// PRE-shift samples, 3 bytes per sample for 17..24-bit streams (Q4). A single stream's MD5 is
+// a serial chain (64 dependent steps per 64-byte block); lanes 1..31 only prefetch and pack.
+#include <type_traits>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace zf {
+
+constexpr int kEpiThreads = 256;
+
+template <typename ST> __device__ __forceinline__ int64_t ld_scratch(const ST *p) { return (int64_t)*p; }
+
+// Decorrelate one stereo pair (values are exact integers; int64 covers the 33-bit side channel).
+__device__ __forceinline__ void decorrelate(uint32_t ch_code, int64_t &a, int64_t &b) {
+    if (ch_code == 8) {         // left/side: R = L - S (:555-560)
+        b = a - b;
+    } else if (ch_code == 9) {  // side/right: L = S + R (:561-566)
+        a = a + b;
+    } else if (ch_code == 10) { // mid/side (:567-576)
+        const int64_t mid = (a << 1) + (b & 1);
+        const int64_t side = b;
+        a = (mid + side) >> 1;
+        b = (mid - side) >> 1;
+    }
+}
+
+template <typename CT> __device__ __forceinline__ CT narrow_shift(int64_t v, uint32_t shift, uint32_t &lossy) {
+    using UT = typename std::conditional<sizeof(CT) == 1, uint8_t, typename std::conditional<sizeof(CT) == 2, uint16_t, uint32_t>::type>::type;
+    const CT c = (CT)(UT)(uint64_t)v;            // @intCast narrowing (wraps where the reference is undefined)
+    const CT sh = (CT)(UT)((UT)c << shift);      // `<<=` discards the bits shifted out
+    if ((CT)(sh >> shift) != c) lossy = 1;
+    return sh;
+}
+
+template <typename ST, typename CT>
+__global__ void __launch_bounds__(kEpiThreads)
+k_epilogue(const FrameRec *__restrict__ frames, const ST *__restrict__ scratch, CT *__restrict__ pcm, uint32_t shift,
+           uint32_t *__restrict__ lossy_flag) {
+    const FrameRec fr = frames[blockIdx.x];
+    const uint32_t bs = fr.block_size, C = fr.channels;
+    const ST *src = scratch + fr.scratch_base;
+    CT *dst = pcm + fr.sample_base;
+    uint32_t lossy = 0;
+    for (uint32_t t = blockIdx.y * kEpiThreads + threadIdx.x; t < bs; t += gridDim.y * kEpiThreads) {
+        if (C == 2) {
+            int64_t a = ld_scratch(src + t), b = ld_scratch(src + fr.scratch_pitch + t);
+            decorrelate(fr.ch_code, a, b);
+            const CT ca = narrow_shift<CT>(a, shift, lossy), cb = narrow_shift<CT>(b, shift, lossy);
+            if (sizeof(CT) == 2) {
+                *reinterpret_cast<uint32_t *>(dst + 2 * (size_t)t) = (uint32_t)(uint16_t)ca | ((uint32_t)(uint16_t)cb << 16);
+            } else if (sizeof(CT) == 4) {
+                *reinterpret_cast<uint2 *>(dst + 2 * (size_t)t) = make_uint2((uint32_t)ca, (uint32_t)cb);
+            } else {
+                *reinterpret_cast<uint16_t *>(dst + 2 * (size_t)t) = (uint16_t)((uint8_t)ca | ((uint16_t)(uint8_t)cb << 8));
+            }
+        } else {
+            for (uint32_t c = 0; c < C; ++c) {
+                const int64_t v = ld_scratch(src + (size_t)c * fr.scratch_pitch + t);
+                dst[(size_t)t * C + c] = narrow_shift<CT>(v, shift, lossy);
+            }
+        }
+    }
+    if (lossy) atomicOr(lossy_flag, 1u);
+}
+
+template <typename CT>
+__global__ void k_shift_inplace(CT *__restrict__ pcm, uint64_t n, uint32_t shift) {
+    using UT = typename std::make_unsigned<CT>::type;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        pcm[i] = (CT)(UT)((UT)pcm[i] << shift);
+}
+
+cudaError_t launch_epilogue(const EpilogueParams &p, cudaStream_t st) {
+    if (p.n_frames == 0) return cudaSuccess;
+    uint32_t gy = (p.max_block_size + kEpiThreads - 1) / kEpiThreads;
+    if (gy > 64) gy = 64;
+    if (gy == 0) gy = 1;
+    dim3 grid(p.n_frames, gy);
+#define ZF_EPI(ST, CT) \
+    k_epilogue<ST, CT><<<grid, kEpiThreads, 0, st>>>(p.frames, (const ST *)p.scratch, (CT *)p.pcm, p.msb_shift, p.lossy_flag)
+    if (p.wide_scratch) {
+        if (p.container_bytes == 1) ZF_EPI(int64_t, int8_t);
+        else if (p.container_bytes == 2) ZF_EPI(int64_t, int16_t);
+        else ZF_EPI(int64_t, int32_t);
+    } else {
+        if (p.container_bytes == 1) ZF_EPI(int32_t, int8_t);
+        else if (p.container_bytes == 2) ZF_EPI(int32_t, int16_t);
+        else ZF_EPI(int32_t, int32_t);
+    }
+#undef ZF_EPI
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shift_inplace(void *pcm, uint64_t n_samples, uint32_t container_bytes, uint32_t shift, cudaStream_t st) {
+    if (n_samples == 0 || shift == 0) return cudaSuccess;
+    const int threads = 256;
+    uint64_t want = (n_samples + threads - 1) / threads;
+    const uint32_t blocks = (uint32_t)(want < 148ull * 16 ? want : 148ull * 16);
+    if (container_bytes == 2) k_shift_inplace<int16_t><<<blocks, threads, 0, st>>>((int16_t *)pcm, n_samples, shift);
+    else if (container_bytes == 4) k_shift_inplace<int32_t><<<blocks, threads, 0, st>>>((int32_t *)pcm, n_samples, shift);
+    else k_shift_inplace<int8_t><<<blocks, threads, 0, st>>>((int8_t *)pcm, n_samples, shift);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ K4: MD5 (RFC 1321)
+__constant__ uint32_t c_md5_k[64] = {
+    0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501,
+    0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821,
+    0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8,
+    0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a,
+    0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70,
+    0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665,
+    0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1,
+    0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
+
+#define MD5_STEP(f, a, b, c, d, m, k, s)                     \
+    do {                                                     \
+        a += f(b, c, d) + (m) + (k);                         \
+        a = __funnelshift_l(a, a, s) + b;                    \
+    } while (0)
+#define MD5_F(x, y, z) ((z) ^ ((x) & ((y) ^ (z))))
+#define MD5_G(x, y, z) ((y) ^ ((z) & ((x) ^ (y))))
+#define MD5_H(x, y, z) ((x) ^ (y) ^ (z))
+#define MD5_I(x, y, z) ((y) ^ ((x) | ~(z)))
+
+__device__ __forceinline__ void md5_block(uint32_t (&st)[4], const uint32_t *__restrict__ M) {
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3];
+    uint32_t m[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) m[i] = M[i];
+#define R1(i, a, b, c, d, s) MD5_STEP(MD5_F, a, b, c, d, m[(i)], c_md5_k[(i)], s)
+#define R2(i, a, b, c, d, s) MD5_STEP(MD5_G, a, b, c, d, m[(5 * (i) + 1) & 15], c_md5_k[(i)], s)
+#define R3(i, a, b, c, d, s) MD5_STEP(MD5_H, a, b, c, d, m[(3 * (i) + 5) & 15], c_md5_k[(i)], s)
+#define R4(i, a, b, c, d, s) MD5_STEP(MD5_I, a, b, c, d, m[(7 * (i)) & 15], c_md5_k[(i)], s)
+#pragma unroll
+    for (int i = 0; i < 16; i += 4) {
+        R1(i + 0, a, b, c, d, 7); R1(i + 1, d, a, b, c, 12); R1(i + 2, c, d, a, b, 17); R1(i + 3, b, c, d, a, 22);
+    }
+#pragma unroll
+    for (int i = 16; i < 32; i += 4) {
+        R2(i + 0, a, b, c, d, 5); R2(i + 1, d, a, b, c, 9); R2(i + 2, c, d, a, b, 14); R2(i + 3, b, c, d, a, 20);
+    }
+#pragma unroll
+    for (int i = 32; i < 48; i += 4) {
+        R3(i + 0, a, b, c, d, 4); R3(i + 1, d, a, b, c, 11); R3(i + 2, c, d, a, b, 16); R3(i + 3, b, c, d, a, 23);
+    }
+#pragma unroll
+    for (int i = 48; i < 64; i += 4) {
+        R4(i + 0, a, b, c, d, 6); R4(i + 1, d, a, b, c, 10); R4(i + 2, c, d, a, b, 15); R4(i + 3, b, c, d, a, 21);
+    }
+#undef R1
+#undef R2
+#undef R3
+#undef R4
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d;
+}
+
+// Byte `m` of the padded MD5 message of a job.
+template <int HB> __device__ __forceinline__ uint32_t md5_msg_byte(const Md5Job &j, uint64_t m, uint64_t msg_len, uint64_t padded_len) {
+    if (m < msg_len) {
+        const uint64_t smp = m / HB;
+        const uint32_t byt = (uint32_t)(m % HB);
+        int32_t v;
+        if (j.container_bytes == 1) v = ((const int8_t *)j.pcm)[smp];
+        else if (j.container_bytes == 2) v = ((const int16_t *)j.pcm)[smp];
+        else v = ((const int32_t *)j.pcm)[smp];
+        v >>= j.unshift;
+        return ((uint32_t)v >> (8 * byt)) & 0xFFu;
+    }
+    if (m == msg_len) return 0x80u;
+    if (m >= padded_len - 8) return (uint32_t)(((msg_len * 8) >> (8 * (m - (padded_len - 8)))) & 0xFFu);
+    return 0u;
+}
+
+constexpr int kMd5ChunkBlocks = 32;  // 64-byte blocks staged per round: one per lane
+
+template <int HB>
+__device__ void md5_run(const Md5Job &j, uint8_t *digest, uint32_t (*stage)[16]) {
+    const int lane = threadIdx.x & 31;
+    const uint64_t msg_len = j.n_samples * HB;
+    const uint64_t padded_len = (msg_len + 9 + 63) & ~63ull;
+    const uint64_t n_blocks = padded_len >> 6;
+    const bool raw = (HB == (int)j.container_bytes) && j.unshift == 0 && ((uintptr_t)j.pcm & 3) == 0;
+    uint32_t st[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+    for (uint64_t b0 = 0; b0 < n_blocks; b0 += kMd5ChunkBlocks) {
+        const uint64_t blk = b0 + lane;
+        if (blk < n_blocks) {
+            const uint64_t byte0 = blk << 6;
+            if (raw && byte0 + 64 <= msg_len) {  // the message is the PCM memory itself
+                const uint4 *p = reinterpret_cast<const uint4 *>((const uint8_t *)j.pcm + byte0);
+                if (((uintptr_t)p & 15) == 0) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint4 v = __ldg(p + q);
+                        stage[lane][4 * q + 0] = v.x; stage[lane][4 * q + 1] = v.y;
+                        stage[lane][4 * q + 2] = v.z; stage[lane][4 * q + 3] = v.w;
+                    }
+                } else {
+                    const uint32_t *pw = reinterpret_cast<const uint32_t *>((const uint8_t *)j.pcm + byte0);
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) stage[lane][q] = __ldg(pw + q);
+                }
+            } else {
+                for (int wi = 0; wi < 16; ++wi) {
+                    uint32_t w = 0;
+#pragma unroll
+                    for (int bb = 0; bb < 4; ++bb) w |= md5_msg_byte<HB>(j, byte0 + 4 * wi + bb, msg_len, padded_len) << (8 * bb);
+                    stage[lane][wi] = w;
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) {
+            const int nb = (n_blocks - b0) < (uint64_t)kMd5ChunkBlocks ? (int)(n_blocks - b0) : kMd5ChunkBlocks;
+            for (int i = 0; i < nb; ++i) md5_block(st, stage[i]);
+        }
+        __syncwarp();
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) digest[4 * i + k] = (uint8_t)(st[i] >> (8 * k));
+    }
+}
+
+constexpr int kMd5WarpsPerBlock = 2;
+
+__global__ void __launch_bounds__(32 * kMd5WarpsPerBlock)
+k_md5(const Md5Job *__restrict__ jobs, uint32_t n_jobs, uint8_t *__restrict__ digests) {
+    __shared__ uint32_t stage[kMd5WarpsPerBlock][kMd5ChunkBlocks][16];
+    const uint32_t job = blockIdx.x * kMd5WarpsPerBlock + (threadIdx.x >> 5);
+    if (job >= n_jobs) return;
+    const Md5Job j = jobs[job];
+    uint32_t(*stg)[16] = stage[threadIdx.x >> 5];
+    uint8_t *dg = digests + 16 * (size_t)job;
+    switch (j.hash_bytes) {
+        case 1: md5_run<1>(j, dg, stg); break;
+        case 2: md5_run<2>(j, dg, stg); break;
+        case 3: md5_run<3>(j, dg, stg); break;
+        default: md5_run<4>(j, dg, stg); break;
+    }
+}
+
+cudaError_t launch_md5(const Md5Job *d_jobs, uint32_t n_jobs, uint8_t *d_digests, cudaStream_t st) {
+    if (n_jobs == 0) return cudaSuccess;
+    k_md5<<<(n_jobs + kMd5WarpsPerBlock - 1) / kMd5WarpsPerBlock, 32 * kMd5WarpsPerBlock, 0, st>>>(d_jobs, n_jobs, d_digests);
+    return cudaGetLastError();
+}
+
+}  // namespace zf

@@ -1,0 +1,47 @@
+// kernels.cuh — host-side launchers of the sm_100a kernels (one translation unit each).
+#pragma once
+#include "common.cuh"
+
+namespace zf {
+
+// scan.cu
+cudaError_t scan_init_constants();
+uint32_t scan_tile_count(uint64_t scan_begin, uint64_t len);
+cudaError_t launch_sync_scan(const uint8_t *d_stream, uint64_t scan_begin, uint64_t len, Cand *d_cands, uint32_t cap,
+                             uint32_t *d_total, unsigned long long *d_tile_state, uint32_t *d_ticket, cudaStream_t st);
+cudaError_t launch_frame_link(const uint8_t *d_stream, uint64_t len, const Cand *d_cands, uint32_t n, uint32_t *d_link,
+                              uint32_t window, uint64_t max_frame_bytes, cudaStream_t st);
+cudaError_t launch_crc16_ranges(const uint8_t *d_stream, const uint64_t *d_begin, const uint64_t *d_end, uint32_t n,
+                                uint16_t *d_crc, cudaStream_t st);
+
+// decode.cu
+cudaError_t launch_decode_frames(const uint8_t *d_stream, uint64_t len, const FrameRec *d_frames, uint32_t n_frames,
+                                 void *d_scratch, bool wide_scratch, FrameOut *d_outs, bool write_samples,
+                                 cudaStream_t st);
+
+// epilogue.cu
+struct EpilogueParams {
+    const FrameRec *frames;
+    uint32_t n_frames;
+    uint32_t max_block_size;
+    const void *scratch;
+    bool wide_scratch;
+    void *pcm;
+    uint32_t container_bytes;  // 1, 2, 4
+    uint32_t msb_shift;        // left shift applied to every container value (zflac.zig:287-306)
+    uint32_t *lossy_flag;      // set to 1 if a shifted value no longer shifts back (MD5 must then hash pre-shift data)
+};
+cudaError_t launch_epilogue(const EpilogueParams &p, cudaStream_t st);
+cudaError_t launch_shift_inplace(void *pcm, uint64_t n_samples, uint32_t container_bytes, uint32_t shift, cudaStream_t st);
+
+struct Md5Job {
+    const void *pcm;        // container-typed samples
+    uint64_t n_samples;
+    uint32_t container_bytes;
+    uint32_t hash_bytes;    // bytes of each sample that enter the hash: 1, 2, 3 or 4 (Q4)
+    uint32_t unshift;       // arithmetic right shift that undoes the MSB-align shift before hashing
+    uint32_t pad;
+};
+cudaError_t launch_md5(const Md5Job *d_jobs, uint32_t n_jobs, uint8_t *d_digests, cudaStream_t st);
+
+}  // namespace zf

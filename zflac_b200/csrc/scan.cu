@@ -1,0 +1,405 @@
+// scan.cu — K1 sync_scan and K1b frame_link (sm_100a).
+//
+// K1 restates, as a data-parallel predicate over every byte position, the frame-header
+// grammar the reference walks sequentially (src/zflac.zig:343-374 FrameHeader bitfields
+// :165-173, read_coded_number :203-214, block-size / sample-rate escapes :356-374), plus
+// the CRC-8 the reference reads and ignores (:407-410). Candidates leave the kernel in
+// stream order: per-tile ballot/scan ranks + a decoupled look-back across tiles.
+//
+// K1b computes the CRC-16 (:551, also ignored by the reference) of the bytes between
+// neighbouring candidates. A match proves "candidate k is a frame that ends where candidate j
+// starts" without entropy-decoding it, which is what lets K2 decode every frame in parallel
+// with its output offset already known. A mismatch proves nothing (the reference would
+// still decode the frame, Q1): the host then probes that frame's end with K2 instead.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace zf {
+
+// ------------------------------------------------------------------ CRC helpers
+__device__ __forceinline__ uint32_t crc8_byte(uint32_t crc, uint32_t b) {
+    crc ^= b;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) crc = (crc & 0x80u) ? ((crc << 1) ^ 0x07u) & 0xFFu : (crc << 1) & 0xFFu;
+    return crc;
+}
+
+__constant__ uint32_t c_rate_table[16] = {0, 88200, 176400, 192000, 8000, 16000, 22050, 24000,
+                                          32000, 44100, 48000, 96000, 0, 0, 0, 0};
+
+// Full header check at byte position p. Returns true and fills `c` when the bytes at p are a
+// frame header the reference would accept (grammar) AND the CRC-8 matches.
+__device__ bool parse_header_at(const uint8_t *__restrict__ s, uint64_t p, uint64_t len, Cand &c) {
+    if (p + 6 > len) return false;
+    uint8_t b[16];
+    const int avail = (len - p) < 16 ? (int)(len - p) : 16;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) b[i] = (i < avail) ? s[p + i] : 0;
+    if (b[0] != 0xFF || (b[1] & 0xFE) != 0xF8) return false;
+    const uint32_t bs_code = b[2] >> 4, sr_code = b[2] & 15, ch_code = b[3] >> 4, bd_code = (b[3] >> 1) & 7;
+    if (bs_code == 0 || sr_code == 15 || ch_code > 10 || bd_code == 3) return false;
+    const uint32_t c0 = b[4];
+    const uint32_t ones = __clz((int)((~c0 & 0xFFu) << 24 | 0x00800000u));  // leading ones of c0 (0..8)
+    if (c0 == 0xFF || ones == 1) return false;
+    int n = 4 + (ones == 0 ? 1 : (int)ones);
+    uint32_t block_size;
+    if (bs_code == 6) {
+        block_size = (uint32_t)b[n] + 1;
+        n += 1;
+    } else if (bs_code == 7) {
+        const uint32_t v = ((uint32_t)b[n] << 8) | b[n + 1];
+        if (v == 0xFFFF) return false;
+        block_size = v + 1;
+        n += 2;
+    } else if (bs_code == 1) {
+        block_size = 192;
+    } else if (bs_code <= 5) {
+        block_size = 144u << bs_code;
+    } else {
+        block_size = 1u << bs_code;
+    }
+    uint32_t sr_value = c_rate_table[sr_code];
+    if (sr_code == 12) {
+        sr_value = b[n];
+        n += 1;
+    } else if (sr_code == 13) {
+        sr_value = ((uint32_t)b[n] << 8) | b[n + 1];
+        n += 2;
+    } else if (sr_code == 14) {
+        sr_value = 10u * (((uint32_t)b[n] << 8) | b[n + 1]);
+        n += 2;
+    }
+    if (n + 1 > avail) return false;
+    uint32_t crc = 0;
+    for (int i = 0; i < n; ++i) crc = crc8_byte(crc, b[i]);
+    if (crc != b[n]) return false;
+    c.offset = p;
+    c.block_size = block_size;
+    c.sr_value = sr_value;
+    c.header_len = (uint8_t)(n + 1);
+    c.ch_code = (uint8_t)ch_code;
+    c.bd_code = (uint8_t)bd_code;
+    c.sr_code = (uint8_t)sr_code;
+    c.pad = 0;
+    return true;
+}
+
+// ------------------------------------------------------------------ K1
+// One CTA scans one 16 KB tile: 4 rows of 256 threads x 16 bytes, every global load a
+// coalesced 128-bit vector. Sync codes are found four bytes at a time with SIMD-in-register
+// byte compares; only the (rare) hits run the full header check.
+constexpr int kScanThreads = 256;
+constexpr int kScanRows = 4;
+constexpr int kScanTileBytes = kScanThreads * 16 * kScanRows;
+
+constexpr unsigned long long kFlagAgg = 1ull << 62;
+constexpr unsigned long long kFlagPrefix = 2ull << 62;
+constexpr unsigned long long kValueMask = (1ull << 62) - 1;
+
+__device__ __forceinline__ uint32_t sync_mask4(uint32_t cur, uint32_t nxt) {
+    // byte i of cur == 0xFF and byte i of nxt (the following stream byte) in {0xF8, 0xF9}
+    const uint32_t m = __vcmpeq4(cur, 0xFFFFFFFFu) & __vcmpeq4(nxt & 0xFEFEFEFEu, 0xF8F8F8F8u);
+    return ((m & 0x01010101u) * 0x01020408u) >> 24;  // 4-bit mask, bit i <-> byte i
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t len, uint64_t tile0, uint32_t n_tiles,
+            Cand *__restrict__ out, uint32_t cap, uint32_t *__restrict__ total_out,
+            unsigned long long *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_warp_sum[kScanThreads / 32];
+    __shared__ unsigned long long s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    if (tile >= n_tiles) return;
+    const uint64_t tile_base = tile0 + (uint64_t)tile * kScanTileBytes;
+
+    uint32_t valid[kScanRows];   // per row: 16-bit mask of validated candidates in my 16 bytes
+    uint32_t rank[kScanRows];    // per row: exclusive rank of my first candidate inside the tile
+    uint32_t running = 0;        // candidates in earlier rows of this tile
+
+#pragma unroll
+    for (int r = 0; r < kScanRows; ++r) {
+        const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+        uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0, nb = 0;
+        if (pos + 17 <= len) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(s + pos));
+            w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
+            nb = s[pos + 16];
+        } else if (pos < len) {  // stream tail: bytes past len read as zero
+            uint32_t t[5] = {0, 0, 0, 0, 0};
+            for (int i = 0; i < 17 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+            w0 = t[0]; w1 = t[1]; w2 = t[2]; w3 = t[3]; nb = t[4];
+        }
+        uint32_t raw = sync_mask4(w0, __funnelshift_r(w0, w1, 8)) |
+                       (sync_mask4(w1, __funnelshift_r(w1, w2, 8)) << 4) |
+                       (sync_mask4(w2, __funnelshift_r(w2, w3, 8)) << 8) |
+                       (sync_mask4(w3, __funnelshift_r(w3, nb, 8)) << 12);
+        uint32_t ok = 0;
+        while (raw) {  // rare: ~2^-15 per byte on compressed data
+            const int b = __ffs(raw) - 1;
+            raw &= raw - 1;
+            const uint64_t p = pos + b;
+            Cand c;
+            if (p >= scan_begin && parse_header_at(s, p, len, c)) ok |= 1u << b;
+        }
+        valid[r] = ok;
+        // exclusive scan of popc(ok) over the 256 threads of this row
+        const uint32_t cnt = __popc(ok);
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) s_warp_sum[warp] = incl;
+        __syncthreads();
+        uint32_t warp_off = 0, row_total = 0;
+#pragma unroll
+        for (int w = 0; w < kScanThreads / 32; ++w) {
+            const uint32_t t = s_warp_sum[w];
+            if (w < warp) warp_off += t;
+            row_total += t;
+        }
+        rank[r] = running + warp_off + incl - cnt;
+        running += row_total;
+        __syncthreads();
+    }
+
+    // decoupled look-back: tile t publishes its aggregate, then sums its predecessors'
+    if (tid == 0) {
+        unsigned long long base = 0;
+        volatile unsigned long long *st = tile_state;
+        if (tile > 0) {
+            atomicExch(&tile_state[tile], kFlagAgg | (unsigned long long)running);
+            for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
+                unsigned long long v;
+                do {
+                    v = st[t];
+                } while ((v >> 62) == 0);
+                base += v & kValueMask;
+                if ((v >> 62) == 2) break;
+            }
+        }
+        atomicExch(&tile_state[tile], kFlagPrefix | (base + running));
+        s_base = base;
+        if (tile == n_tiles - 1) *total_out = (uint32_t)min(base + running, (unsigned long long)0xFFFFFFFFull);
+    }
+    __syncthreads();
+    const unsigned long long base = s_base;
+
+#pragma unroll
+    for (int r = 0; r < kScanRows; ++r) {
+        uint32_t ok = valid[r];
+        unsigned long long slot = base + rank[r];
+        const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+        while (ok) {
+            const int b = __ffs(ok) - 1;
+            ok &= ok - 1;
+            Cand c;
+            parse_header_at(s, pos + b, len, c);
+            if (slot < cap) out[slot] = c;
+            ++slot;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ K1b
+// CRC-16 (poly 0x8005, init 0, MSB first) as arithmetic in GF(2)[x]/P: the state after a
+// message M is M(x)*x^16 mod P, so state(A||B) = state(A)*x^(8|B|) + state(B). A warp covers a
+// byte range with coalesced 16-byte groups: lane L takes groups L, L+32, ... (Horner step
+// x^(8*512)), the lanes are then aligned with x^(128*t) and XOR-reduced.
+__constant__ uint16_t c_pow_x8[40];    // x^(8*2^i) mod P
+__constant__ uint16_t c_pow_x128[32];  // x^(128*t) mod P
+__constant__ uint16_t c_x3968;         // x^(8*(512-16)) mod P
+
+__host__ __device__ inline uint32_t gf16_mul(uint32_t a, uint32_t b) {
+    uint32_t r = 0;
+    for (int i = 15; i >= 0; --i) {
+        r = ((r << 1) ^ ((r & 0x8000u) ? 0x8005u : 0u)) & 0xFFFFu;
+        if ((b >> i) & 1u) r ^= a;
+    }
+    return r;
+}
+
+struct CrcTables {
+    uint16_t byte[256];   // state update for one byte
+    uint16_t mul_hi[256]; // (v<<8) * x^3968
+    uint16_t mul_lo[256]; // v * x^3968
+};
+
+__device__ void build_crc_tables(CrcTables &t) {
+    for (int v = threadIdx.x; v < 256; v += blockDim.x) {
+        uint32_t crc = (uint32_t)v << 8;
+        for (int i = 0; i < 8; ++i) crc = (crc & 0x8000u) ? ((crc << 1) ^ 0x8005u) & 0xFFFFu : (crc << 1) & 0xFFFFu;
+        t.byte[v] = (uint16_t)crc;
+        t.mul_hi[v] = (uint16_t)gf16_mul((uint32_t)v << 8, c_x3968);
+        t.mul_lo[v] = (uint16_t)gf16_mul((uint32_t)v, c_x3968);
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t crc16_absorb_word(const CrcTables &t, uint32_t st, uint32_t w_le) {
+    // w_le holds 4 stream bytes, first byte in bits 0..7
+    st = ((st << 8) & 0xFFFFu) ^ t.byte[(st >> 8) ^ (w_le & 0xFFu)];
+    st = ((st << 8) & 0xFFFFu) ^ t.byte[(st >> 8) ^ ((w_le >> 8) & 0xFFu)];
+    st = ((st << 8) & 0xFFFFu) ^ t.byte[(st >> 8) ^ ((w_le >> 16) & 0xFFu)];
+    st = ((st << 8) & 0xFFFFu) ^ t.byte[(st >> 8) ^ (w_le >> 24)];
+    return st;
+}
+
+__device__ __forceinline__ uint32_t gf16_shift_bytes(uint32_t st, uint64_t nbytes) {
+    for (int i = 0; nbytes; ++i, nbytes >>= 1)
+        if (nbytes & 1) st = gf16_mul(st, c_pow_x8[i]);
+    return st;
+}
+
+// CRC-16 state of s[a, e), computed by a whole warp; result valid in every lane.
+__device__ uint32_t warp_crc16(const CrcTables &t, const uint8_t *__restrict__ s, uint64_t a, uint64_t e) {
+    const int lane = threadIdx.x & 31;
+    if (e <= a) return 0;
+    const uint64_t a0 = a & ~15ull, e0 = e & ~15ull;
+    uint32_t st = 0;
+    uint64_t tail_from = a;
+    if (e0 > a0) {
+        const uint64_t m = (e0 - a0) >> 4;  // full 16-byte groups in [a0, e0)
+        uint64_t last = 0;
+        bool any = false;
+        for (uint64_t g = lane; g < m; g += 32) {
+            uint4 v = __ldg(reinterpret_cast<const uint4 *>(s + a0 + (g << 4)));
+            if (g == 0 && a > a0) {  // leading bytes before `a` count as zeros (init 0: no effect)
+                const uint32_t skip = (uint32_t)(a - a0);
+                uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int lo = i * 4;
+                    if ((int)skip >= lo + 4) w[i] = 0;
+                    else if ((int)skip > lo) w[i] &= 0xFFFFFFFFu << (8 * (skip - lo));
+                }
+                v = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            st = t.mul_hi[st >> 8] ^ t.mul_lo[st & 0xFFu];  // * x^(8*496)
+            st = crc16_absorb_word(t, st, v.x);             // * x^128 + group
+            st = crc16_absorb_word(t, st, v.y);
+            st = crc16_absorb_word(t, st, v.z);
+            st = crc16_absorb_word(t, st, v.w);
+            last = g;
+            any = true;
+        }
+        if (any) st = gf16_mul(st, c_pow_x128[(m - 1 - last) & 31]);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) st ^= __shfl_xor_sync(0xFFFFFFFFu, st, d);
+        tail_from = e0;
+    }
+    // tail (< 16 bytes, or a range that never reaches a 16-byte boundary): lane 0, bytewise
+    if (lane == 0) {
+        for (uint64_t p = tail_from; p < e; ++p) st = ((st << 8) & 0xFFFFu) ^ t.byte[(st >> 8) ^ s[p]];
+    }
+    return __shfl_sync(0xFFFFFFFFu, st, 0);
+}
+
+constexpr int kLinkThreads = 256;
+
+__global__ void __launch_bounds__(kLinkThreads)
+k_frame_link(const uint8_t *__restrict__ s, uint64_t len, const Cand *__restrict__ cands, uint32_t n,
+             uint32_t *__restrict__ link, uint32_t window, uint64_t max_frame_bytes) {
+    __shared__ CrcTables tab;
+    build_crc_tables(tab);
+    const uint32_t k = blockIdx.x * (kLinkThreads / 32) + (threadIdx.x >> 5);
+    if (k >= n) return;
+    const uint64_t a = cands[k].offset;
+    uint32_t acc = 0, found = kNoLink;
+    uint64_t done_to = a;
+    for (uint32_t t = 1; t <= window; ++t) {
+        const uint32_t j = k + t;
+        if (j > n) break;
+        const uint64_t b = (j < n) ? cands[j].offset : len;  // j == n: the end of the stream
+        if (b - a > max_frame_bytes) break;
+        if (b < a + 8) continue;  // shorter than any frame (header 6 + 1 + CRC-16... rounded)
+        const uint64_t upto = b - 2;
+        const uint32_t seg = warp_crc16(tab, s, done_to, upto);
+        acc = gf16_shift_bytes(acc, upto - done_to) ^ seg;
+        done_to = upto;
+        const uint32_t stored = ((uint32_t)s[b - 2] << 8) | s[b - 1];
+        if (acc == stored) {
+            found = j;
+            break;
+        }
+    }
+    if ((threadIdx.x & 31) == 0) link[k] = found;
+}
+
+// CRC-16 of explicit [begin, end) ranges (diagnostic check of decoded frames).
+__global__ void __launch_bounds__(kLinkThreads)
+k_crc16_ranges(const uint8_t *__restrict__ s, const uint64_t *__restrict__ begin, const uint64_t *__restrict__ end,
+               uint32_t n, uint16_t *__restrict__ crc_out) {
+    __shared__ CrcTables tab;
+    build_crc_tables(tab);
+    const uint32_t k = blockIdx.x * (kLinkThreads / 32) + (threadIdx.x >> 5);
+    if (k >= n) return;
+    const uint32_t st = warp_crc16(tab, s, begin[k], end[k]);
+    if ((threadIdx.x & 31) == 0) crc_out[k] = (uint16_t)st;
+}
+
+// ------------------------------------------------------------------ host launchers
+static uint32_t host_pow_x(uint64_t bits) {  // x^bits mod P
+    uint32_t r = 1, base = 2;  // base = x
+    while (bits) {
+        if (bits & 1) r = gf16_mul(r, base);
+        base = gf16_mul(base, base);
+        bits >>= 1;
+    }
+    return r;
+}
+
+cudaError_t scan_init_constants() {
+    uint16_t p8[40], p128[32];
+    for (int i = 0; i < 40; ++i) p8[i] = (uint16_t)host_pow_x(8ull << i);
+    for (int t = 0; t < 32; ++t) p128[t] = (uint16_t)host_pow_x(128ull * t);
+    const uint16_t x3968 = (uint16_t)host_pow_x(3968);
+    cudaError_t e;
+    if ((e = cudaMemcpyToSymbol(c_pow_x8, p8, sizeof(p8))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_pow_x128, p128, sizeof(p128))) != cudaSuccess) return e;
+    return cudaMemcpyToSymbol(c_x3968, &x3968, sizeof(x3968));
+}
+
+uint32_t scan_tile_count(uint64_t scan_begin, uint64_t len) {
+    if (len <= scan_begin) return 0;
+    const uint64_t tile0 = scan_begin & ~15ull;
+    return (uint32_t)((len - tile0 + kScanTileBytes - 1) / kScanTileBytes);
+}
+
+cudaError_t launch_sync_scan(const uint8_t *d_stream, uint64_t scan_begin, uint64_t len, Cand *d_cands, uint32_t cap,
+                             uint32_t *d_total, unsigned long long *d_tile_state, uint32_t *d_ticket,
+                             cudaStream_t st) {
+    const uint32_t n_tiles = scan_tile_count(scan_begin, len);
+    cudaError_t e;
+    if ((e = cudaMemsetAsync(d_total, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
+    if (n_tiles == 0) return cudaSuccess;
+    if ((e = cudaMemsetAsync(d_tile_state, 0, sizeof(unsigned long long) * n_tiles, st)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(d_ticket, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
+    k_sync_scan<<<n_tiles, kScanThreads, 0, st>>>(d_stream, scan_begin, len, scan_begin & ~15ull, n_tiles, d_cands, cap,
+                                                  d_total, d_tile_state, d_ticket);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_frame_link(const uint8_t *d_stream, uint64_t len, const Cand *d_cands, uint32_t n, uint32_t *d_link,
+                              uint32_t window, uint64_t max_frame_bytes, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const uint32_t per_block = kLinkThreads / 32;
+    k_frame_link<<<(n + per_block - 1) / per_block, kLinkThreads, 0, st>>>(d_stream, len, d_cands, n, d_link, window,
+                                                                          max_frame_bytes);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_crc16_ranges(const uint8_t *d_stream, const uint64_t *d_begin, const uint64_t *d_end, uint32_t n,
+                                uint16_t *d_crc, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const uint32_t per_block = kLinkThreads / 32;
+    k_crc16_ranges<<<(n + per_block - 1) / per_block, kLinkThreads, 0, st>>>(d_stream, d_begin, d_end, n, d_crc);
+    return cudaGetLastError();
+}
+
+}  // namespace zf
