@@ -105,6 +105,7 @@ int zflacb200_device_count(void);
 void zflacb200_shutdown(void);
 const char *zflacb200_status_name(int status); /* the Zig error name, e.g. "InvalidFrameHeader" */
 const char *zflacb200_last_error(void);        /* thread-local detail for CUDA_ERROR / INVALID_ARGUMENT */
+uint64_t zflacb200_kernel_launches(void);      /* kernels this library has launched since load (bench: gpu_launches) */
 
 /* Replaces the body of decode() (src/zflac.zig:217-310): signature + metadata walk,
  * frame index, subframe decode, decorrelation, MD5 gate, MSB-align shift.

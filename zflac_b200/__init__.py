@@ -118,11 +118,12 @@ def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bo
     return DecodedFLAC(info.channels, info.sample_rate, info.bits_per_sample, out, _info_dict(info))
 
 
-def decode_into(data, dst: np.ndarray, *, device: int = -1, verify_md5: bool = True) -> dict:
-    """One-call variant (zflacb200_decode): decodes into a caller-owned buffer."""
+def decode_into(data, dst: np.ndarray, *, device: int = -1, verify_md5: bool = True, stream: int | None = None) -> dict:
+    """One-call variant (zflacb200_decode): decodes into a caller-owned buffer (pinned host memory
+    makes both copies run at full PCIe speed)."""
     lib = _native.load()
     arr = _as_u8(data)
-    opt = _options(0 if verify_md5 else SKIP_MD5, device)
+    opt = _options(0 if verify_md5 else SKIP_MD5, device, stream)
     info = _native.Info()
     st = lib.zflacb200_decode(arr.ctypes.data, arr.size, C.byref(opt), dst.ctypes.data, dst.nbytes, C.byref(info))
     if st != 0:

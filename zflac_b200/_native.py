@@ -16,7 +16,7 @@ NO_CRC_ACCEL = 0x8
 
 EXPORTS = [
     "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown",
-    "zflacb200_status_name", "zflacb200_last_error", "zflacb200_open", "zflacb200_read",
+    "zflacb200_status_name", "zflacb200_last_error", "zflacb200_kernel_launches", "zflacb200_open", "zflacb200_read",
     "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_open_batch", "zflacb200_frames",
 ]
 
@@ -62,6 +62,7 @@ def load():
     lib.zflacb200_status_name.argtypes = [C.c_int]
     lib.zflacb200_status_name.restype = C.c_char_p
     lib.zflacb200_last_error.restype = C.c_char_p
+    lib.zflacb200_kernel_launches.restype = C.c_uint64
     lib.zflacb200_open.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.POINTER(C.c_void_p), C.POINTER(Info)]
     lib.zflacb200_open.restype = C.c_int
     lib.zflacb200_read.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]

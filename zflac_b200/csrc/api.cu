@@ -22,6 +22,10 @@
 
 using namespace zf;
 
+namespace zf {
+std::atomic<unsigned long long> g_kernel_launches{0};
+}
+
 namespace {
 
 thread_local std::string g_last_error;
@@ -717,6 +721,8 @@ const char *zflacb200_status_name(int status) {
 }
 
 const char *zflacb200_last_error(void) { return g_last_error.c_str(); }
+
+uint64_t zflacb200_kernel_launches(void) { return g_kernel_launches.load(); }
 
 int zflacb200_open(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info) {
     std::lock_guard<std::mutex> lock(g_mutex);

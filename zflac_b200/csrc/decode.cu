@@ -506,6 +506,7 @@ cudaError_t launch_decode_frames(const uint8_t *d_stream, uint64_t len, const Fr
                                  cudaStream_t st) {
     if (n_frames == 0) return cudaSuccess;
     const uint32_t blocks = (n_frames + kDecodeThreads - 1) / kDecodeThreads;
+    ZF_COUNT_LAUNCH();
     if (wide_scratch)
         k_decode_frames<int64_t><<<blocks, kDecodeThreads, 0, st>>>(d_stream, len, d_frames, n_frames, (int64_t *)d_scratch,
                                                                     d_outs, write_samples ? 1 : 0);

@@ -86,6 +86,7 @@ cudaError_t launch_epilogue(const EpilogueParams &p, cudaStream_t st) {
     if (gy > 64) gy = 64;
     if (gy == 0) gy = 1;
     dim3 grid(p.n_frames, gy);
+    ZF_COUNT_LAUNCH();
 #define ZF_EPI(ST, CT) \
     k_epilogue<ST, CT><<<grid, kEpiThreads, 0, st>>>(p.frames, (const ST *)p.scratch, (CT *)p.pcm, p.msb_shift, p.lossy_flag)
     if (p.wide_scratch) {
@@ -106,6 +107,7 @@ cudaError_t launch_shift_inplace(void *pcm, uint64_t n_samples, uint32_t contain
     const int threads = 256;
     uint64_t want = (n_samples + threads - 1) / threads;
     const uint32_t blocks = (uint32_t)(want < 148ull * 16 ? want : 148ull * 16);
+    ZF_COUNT_LAUNCH();
     if (container_bytes == 2) k_shift_inplace<int16_t><<<blocks, threads, 0, st>>>((int16_t *)pcm, n_samples, shift);
     else if (container_bytes == 4) k_shift_inplace<int32_t><<<blocks, threads, 0, st>>>((int32_t *)pcm, n_samples, shift);
     else k_shift_inplace<int8_t><<<blocks, threads, 0, st>>>((int8_t *)pcm, n_samples, shift);
@@ -254,6 +256,7 @@ k_md5(const Md5Job *__restrict__ jobs, uint32_t n_jobs, uint8_t *__restrict__ di
 
 cudaError_t launch_md5(const Md5Job *d_jobs, uint32_t n_jobs, uint8_t *d_digests, cudaStream_t st) {
     if (n_jobs == 0) return cudaSuccess;
+    ZF_COUNT_LAUNCH();
     k_md5<<<(n_jobs + kMd5WarpsPerBlock - 1) / kMd5WarpsPerBlock, 32 * kMd5WarpsPerBlock, 0, st>>>(d_jobs, n_jobs, d_digests);
     return cudaGetLastError();
 }

@@ -1,8 +1,14 @@
 // kernels.cuh — host-side launchers of the sm_100a kernels (one translation unit each).
 #pragma once
+#include <atomic>
+
 #include "common.cuh"
 
 namespace zf {
+
+// every kernel launch of the library is counted here (zflacb200_kernel_launches)
+extern std::atomic<unsigned long long> g_kernel_launches;
+#define ZF_COUNT_LAUNCH() (::zf::g_kernel_launches.fetch_add(1, std::memory_order_relaxed))
 
 // scan.cu
 cudaError_t scan_init_constants();

@@ -380,6 +380,7 @@ cudaError_t launch_sync_scan(const uint8_t *d_stream, uint64_t scan_begin, uint6
     if (n_tiles == 0) return cudaSuccess;
     if ((e = cudaMemsetAsync(d_tile_state, 0, sizeof(unsigned long long) * n_tiles, st)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(d_ticket, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
+    ZF_COUNT_LAUNCH();
     k_sync_scan<<<n_tiles, kScanThreads, 0, st>>>(d_stream, scan_begin, len, scan_begin & ~15ull, n_tiles, d_cands, cap,
                                                   d_total, d_tile_state, d_ticket);
     return cudaGetLastError();
@@ -389,6 +390,7 @@ cudaError_t launch_frame_link(const uint8_t *d_stream, uint64_t len, const Cand 
                               uint32_t window, uint64_t max_frame_bytes, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const uint32_t per_block = kLinkThreads / 32;
+    ZF_COUNT_LAUNCH();
     k_frame_link<<<(n + per_block - 1) / per_block, kLinkThreads, 0, st>>>(d_stream, len, d_cands, n, d_link, window,
                                                                           max_frame_bytes);
     return cudaGetLastError();
@@ -398,6 +400,7 @@ cudaError_t launch_crc16_ranges(const uint8_t *d_stream, const uint64_t *d_begin
                                 uint16_t *d_crc, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const uint32_t per_block = kLinkThreads / 32;
+    ZF_COUNT_LAUNCH();
     k_crc16_ranges<<<(n + per_block - 1) / per_block, kLinkThreads, 0, st>>>(d_stream, d_begin, d_end, n, d_crc);
     return cudaGetLastError();
 }
