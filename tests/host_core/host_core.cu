@@ -1,0 +1,60 @@
+// host_core.cu — TEST INFRASTRUCTURE. Instantiates the K2 per-frame decoder
+// (zflac_b200/csrc/decode_core.cuh) on the HOST with a plain-memory word source so that the
+// bit-level logic (funnel reader, Rice fast/slow paths, partition walk, predictor windows) can be
+// unit-tested against the oracle without a GPU. Built into tests/host_core/_build/ only; it is
+// never linked into libzflacb200.so and the product package never loads it.
+#include <cstring>
+
+#include "../../zflac_b200/csrc/decode_core.cuh"
+
+namespace {
+
+struct HostSrc {
+    const uint8_t *g;
+    uint64_t avail;
+    // poison tracking: the device ring only guarantees kFastWords resident words after top_up();
+    // mimic that so an unchecked read beyond the guarantee is caught here, not on the GPU
+    uint32_t guaranteed;
+    int violations;
+    __host__ __device__ uint32_t raw(uint32_t w) const {
+        uint32_t v = 0;
+        for (int i = 0; i < 4; ++i) {
+            const uint64_t off = (uint64_t)w * 4 + i;
+            v = (v << 8) | (off < avail ? g[off] : 0u);
+        }
+        return __builtin_bswap32(v);
+    }
+    __host__ __device__ uint32_t word(uint32_t w) {
+        if (w >= guaranteed) ++violations;
+        return raw(w);
+    }
+    __host__ __device__ uint32_t word_checked(uint32_t w) { return raw(w); }
+    __host__ __device__ void top_up(uint32_t cur) { guaranteed = cur + zf::kFastWords; }
+    // raw order here = byte-reversed, like the little-endian shared-memory word of the device ring
+    static __host__ __device__ uint32_t fix(uint32_t raw) { return __builtin_bswap32(raw); }
+};
+
+}  // namespace
+
+extern "C" {
+
+// Decodes one frame on the host. scratch: int32 (wide == 0) or int64 planes. Returns the number of
+// unchecked-read violations (must be 0).
+int zf_host_decode_frame(const uint8_t *stream, const zf::FrameRec *fr, void *scratch, int wide, int write_samples,
+                         zf::FrameOut *out) {
+    const uint64_t start = fr->offset + fr->header_len;
+    const uint64_t origin = start & ~3ull;
+    const uint64_t bytes = fr->stream_end > origin ? fr->stream_end - origin : 0;
+    zf::BitReader<HostSrc> br;
+    br.src.g = stream + origin;
+    br.src.avail = bytes;
+    br.src.guaranteed = 0;
+    br.src.violations = 0;
+    br.init((uint32_t)(start & 3));
+    if (wide) zf::decode_frame<int64_t>(br, *fr, (int64_t *)scratch, bytes * 8, write_samples != 0, origin, *out);
+    else zf::decode_frame<int32_t>(br, *fr, (int32_t *)scratch, bytes * 8, write_samples != 0, origin, *out);
+    return br.src.violations;
+}
+
+int zf_host_framerec_size(void) { return (int)sizeof(zf::FrameRec); }
+}

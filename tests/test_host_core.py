@@ -1,0 +1,109 @@
+"""CPU unit test of the K2 per-frame decoder logic (zflac_b200/csrc/decode_core.cuh).
+
+tests/host_core/host_core.cu instantiates the SAME header the CUDA kernel uses with a host word source;
+here every frame of every corpus file / synthetic stream is decoded through it and compared with the
+oracle: frame end offsets, and the PCM after a numpy restatement of K3 (decorrelation, MSB-align shift,
+interleave). This pins the bit reader, Rice fast/slow paths, partition walk and predictor windows on CPU;
+the `-m gpu` tests pin the device word ring on top. Test infrastructure only — nothing in zflac_b200/
+loads this library.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, corpus_bytes, corpus_entries, corpus_ids
+from oracle import oracle
+import synth_cases
+
+HERE = os.path.join(ROOT, "tests", "host_core")
+LIB = os.path.join(HERE, "_build", "libzf_host_core.so")
+SRC = os.path.join(HERE, "host_core.cu")
+DEPS = [SRC, os.path.join(ROOT, "zflac_b200", "csrc", "decode_core.cuh"), os.path.join(ROOT, "zflac_b200", "csrc", "common.cuh")]
+
+FRAME_REC = np.dtype([("offset", "<u8"), ("stream_end", "<u8"), ("sample_base", "<u8"), ("scratch_base", "<u8"),
+                      ("block_size", "<u4"), ("scratch_pitch", "<u4"), ("header_len", "u1"), ("ch_code", "u1"),
+                      ("channels", "u1"), ("bps", "u1"), ("stream_id", "<u4")])
+FRAME_OUT = np.dtype([("end_offset", "<u8"), ("status", "<u4"), ("stored_crc16", "<u4")])
+
+
+@pytest.fixture(scope="module")
+def core():
+    stale = (not os.path.exists(LIB)) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in DEPS)
+    if stale:
+        os.makedirs(os.path.dirname(LIB), exist_ok=True)
+        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+        subprocess.run([nvcc, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC",
+                        "--expt-relaxed-constexpr", "-o", LIB, SRC], check=True, capture_output=True)
+    lib = C.CDLL(LIB)
+    lib.zf_host_decode_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.zf_host_decode_frame.restype = C.c_int
+    assert lib.zf_host_framerec_size() == FRAME_REC.itemsize
+    return lib
+
+
+def host_decode(lib, data: bytes, ref):
+    """Decode all frames of the oracle's frame trace with the host core; return interleaved PCM like the reference's."""
+    arr = np.frombuffer(data, dtype=np.uint8)
+    ch, bps = ref.channels, ref.bits_per_sample
+    wide = bps == 32
+    cb = ref.container_bytes
+    n_total = int(ref.samples.size)
+    pcm = np.zeros(n_total, dtype=np.int64)
+    depth_si = bps  # corpus/synth: STREAMINFO depth == first-frame depth whenever decode succeeds with a valid MD5
+    for fr in ref.frames:
+        bs = int(fr["block_size"])
+        pitch = (bs + 7) // 8 * 8
+        rec = np.zeros(1, dtype=FRAME_REC)
+        rec["offset"], rec["stream_end"] = fr["offset"], len(data)
+        rec["block_size"], rec["scratch_pitch"] = bs, pitch
+        rec["header_len"], rec["ch_code"], rec["channels"], rec["bps"] = fr["header_len"], fr["channel_code"], ch, bps
+        scratch = np.zeros(pitch * ch, dtype=np.int64 if wide else np.int32)
+        out = np.zeros(1, dtype=FRAME_OUT)
+        viol = lib.zf_host_decode_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, int(wide), 1, out.ctypes.data)
+        assert viol == 0, "unchecked word read beyond the top_up guarantee"
+        assert int(out["status"][0]) == 0, (int(fr["offset"]), int(out["status"][0]))
+        assert int(out["end_offset"][0]) == int(fr["end_offset"]), int(fr["offset"])
+        planes = scratch.reshape(ch, pitch)[:, :bs].astype(np.int64)
+        code = int(fr["channel_code"])
+        if code == 8:
+            planes[1] = planes[0] - planes[1]
+        elif code == 9:
+            planes[0] = planes[0] + planes[1]
+        elif code == 10:
+            mid = (planes[0] << 1) + (planes[1] & 1)
+            side = planes[1].copy()
+            planes[0] = (mid + side) >> 1
+            planes[1] = (mid - side) >> 1
+        base = int(fr["sample_offset"])
+        pcm[base:base + bs * ch] = planes.T.reshape(-1)
+    shift = 0
+    if 9 <= depth_si <= 15:
+        shift = 16 - depth_si
+    elif 17 <= depth_si <= 31:
+        shift = 32 - depth_si
+    dt = {1: np.int8, 2: np.int16, 4: np.int32}[cb]
+    return (pcm << shift).astype(dt)
+
+
+@pytest.mark.parametrize("entry", [e for e in corpus_entries() if not e["expect_error"]],
+                         ids=[i for i, e in zip(corpus_ids(), corpus_entries()) if not e["expect_error"]])
+def test_host_core_corpus(core, entry):
+    data = corpus_bytes(entry)
+    ref = oracle.decode(data, trace_frames=True)
+    if ref.error != "OK":
+        pytest.skip(f"oracle: {ref.error}")
+    got = host_decode(core, data, ref)
+    assert np.array_equal(got, ref.samples)
+
+
+@pytest.mark.parametrize("name", sorted(synth_cases.CASES))
+def test_host_core_synth(core, name):
+    s = synth_cases.make(name)
+    data = s.flac.tobytes()
+    ref = oracle.decode(data, trace_frames=True)
+    assert ref.error == "OK"
+    got = host_decode(core, data, ref)
+    assert np.array_equal(got, ref.samples)

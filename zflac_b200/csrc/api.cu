@@ -232,7 +232,7 @@ struct Pipeline {
 
     int probe(const FrameRec &rec, FrameOut &out) {
         CU_CHECK(cudaMemcpyAsync(d_probe_rec, &rec, sizeof(rec), cudaMemcpyHostToDevice, st));
-        CU_CHECK(launch_decode_frames(d_stream, len, d_probe_rec, 1, nullptr, wide, d_probe_out, false, st));
+        CU_CHECK(launch_decode_frames(d_stream, d_probe_rec, 1, nullptr, wide, d_probe_out, false, st));
         CU_CHECK(cudaMemcpyAsync(&out, d_probe_out, sizeof(out), cudaMemcpyDeviceToHost, st));
         CU_CHECK(cudaStreamSynchronize(st));
         return ZFLACB200_OK;
@@ -306,6 +306,7 @@ struct Pipeline {
             }
             ChainFrame cf;
             cf.rec.offset = pos;
+            cf.rec.stream_end = len;
             cf.rec.sample_base = off;
             cf.rec.scratch_base = ch.scratch_elems;
             cf.rec.block_size = h.block_size;
@@ -523,7 +524,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
         if (nf) {
             CU_CHECK(cudaMemcpyAsync(b_frames.p, recs.data(), sizeof(FrameRec) * nf, cudaMemcpyHostToDevice, st));
             CU_CHECK(cudaEventRecord(ev.e[4], st));
-            CU_CHECK(launch_decode_frames(pl.d_stream, len, (const FrameRec *)b_frames.p, nf, b_scratch.p, pl.wide,
+            CU_CHECK(launch_decode_frames(pl.d_stream, (const FrameRec *)b_frames.p, nf, b_scratch.p, pl.wide,
                                           (FrameOut *)b_outs.p, write, st));
             CU_CHECK(cudaEventRecord(ev.e[5], st));
             CU_CHECK(cudaMemcpyAsync(outs.data(), b_outs.p, sizeof(FrameOut) * nf, cudaMemcpyDeviceToHost, st));

@@ -42,12 +42,14 @@ struct Cand {
 };
 static_assert(sizeof(Cand) == 24, "Cand layout");
 
-// K2 input: one frame of the chain.
+// K2 input: one frame of the chain. Offsets are absolute in the device buffer that holds the
+// stream (batch mode: the packed buffer of all streams), so one launch can mix streams.
 struct FrameRec {
     uint64_t offset;        // byte offset of the sync code
+    uint64_t stream_end;    // end of the stream the frame belongs to (the reader's EndOfStream bound)
     uint64_t sample_base;   // interleaved-sample offset of the frame in the PCM buffer
     uint64_t scratch_base;  // element offset of the frame in the planar scratch
-    uint32_t block_size;
+    uint32_t block_size;    // 0 = slot not in use (dropped candidate): K2/K3 skip it
     uint32_t scratch_pitch; // elements per channel plane (block_size rounded up to 8)
     uint8_t header_len;
     uint8_t ch_code;
@@ -55,7 +57,7 @@ struct FrameRec {
     uint8_t bps;            // bits per sample latched from the first frame (zflac.zig:381-384)
     uint32_t stream_id;     // batch mode: which stream the frame belongs to
 };
-static_assert(sizeof(FrameRec) == 40, "FrameRec layout");
+static_assert(sizeof(FrameRec) == 48, "FrameRec layout");
 
 // K2 output.
 struct FrameOut {

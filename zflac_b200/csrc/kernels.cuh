@@ -21,9 +21,8 @@ cudaError_t launch_crc16_ranges(const uint8_t *d_stream, const uint64_t *d_begin
                                 uint16_t *d_crc, cudaStream_t st);
 
 // decode.cu
-cudaError_t launch_decode_frames(const uint8_t *d_stream, uint64_t len, const FrameRec *d_frames, uint32_t n_frames,
-                                 void *d_scratch, bool wide_scratch, FrameOut *d_outs, bool write_samples,
-                                 cudaStream_t st);
+cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, void *d_scratch,
+                                 bool wide_scratch, FrameOut *d_outs, bool write_samples, cudaStream_t st);
 
 // epilogue.cu
 struct EpilogueParams {
