@@ -3,7 +3,7 @@
 //   * on the device, fed by a per-lane shared-memory word ring that cp.async keeps full
 //     (RingSrc in decode.cu), and
 //   * on the host inside tests/host_core/ (HostSrc), where the bit-level logic is unit-tested
-//     against the oracle without a GPU. libzflacb200.so never instantiates the host source:
+//     against the CPU restatement without a GPU. libzflacb200.so never instantiates the host source:
 //     the product has no CPU decode path.
 //
 // Restates, per frame, the reference's subframe loop (src/zflac.zig:425-544): subframe header

@@ -16,9 +16,7 @@
 
 namespace zf {
 
-constexpr int kEpiThreads = 256;
-
-template <typename ST> __device__ __forceinline__ int64_t ld_scratch(const ST *p) { return (int64_t)*p; }
+constexpr int kEpiThreads = 128;
 
 // Decorrelate one stereo pair (values are exact integers; int64 covers the 33-bit side channel).
 __device__ __forceinline__ void decorrelate(uint32_t ch_code, int64_t &a, int64_t &b) {
@@ -42,33 +40,85 @@ template <typename CT> __device__ __forceinline__ CT narrow_shift(int64_t v, uin
     return sh;
 }
 
+// 4 consecutive samples of one channel plane starting at an index that is a multiple of 4 (planes
+// start at multiples of 8 elements, so the vector loads are aligned).
+__device__ __forceinline__ void ld_plane4(const int32_t *p, int64_t (&v)[4]) {
+    const int4 q = __ldg(reinterpret_cast<const int4 *>(p));
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+}
+__device__ __forceinline__ void ld_plane4(const int64_t *p, int64_t (&v)[4]) {
+    const longlong2 a = __ldg(reinterpret_cast<const longlong2 *>(p));
+    const longlong2 b = __ldg(reinterpret_cast<const longlong2 *>(p + 2));
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+
+// One thread = 4 consecutive time steps x all C channels of one frame: C coalesced 128-bit plane
+// loads in, 4*C contiguous container values out (128-bit stores when the PCM address allows).
+template <typename ST, typename CT, int C>
+__device__ __forceinline__ void epilogue_frame(const FrameRec &fr, const ST *__restrict__ scratch, CT *__restrict__ pcm,
+                                               uint32_t shift, uint32_t &lossy) {
+    using UT = typename std::conditional<sizeof(CT) == 1, uint8_t, typename std::conditional<sizeof(CT) == 2, uint16_t, uint32_t>::type>::type;
+    constexpr int kWords = 4 * C * (int)sizeof(CT) / 4;  // 32-bit words written per thread
+    const uint32_t bs = fr.block_size;
+    const ST *src = scratch + fr.scratch_base;
+    CT *dst = pcm + fr.sample_base;
+    for (uint32_t t = 4 * (blockIdx.y * kEpiThreads + threadIdx.x); t < bs; t += 4 * gridDim.y * kEpiThreads) {
+        int64_t v[C][4];
+#pragma unroll
+        for (int c = 0; c < C; ++c) ld_plane4(src + (size_t)c * fr.scratch_pitch + t, v[c]);  // pitch is padded to 8: in bounds
+        CT o[4 * C];
+        uint32_t ignored = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (C == 2) decorrelate(fr.ch_code, v[0][k], v[C - 1][k]);
+#pragma unroll
+            for (int c = 0; c < C; ++c) o[k * C + c] = narrow_shift<CT>(v[c][k], shift, t + k < bs ? lossy : ignored);  // plane padding is garbage
+        }
+        CT *out = dst + (size_t)t * C;
+        const uint32_t valid = bs - t < 4 ? bs - t : 4;
+        if (valid == 4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+            uint32_t w[kWords];
+#pragma unroll
+            for (int i = 0; i < kWords; ++i) {
+                if (sizeof(CT) == 4) w[i] = (uint32_t)o[i];
+                else if (sizeof(CT) == 2) w[i] = (uint32_t)(UT)o[2 * i] | ((uint32_t)(UT)o[2 * i + 1] << 16);
+                else w[i] = (uint32_t)(UT)o[4 * i] | ((uint32_t)(UT)o[4 * i + 1] << 8) | ((uint32_t)(UT)o[4 * i + 2] << 16) | ((uint32_t)(UT)o[4 * i + 3] << 24);
+            }
+            if (kWords % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+#pragma unroll
+                for (int i = 0; i < kWords / 4; ++i)
+                    reinterpret_cast<uint4 *>(out)[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+            } else if (kWords % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0) {
+#pragma unroll
+                for (int i = 0; i < kWords / 2; ++i) reinterpret_cast<uint2 *>(out)[i] = make_uint2(w[2 * i], w[2 * i + 1]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < kWords; ++i) reinterpret_cast<uint32_t *>(out)[i] = w[i];
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4 * C; ++i)
+                if (i < (int)valid * C) out[i] = o[i];
+        }
+    }
+}
+
 template <typename ST, typename CT>
 __global__ void __launch_bounds__(kEpiThreads)
 k_epilogue(const FrameRec *__restrict__ frames, const ST *__restrict__ scratch, CT *__restrict__ pcm, uint32_t shift,
            uint32_t *__restrict__ lossy_flag) {
     const FrameRec fr = frames[blockIdx.x];
-    const uint32_t bs = fr.block_size, C = fr.channels;
-    const ST *src = scratch + fr.scratch_base;
-    CT *dst = pcm + fr.sample_base;
+    if (fr.block_size == 0) return;  // dropped candidate slot
     uint32_t lossy = 0;
-    for (uint32_t t = blockIdx.y * kEpiThreads + threadIdx.x; t < bs; t += gridDim.y * kEpiThreads) {
-        if (C == 2) {
-            int64_t a = ld_scratch(src + t), b = ld_scratch(src + fr.scratch_pitch + t);
-            decorrelate(fr.ch_code, a, b);
-            const CT ca = narrow_shift<CT>(a, shift, lossy), cb = narrow_shift<CT>(b, shift, lossy);
-            if (sizeof(CT) == 2) {
-                *reinterpret_cast<uint32_t *>(dst + 2 * (size_t)t) = (uint32_t)(uint16_t)ca | ((uint32_t)(uint16_t)cb << 16);
-            } else if (sizeof(CT) == 4) {
-                *reinterpret_cast<uint2 *>(dst + 2 * (size_t)t) = make_uint2((uint32_t)ca, (uint32_t)cb);
-            } else {
-                *reinterpret_cast<uint16_t *>(dst + 2 * (size_t)t) = (uint16_t)((uint8_t)ca | ((uint16_t)(uint8_t)cb << 8));
-            }
-        } else {
-            for (uint32_t c = 0; c < C; ++c) {
-                const int64_t v = ld_scratch(src + (size_t)c * fr.scratch_pitch + t);
-                dst[(size_t)t * C + c] = narrow_shift<CT>(v, shift, lossy);
-            }
-        }
+    switch (fr.channels) {
+        case 1: epilogue_frame<ST, CT, 1>(fr, scratch, pcm, shift, lossy); break;
+        case 2: epilogue_frame<ST, CT, 2>(fr, scratch, pcm, shift, lossy); break;
+        case 3: epilogue_frame<ST, CT, 3>(fr, scratch, pcm, shift, lossy); break;
+        case 4: epilogue_frame<ST, CT, 4>(fr, scratch, pcm, shift, lossy); break;
+        case 5: epilogue_frame<ST, CT, 5>(fr, scratch, pcm, shift, lossy); break;
+        case 6: epilogue_frame<ST, CT, 6>(fr, scratch, pcm, shift, lossy); break;
+        case 7: epilogue_frame<ST, CT, 7>(fr, scratch, pcm, shift, lossy); break;
+        default: epilogue_frame<ST, CT, 8>(fr, scratch, pcm, shift, lossy); break;
     }
     if (lossy) atomicOr(lossy_flag, 1u);
 }
@@ -82,7 +132,7 @@ __global__ void k_shift_inplace(CT *__restrict__ pcm, uint64_t n, uint32_t shift
 
 cudaError_t launch_epilogue(const EpilogueParams &p, cudaStream_t st) {
     if (p.n_frames == 0) return cudaSuccess;
-    uint32_t gy = (p.max_block_size + kEpiThreads - 1) / kEpiThreads;
+    uint32_t gy = (p.max_block_size + 4 * kEpiThreads - 1) / (4 * kEpiThreads);
     if (gy > 64) gy = 64;
     if (gy == 0) gy = 1;
     dim3 grid(p.n_frames, gy);

@@ -107,32 +107,39 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t len, ui
             Cand *__restrict__ out, uint32_t cap, uint32_t *__restrict__ total_out,
             unsigned long long *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
     __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_warp_sum[kScanThreads / 32];
+    __shared__ unsigned long long s_warp_sum[kScanThreads / 32];  // 4 x 16-bit row counts per warp
     __shared__ unsigned long long s_base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // tiles start in order: look-back below cannot deadlock
     __syncthreads();
     const uint32_t tile = s_tile;
     if (tile >= n_tiles) return;
     const uint64_t tile_base = tile0 + (uint64_t)tile * kScanTileBytes;
 
-    uint32_t valid[kScanRows];   // per row: 16-bit mask of validated candidates in my 16 bytes
-    uint32_t rank[kScanRows];    // per row: exclusive rank of my first candidate inside the tile
-    uint32_t running = 0;        // candidates in earlier rows of this tile
-
+    // ---- all loads of the tile first (4 independent 128-bit loads in flight per thread)
+    uint4 v[kScanRows];
 #pragma unroll
     for (int r = 0; r < kScanRows; ++r) {
         const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-        uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0, nb = 0;
-        if (pos + 17 <= len) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(s + pos));
-            w0 = v.x; w1 = v.y; w2 = v.z; w3 = v.w;
-            nb = s[pos + 16];
+        v[r] = make_uint4(0, 0, 0, 0);
+        if (pos + 16 <= len) {
+            v[r] = __ldg(reinterpret_cast<const uint4 *>(s + pos));
         } else if (pos < len) {  // stream tail: bytes past len read as zero
-            uint32_t t[5] = {0, 0, 0, 0, 0};
-            for (int i = 0; i < 17 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
-            w0 = t[0]; w1 = t[1]; w2 = t[2]; w3 = t[3]; nb = t[4];
+            uint32_t t[4] = {0, 0, 0, 0};
+            for (int i = 0; i < 16 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+            v[r] = make_uint4(t[0], t[1], t[2], t[3]);
         }
+    }
+
+    uint32_t valid[kScanRows];       // per row: 16-bit mask of validated candidates in my 16 bytes
+    unsigned long long counts = 0;   // 16 bits per row
+#pragma unroll
+    for (int r = 0; r < kScanRows; ++r) {
+        const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+        // the byte after my 16: the next lane's first byte; lane 31 fetches it (L1/L2 hit: a neighbour loads that line)
+        uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1) & 0xFFu;
+        if (lane == 31) nb = (pos + 16 < len) ? s[pos + 16] : 0u;
+        const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
         uint32_t raw = sync_mask4(w0, __funnelshift_r(w0, w1, 8)) |
                        (sync_mask4(w1, __funnelshift_r(w1, w2, 8)) << 4) |
                        (sync_mask4(w2, __funnelshift_r(w2, w3, 8)) << 8) |
@@ -146,46 +153,63 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t len, ui
             if (p >= scan_begin && parse_header_at(s, p, len, c)) ok |= 1u << b;
         }
         valid[r] = ok;
-        // exclusive scan of popc(ok) over the 256 threads of this row
-        const uint32_t cnt = __popc(ok);
-        uint32_t incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-            if (lane >= d) incl += t;
-        }
-        if (lane == 31) s_warp_sum[warp] = incl;
-        __syncthreads();
-        uint32_t warp_off = 0, row_total = 0;
-#pragma unroll
-        for (int w = 0; w < kScanThreads / 32; ++w) {
-            const uint32_t t = s_warp_sum[w];
-            if (w < warp) warp_off += t;
-            row_total += t;
-        }
-        rank[r] = running + warp_off + incl - cnt;
-        running += row_total;
-        __syncthreads();
+        counts |= (unsigned long long)__popc(ok) << (16 * r);
     }
 
-    // decoupled look-back: tile t publishes its aggregate, then sums its predecessors'
-    if (tid == 0) {
+    // ---- one block-wide exclusive scan for all four rows at once (row counts <= 4096 fit 16 bits)
+    unsigned long long incl = counts;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    unsigned long long warp_off = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+        const unsigned long long t = s_warp_sum[w];
+        if (w < warp) warp_off += t;
+        all += t;
+    }
+    const unsigned long long excl = warp_off + incl - counts;
+    uint32_t rank[kScanRows];
+    uint32_t running = 0;  // candidates in earlier rows of this tile
+#pragma unroll
+    for (int r = 0; r < kScanRows; ++r) {
+        rank[r] = running + (uint32_t)((excl >> (16 * r)) & 0xFFFFu);
+        running += (uint32_t)((all >> (16 * r)) & 0xFFFFu);
+    }
+
+    // ---- decoupled look-back by warp 0: tile t publishes its aggregate, then 32 predecessors at a
+    // time are inspected until one of them carries an inclusive prefix
+    if (warp == 0) {
         unsigned long long base = 0;
         volatile unsigned long long *st = tile_state;
         if (tile > 0) {
-            atomicExch(&tile_state[tile], kFlagAgg | (unsigned long long)running);
-            for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
-                unsigned long long v;
-                do {
-                    v = st[t];
-                } while ((v >> 62) == 0);
-                base += v & kValueMask;
-                if ((v >> 62) == 2) break;
+            if (lane == 0) atomicExch(&tile_state[tile], kFlagAgg | (unsigned long long)running);
+            for (int64_t hi = (int64_t)tile - 1;; hi -= 32) {
+                const int64_t idx = hi - lane;
+                unsigned long long val = kFlagPrefix;  // before tile 0: an empty prefix
+                if (idx >= 0) {
+                    do {
+                        val = st[idx];
+                    } while ((val >> 62) == 0);
+                }
+                const uint32_t has_prefix = __ballot_sync(0xFFFFFFFFu, (val >> 62) == 2);
+                const int first = has_prefix ? __ffs(has_prefix) - 1 : 32;  // nearest predecessor with a prefix
+                unsigned long long contrib = lane <= first ? (val & kValueMask) : 0ull;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) contrib += __shfl_xor_sync(0xFFFFFFFFu, contrib, d);
+                base += contrib;
+                if (has_prefix) break;
             }
         }
-        atomicExch(&tile_state[tile], kFlagPrefix | (base + running));
-        s_base = base;
-        if (tile == n_tiles - 1) *total_out = (uint32_t)min(base + running, (unsigned long long)0xFFFFFFFFull);
+        if (lane == 0) {
+            atomicExch(&tile_state[tile], kFlagPrefix | (base + running));
+            s_base = base;
+            if (tile == n_tiles - 1) *total_out = (uint32_t)min(base + running, (unsigned long long)0xFFFFFFFFull);
+        }
     }
     __syncthreads();
     const unsigned long long base = s_base;
@@ -230,14 +254,23 @@ struct CrcTables {
     uint16_t mul_lo[256]; // v * x^3968
 };
 
+// built once per device by k_init_crc_tables (scan_init_constants); every CTA copies the 1.5 KB into shared memory
+__device__ CrcTables g_crc_tables;
+
+__global__ void k_init_crc_tables() {
+    const int v = threadIdx.x;
+    uint32_t crc = (uint32_t)v << 8;
+    for (int i = 0; i < 8; ++i) crc = (crc & 0x8000u) ? ((crc << 1) ^ 0x8005u) & 0xFFFFu : (crc << 1) & 0xFFFFu;
+    g_crc_tables.byte[v] = (uint16_t)crc;
+    g_crc_tables.mul_hi[v] = (uint16_t)gf16_mul((uint32_t)v << 8, c_x3968);
+    g_crc_tables.mul_lo[v] = (uint16_t)gf16_mul((uint32_t)v, c_x3968);
+}
+
 __device__ void build_crc_tables(CrcTables &t) {
-    for (int v = threadIdx.x; v < 256; v += blockDim.x) {
-        uint32_t crc = (uint32_t)v << 8;
-        for (int i = 0; i < 8; ++i) crc = (crc & 0x8000u) ? ((crc << 1) ^ 0x8005u) & 0xFFFFu : (crc << 1) & 0xFFFFu;
-        t.byte[v] = (uint16_t)crc;
-        t.mul_hi[v] = (uint16_t)gf16_mul((uint32_t)v << 8, c_x3968);
-        t.mul_lo[v] = (uint16_t)gf16_mul((uint32_t)v, c_x3968);
-    }
+    static_assert(sizeof(CrcTables) % 4 == 0, "word copy");
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(&g_crc_tables);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&t);
+    for (int i = threadIdx.x; i < (int)(sizeof(CrcTables) / 4); i += blockDim.x) dst[i] = src[i];
     __syncthreads();
 }
 
@@ -362,7 +395,10 @@ cudaError_t scan_init_constants() {
     cudaError_t e;
     if ((e = cudaMemcpyToSymbol(c_pow_x8, p8, sizeof(p8))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_pow_x128, p128, sizeof(p128))) != cudaSuccess) return e;
-    return cudaMemcpyToSymbol(c_x3968, &x3968, sizeof(x3968));
+    if ((e = cudaMemcpyToSymbol(c_x3968, &x3968, sizeof(x3968))) != cudaSuccess) return e;
+    k_init_crc_tables<<<1, 256>>>();
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    return cudaDeviceSynchronize();
 }
 
 uint32_t scan_tile_count(uint64_t scan_begin, uint64_t len) {
