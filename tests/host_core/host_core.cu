@@ -15,6 +15,7 @@ struct HostSrc {
     // poison tracking: the device ring only guarantees kFastWords resident words after top_up();
     // mimic that so an unchecked read beyond the guarantee is caught here, not on the GPU
     uint32_t guaranteed;
+    uint32_t consumed_below;  // words below this index may already be overwritten in the device ring
     int violations;
     __host__ __device__ uint32_t raw(uint32_t w) const {
         uint32_t v = 0;
@@ -25,11 +26,17 @@ struct HostSrc {
         return __builtin_bswap32(v);
     }
     __host__ __device__ uint32_t word(uint32_t w) {
-        if (w >= guaranteed) ++violations;
+        if (w >= guaranteed || w < consumed_below) ++violations;
         return raw(w);
     }
-    __host__ __device__ uint32_t word_checked(uint32_t w) { return raw(w); }
-    __host__ __device__ void top_up(uint32_t cur) { guaranteed = cur + zf::kFastWords; }
+    __host__ __device__ uint32_t word_checked(uint32_t w) {
+        if (w > consumed_below) consumed_below = w;  // the device refills with `words < w are consumed`
+        return raw(w);
+    }
+    __host__ __device__ void top_up(uint32_t cur) {
+        guaranteed = cur + zf::kFastWords;
+        if (cur > consumed_below) consumed_below = cur;
+    }
     // raw order here = byte-reversed, like the little-endian shared-memory word of the device ring
     static __host__ __device__ uint32_t fix(uint32_t raw) { return __builtin_bswap32(raw); }
 };
@@ -49,6 +56,7 @@ int zf_host_decode_frame(const uint8_t *stream, const zf::FrameRec *fr, void *sc
     br.src.g = stream + origin;
     br.src.avail = bytes;
     br.src.guaranteed = 0;
+    br.src.consumed_below = 0;
     br.src.violations = 0;
     br.init((uint32_t)(start & 3));
     if (wide) zf::decode_frame<int64_t>(br, *fr, (int64_t *)scratch, bytes * 8, write_samples != 0, origin, *out);

@@ -37,19 +37,21 @@ __device__ __noinline__ uint32_t ring_wait(uint32_t need, uint32_t ready, uint32
     return filled;
 }
 
+extern __shared__ uint32_t zf_ring[];  // kRingWords x NT words
+
 template <int NT>
 struct RingSrc {
     const uint8_t *g;    // global address of word 0 (4-byte aligned)
     uint32_t avail;      // bytes readable from g (stream end), clamped
-    uint32_t col;        // shared-space address of ring[0][lane column]
+    uint32_t col;        // shared-space byte address of zf_ring[lane column]: word w lives (w % kRingWords) * NT words further
     uint32_t filled;     // words < filled have been issued
     uint32_t ready;      // words < ready have landed
     uint32_t h0, h1, h2; // `filled` before the newest / 2nd newest / 3rd newest committed group
 
-    __device__ __forceinline__ void init(const uint8_t *base, uint64_t bytes, uint32_t *column) {
+    __device__ __forceinline__ void init(const uint8_t *base, uint64_t bytes, uint32_t column) {
         g = base;
         avail = bytes > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)bytes;
-        col = (uint32_t)__cvta_generic_to_shared(column);
+        col = (uint32_t)__cvta_generic_to_shared(&zf_ring[column]);
         filled = ready = h0 = h1 = h2 = 0;
     }
     __device__ __forceinline__ uint32_t slot(uint32_t w) const { return col + (w & (kRingWords - 1)) * (NT * 4); }
@@ -65,6 +67,7 @@ struct RingSrc {
     __device__ __forceinline__ void fill(uint32_t cur) {
         if (filled < cur + kRingWords) {
             const uint32_t before = filled;
+#pragma unroll 1
             do {
                 issue(filled);
                 ++filled;
@@ -101,7 +104,6 @@ template <typename ST>
 __global__ void __launch_bounds__(kDecodeThreads)
 k_decode_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frames, uint32_t n_frames,
                 ST *__restrict__ scratch, FrameOut *__restrict__ outs, int write_samples) {
-    __shared__ uint32_t ring[kRingWords * kDecodeThreads];
     const uint32_t f = blockIdx.x * kDecodeThreads + threadIdx.x;
     if (f >= n_frames) return;
     const FrameRec fr = frames[f];
@@ -109,7 +111,7 @@ k_decode_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ fram
     const uint64_t start = fr.offset + fr.header_len;  // first subframe header
     const uint64_t origin = start & ~3ull;             // word 0 of the lane's source
     BitReader<RingSrc<kDecodeThreads>> br;
-    br.src.init(s + origin, fr.stream_end > origin ? fr.stream_end - origin : 0, ring + threadIdx.x);
+    br.src.init(s + origin, fr.stream_end > origin ? fr.stream_end - origin : 0, threadIdx.x);
     br.init((uint32_t)(start & 3));
     const uint64_t len_bits = (fr.stream_end > origin ? fr.stream_end - origin : 0) * 8;
     FrameOut o;
@@ -124,10 +126,10 @@ cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_fram
     const uint32_t blocks = (n_frames + kDecodeThreads - 1) / kDecodeThreads;
     ZF_COUNT_LAUNCH();
     if (wide_scratch)
-        k_decode_frames<int64_t><<<blocks, kDecodeThreads, 0, st>>>(d_stream, d_frames, n_frames, (int64_t *)d_scratch, d_outs,
+        k_decode_frames<int64_t><<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(d_stream, d_frames, n_frames, (int64_t *)d_scratch, d_outs,
                                                                     write_samples ? 1 : 0);
     else
-        k_decode_frames<int32_t><<<blocks, kDecodeThreads, 0, st>>>(d_stream, d_frames, n_frames, (int32_t *)d_scratch, d_outs,
+        k_decode_frames<int32_t><<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(d_stream, d_frames, n_frames, (int32_t *)d_scratch, d_outs,
                                                                     write_samples ? 1 : 0);
     return cudaGetLastError();
 }

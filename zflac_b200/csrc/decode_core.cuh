@@ -64,11 +64,12 @@ ZF_HD uint32_t shl_c(uint32_t v, uint32_t n) {  // n >= 32 -> 0
     return n >= 32 ? 0u : v << n;
 #endif
 }
-// top 32 bits of (hi:lo) << s, s in [0, 31]
+// top 32 bits of (hi:lo) << (s & 31)
 ZF_HD uint32_t funnel_hi(uint32_t hi, uint32_t lo, uint32_t s) {
 #ifdef __CUDA_ARCH__
     return __funnelshift_l(lo, hi, s);
 #else
+    s &= 31;
     return s ? (hi << s) | (lo >> (32 - s)) : hi;
 #endif
 }
@@ -85,7 +86,7 @@ ZF_HD int32_t zigzag(uint32_t u) { return (int32_t)((u >> 1) ^ (0u - (u & 1u)));
 // Words at or past the end of the stream read as zero; running off the stream is detected
 // from the bit position, exactly when the reference's byte reader returns EndOfStream.
 // ---------------------------------------------------------------------------------------
-constexpr uint32_t kFastWords = 9;  // 8 unchecked codewords of <= 32 bits pull at most 8 words (+1 slack)
+constexpr uint32_t kFastWords = 9;  // a fast body re-reads word next-1 and pulls at most 8 more: next-1 .. next+7
 
 template <class Src>
 struct BitReader {
@@ -106,12 +107,24 @@ struct BitReader {
     ZF_HD uint32_t peek() const { return funnel_hi(A, B, o); }
     template <bool CHECKED> ZF_HD void skip(uint32_t n) {  // n <= 32
         o += n;
-        if (o >= 32) {
-            o -= 32;
-            A = B;
-            B = Src::fix(N);
-            N = CHECKED ? src.word_checked(next) : src.word(next);
-            ++next;
+        if (CHECKED) {
+            if (o >= 32) {
+                o -= 32;
+                A = B;
+                B = Src::fix(N);
+                N = src.word_checked(next);
+                ++next;
+            }
+        } else {
+            // Branch-free (fast 8-row bodies): the word pipeline advances under a predicate and N is
+            // RE-loaded from its own (possibly advanced) index every row, so no select ever sits on a
+            // value fresh out of shared memory and the compiler can schedule across rows.
+            const bool wrap = o >= 32;
+            o &= 31u;
+            A = wrap ? B : A;
+            B = wrap ? Src::fix(N) : B;
+            next = wrap ? next + 1 : next;
+            N = src.word(next - 1);
         }
     }
     ZF_HD uint32_t read(uint32_t n) {  // n in [0, 32]
@@ -147,7 +160,8 @@ struct BitReader {
         }
     }
     ZF_HD void align_byte() { skip<true>((8u - (o & 7u)) & 7u); }  // word starts are byte aligned
-    ZF_HD void prepare_fast() { src.top_up(next); }
+    // N (word next-1) is re-read by the branch-free skip: it still counts as live
+    ZF_HD void prepare_fast() { src.top_up(next - 1); }
 };
 
 ZF_HD int32_t fixed_coef(uint32_t order, int j) {  // :481-490 {1; 2,-1; 3,-3,1; 4,-6,4,-1}
@@ -247,11 +261,16 @@ ZF_HDI uint32_t predicted_subframe(BitReader<Src> &br, int32_t *__restrict__ out
             }
         } else {
             const uint32_t k = param, kp1 = param + 1, rsh = 32 - param;
+            uint32_t force_single = 0;  // rows that must take the checked one-row path (after a rolled-back body)
 #pragma unroll 1
             while (i < end) {
-                if ((i & 7u) == 0 && i + 8 <= end) {
-                    // ---- 8 rows: unchecked word loads, static window indices, two 128-bit stores
+                if (force_single == 0 && (i & 7u) == 0 && i + 8 <= end) {
+                    // ---- 8 rows, speculative: straight-line code, unchecked word loads, static window
+                    // indices. A codeword longer than the 32-bit window (rare) only raises `bad`; the
+                    // body is then rolled back and its rows are redone one by one below.
                     br.prepare_fast();
+                    const uint32_t sA = br.A, sB = br.B, sN = br.N, so = br.o, snext = br.next;
+                    uint32_t bad = 0;
                     int32_t x[P + 8];
 #pragma unroll
                     for (int j = 0; j < P; ++j) x[j] = h[j];
@@ -260,37 +279,37 @@ ZF_HDI uint32_t predicted_subframe(BitReader<Src> &br, int32_t *__restrict__ out
                         const uint32_t win = br.peek();
                         const uint32_t z = clz32(win);
                         const uint32_t n = z + kp1;
-                        uint32_t cw;
-                        if (n <= 32) {  // whole codeword inside the window: the common case
-                            cw = (z << k) | shr_c(shl_c(win, z + 1), rsh);
-                            br.template skip<false>(n);
-                        } else {
-                            cw = rice_slow(br, k, len_bits, err);
-                            br.prepare_fast();
-                        }
+                        bad |= (n > 32u) ? 1u : 0u;
+                        const uint32_t cw = (z << k) | shr_c(shl_c(win, z + 1), rsh);
+                        br.template skip<false>(n & 63u);
                         ACC acc = 0;
 #pragma unroll
                         for (int j = P - 1; j >= 0; --j) acc += (ACC)c[j] * (ACC)x[P + u - 1 - j];  // newest tap last
                         x[P + u] = zigzag(cw) + (int32_t)(acc >> shift);
                     }
+                    if (!bad) {
 #pragma unroll
-                    for (int j = 0; j < P; ++j) h[j] = x[j + 8];
-                    if (wr) {
-                        int4 a, b;
-                        a.x = (int32_t)((uint32_t)x[P + 0] << wasted);
-                        a.y = (int32_t)((uint32_t)x[P + 1] << wasted);
-                        a.z = (int32_t)((uint32_t)x[P + 2] << wasted);
-                        a.w = (int32_t)((uint32_t)x[P + 3] << wasted);
-                        b.x = (int32_t)((uint32_t)x[P + 4] << wasted);
-                        b.y = (int32_t)((uint32_t)x[P + 5] << wasted);
-                        b.z = (int32_t)((uint32_t)x[P + 6] << wasted);
-                        b.w = (int32_t)((uint32_t)x[P + 7] << wasted);
-                        *reinterpret_cast<int4 *>(out + i) = a;
-                        *reinterpret_cast<int4 *>(out + i + 4) = b;
+                        for (int j = 0; j < P; ++j) h[j] = x[j + 8];
+                        if (wr) {
+                            int4 a, b;
+                            a.x = (int32_t)((uint32_t)x[P + 0] << wasted);
+                            a.y = (int32_t)((uint32_t)x[P + 1] << wasted);
+                            a.z = (int32_t)((uint32_t)x[P + 2] << wasted);
+                            a.w = (int32_t)((uint32_t)x[P + 3] << wasted);
+                            b.x = (int32_t)((uint32_t)x[P + 4] << wasted);
+                            b.y = (int32_t)((uint32_t)x[P + 5] << wasted);
+                            b.z = (int32_t)((uint32_t)x[P + 6] << wasted);
+                            b.w = (int32_t)((uint32_t)x[P + 7] << wasted);
+                            *reinterpret_cast<int4 *>(out + i) = a;
+                            *reinterpret_cast<int4 *>(out + i + 4) = b;
+                        }
+                        i += 8;
+                    } else {
+                        br.A = sA; br.B = sB; br.N = sN; br.o = so; br.next = snext;
+                        force_single = 8;
                     }
-                    i += 8;
                 } else {
-                    // ---- one row (head up to an 8-aligned index, partition tails): checked reads
+                    // ---- one row (head up to an 8-aligned index, partition tails, rolled-back bodies): checked reads
                     const uint32_t win = br.peek();
                     const uint32_t z = clz32(win);
                     const uint32_t n = z + kp1;
@@ -310,8 +329,9 @@ ZF_HDI uint32_t predicted_subframe(BitReader<Src> &br, int32_t *__restrict__ out
                     h[P - 1] = v;
                     if (wr) out[i] = (int32_t)((uint32_t)v << wasted);
                     ++i;
+                    if (force_single) --force_single;
+                    if (err != ST_OK) return err;
                 }
-                if (err != ST_OK) return err;
             }
         }
         if (br.pos_bits() > len_bits) return ST_END_OF_STREAM;
