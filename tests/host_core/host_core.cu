@@ -17,6 +17,7 @@ struct HostSrc {
     uint32_t guaranteed;
     uint32_t consumed_below;  // words below this index may already be overwritten in the device ring
     int violations;
+    int rollbacks;  // fast bodies that met a codeword longer than the 32-bit window
     __host__ __device__ uint32_t raw(uint32_t w) const {
         uint32_t v = 0;
         for (int i = 0; i < 4; ++i) {
@@ -38,10 +39,13 @@ struct HostSrc {
         if (cur > consumed_below) consumed_below = cur;
     }
     // raw order here = byte-reversed, like the little-endian shared-memory word of the device ring
+    __host__ __device__ void note_rollback() { ++rollbacks; }
     static __host__ __device__ uint32_t fix(uint32_t raw) { return __builtin_bswap32(raw); }
 };
 
 }  // namespace
+
+static long long *g_rollbacks = nullptr;
 
 extern "C" {
 
@@ -58,11 +62,15 @@ int zf_host_decode_frame(const uint8_t *stream, const zf::FrameRec *fr, void *sc
     br.src.guaranteed = 0;
     br.src.consumed_below = 0;
     br.src.violations = 0;
+    br.src.rollbacks = 0;
     br.init((uint32_t)(start & 3));
     if (wide) zf::decode_frame<int64_t>(br, *fr, (int64_t *)scratch, bytes * 8, write_samples != 0, origin, *out);
     else zf::decode_frame<int32_t>(br, *fr, (int32_t *)scratch, bytes * 8, write_samples != 0, origin, *out);
+    if (g_rollbacks) *g_rollbacks += br.src.rollbacks;
     return br.src.violations;
 }
+
+void zf_host_set_rollback_counter(long long *p) { g_rollbacks = p; }
 
 int zf_host_framerec_size(void) { return (int)sizeof(zf::FrameRec); }
 }

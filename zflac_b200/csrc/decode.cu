@@ -18,7 +18,7 @@
 
 namespace zf {
 
-constexpr int kDecodeThreads = 64;
+constexpr int kDecodeThreads = 128;
 constexpr uint32_t kRingWords = 32;  // 128 B per lane ahead of the cursor (~130 rows of 16-bit audio)
 
 // Block until words < need have landed, waiting on as few (= as old) cp.async groups as possible.
@@ -56,12 +56,15 @@ struct RingSrc {
     }
     __device__ __forceinline__ uint32_t slot(uint32_t w) const { return col + (w & (kRingWords - 1)) * (NT * 4); }
     __device__ __forceinline__ void issue(uint32_t w) {
-        const uint32_t off = w * 4u;
-        const uint32_t rem = off < avail ? avail - off : 0u;
-        const uint32_t n = rem < 4u ? rem : 4u;  // bytes past the stream end are zero-filled
-        const uint8_t *src = g + (n ? off : 0u);
         const uint32_t dst = slot(w);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+        if (w < (avail >> 2)) {  // a whole word inside the stream: the hot case
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(g + (size_t)w * 4u) : "memory");
+        } else {                 // bytes past the stream end are zero-filled
+            const uint32_t off = w * 4u;
+            const uint32_t n = off < avail ? avail - off : 0u;  // 0..3
+            const uint8_t *src = g + (n ? off : 0u);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+        }
     }
     // words < cur are consumed: issue everything the ring has room for
     __device__ __forceinline__ void fill(uint32_t cur) {
@@ -88,6 +91,7 @@ struct RingSrc {
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(slot(w)));
         return v;
     }
+    __device__ __forceinline__ void note_rollback() {}
     static __device__ __forceinline__ uint32_t fix(uint32_t raw) { return __byte_perm(raw, 0, 0x0123); }
     __device__ __forceinline__ uint32_t word_checked(uint32_t w) {
         if (w >= ready) {

@@ -306,6 +306,7 @@ ZF_HDI uint32_t predicted_subframe(BitReader<Src> &br, int32_t *__restrict__ out
                         i += 8;
                     } else {
                         br.A = sA; br.B = sB; br.N = sN; br.o = so; br.next = snext;
+                        br.src.note_rollback();
                         force_single = 8;
                     }
                 } else {
