@@ -66,6 +66,7 @@ typedef enum zflacb200_status {
 #define ZFLACB200_SKIP_MD5 0x2u        /* additive: do not hash; never returns InvalidChecksum */
 #define ZFLACB200_INPUT_ON_DEVICE 0x4u /* `data` is a device pointer (bench: inputs resident in HBM) */
 #define ZFLACB200_NO_CRC_ACCEL 0x8u    /* diagnostics: ignore CRC-16 links, probe every frame end (slow path) */
+#define ZFLACB200_NO_FAST_PATH 0x10u   /* diagnostics: skip the device-side hinted chain, walk the chain on the host */
 
 typedef struct zflacb200_options {
     uint32_t struct_size; /* sizeof(zflacb200_options) */
@@ -90,6 +91,7 @@ typedef struct zflacb200_info {
     uint64_t n_candidates;       /* frame-index entries the sync scan emitted */
     uint64_t n_probed_frames;    /* frames whose end had to be found by decoding (no CRC-16 link) */
     uint64_t n_crc16_mismatch;   /* decoded frames whose CRC-16 does not match (reference ignores it, Q1) */
+    uint64_t fast_path;          /* 1: device-side hinted chain accepted; 0: chain walked on the host */
     uint8_t md5_computed[16];
     uint8_t md5_streaminfo[16];
     /* device time of the last open(), ms, CUDA events on the launch stream */

@@ -53,8 +53,8 @@ def test_frame_index_matches_oracle_chain(z, entry):
     from oracle import oracle
     data = corpus_bytes(entry)
     ref = oracle.decode(data, trace_frames=True)
-    for links in (True, False):
-        s = z.open_device(0, 0, host_data=data, use_crc_links=links)
+    for fast, links in ((True, True), (False, True), (False, False)):
+        s = z.open_device(0, 0, host_data=data, use_crc_links=links, use_fast_path=fast)
         fr = s.frames()
         assert np.array_equal(fr["offset"], ref.frames["offset"])
         assert np.array_equal(fr["end_offset"], ref.frames["end_offset"])
@@ -62,6 +62,22 @@ def test_frame_index_matches_oracle_chain(z, entry):
         assert np.array_equal(fr["block_size"], ref.frames["block_size"])
         assert np.array_equal(s.to_host(), ref.samples)
         assert s.info["n_crc16_mismatch"] == 0
+        if not fast:
+            assert s.info["fast_path"] == 0
         if not links:
             assert s.info["n_probed_frames"] == fr.size
         s.close()
+
+
+def test_fast_path_covers_the_regular_corpus(z):
+    """The device-side hinted chain (no host walk) must be the path that actually runs on ordinary streams:
+    every error-free corpus file with a stated total and consecutive coded numbers."""
+    taken = {}
+    for entry in corpus_entries():
+        if entry["expect_error"]:
+            continue
+        s = z.open_device(0, 0, host_data=corpus_bytes(entry))
+        taken[f"{entry['group']}_{entry['id']}"] = s.info["fast_path"]
+        s.close()
+    assert taken["subset_01"] == 1 and taken["subset_28"] == 1
+    assert sum(taken.values()) >= len(taken) * 3 // 4, taken

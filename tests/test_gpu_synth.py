@@ -26,7 +26,11 @@ def test_cuda_matches_oracle_and_generator(z, name):
     assert np.array_equal(got.samples, ref.samples)
     assert got.info["md5_computed"] == s.md5 == ref.md5_computed
     assert got.info["n_frames"] == s.n_frames
-    # same answer when every frame end is found by decoding instead of CRC-16 links
+    if name != "unknown_total":  # regular streams must take the device-side chain (fast path)
+        assert got.info["fast_path"] == 1, name
+    # same answer when the host walks the chain (CRC-16 links), and when every frame end is found by decoding
+    got1 = z.decode(s.flac, use_fast_path=False)
+    assert got1.info["fast_path"] == 0 and np.array_equal(got1.samples, s.pcm)
     got2 = z.decode(s.flac, use_crc_links=False)
     assert np.array_equal(got2.samples, s.pcm)
 
@@ -41,6 +45,9 @@ def test_crc_damage_is_ignored_like_the_reference(z):
     bad_crc = s.flac.copy()
     bad_crc[end - 1] ^= 0x5A
     got = z.decode(bad_crc)
+    assert np.array_equal(got.samples, s.pcm)
+    assert got.info["n_crc16_mismatch"] == 1
+    got = z.decode(bad_crc, use_fast_path=False)
     assert np.array_equal(got.samples, s.pcm)
     assert got.info["n_crc16_mismatch"] == 1 and got.info["n_probed_frames"] >= 1
     hdr = int(r0.frames["offset"][5]) + int(r0.frames["header_len"][5]) - 1  # CRC-8 byte of frame 5

@@ -21,7 +21,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _native
-from ._native import INPUT_ON_DEVICE, NO_CRC_ACCEL, SKIP_MD5, VERIFY_MD5  # noqa: F401
+from ._native import INPUT_ON_DEVICE, NO_CRC_ACCEL, NO_FAST_PATH, SKIP_MD5, VERIFY_MD5  # noqa: F401
 
 __all__ = ["decode", "decode_into", "DecodedFLAC", "ZflacError", "CudaError", "open_device", "DeviceStream"]
 
@@ -95,12 +95,13 @@ def _as_u8(data) -> np.ndarray:
 _DTYPES = {1: np.int8, 2: np.int16, 4: np.int32}
 
 
-def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bool = True) -> DecodedFLAC:
+def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bool = True,
+           use_fast_path: bool = True) -> DecodedFLAC:
     """Drop-in for `zflac.decode(allocator, reader)`: `data` is bytes / ndarray / a readable object
     holding the whole stream. Raises the ZflacError subclass named like the Zig error."""
     lib = _native.load()
     arr = _as_u8(data)
-    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL)
+    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL) | (0 if use_fast_path else NO_FAST_PATH)
     opt = _options(flags, device)
     handle = C.c_void_p()
     info = _native.Info()
@@ -172,11 +173,11 @@ class DeviceStream:
 
 
 def open_device(dev_ptr: int, nbytes: int, *, device: int = -1, stream: int | None = None, verify_md5: bool = True,
-                use_crc_links: bool = True, host_data=None) -> DeviceStream:
+                use_crc_links: bool = True, use_fast_path: bool = True, host_data=None) -> DeviceStream:
     """Decode a stream that already sits in device memory (or, with host_data, upload it first)
     and keep the PCM on the device."""
     lib = _native.load()
-    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL)
+    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL) | (0 if use_fast_path else NO_FAST_PATH)
     if host_data is not None:
         arr = _as_u8(host_data)
         ptr, n = arr.ctypes.data, arr.size

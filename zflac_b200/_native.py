@@ -13,6 +13,7 @@ VERIFY_MD5 = 0x1
 SKIP_MD5 = 0x2
 INPUT_ON_DEVICE = 0x4
 NO_CRC_ACCEL = 0x8
+NO_FAST_PATH = 0x10
 
 EXPORTS = [
     "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown",
@@ -30,7 +31,7 @@ class Info(C.Structure):
                 ("md5_checked", C.c_uint8), ("sample_rate", C.c_uint32), ("n_samples", C.c_uint64),
                 ("pcm_bytes", C.c_uint64), ("n_frames", C.c_uint64), ("audio_offset", C.c_uint64),
                 ("audio_bytes", C.c_uint64), ("n_candidates", C.c_uint64), ("n_probed_frames", C.c_uint64),
-                ("n_crc16_mismatch", C.c_uint64), ("md5_computed", C.c_uint8 * 16),
+                ("n_crc16_mismatch", C.c_uint64), ("fast_path", C.c_uint64), ("md5_computed", C.c_uint8 * 16),
                 ("md5_streaminfo", C.c_uint8 * 16), ("ms_scan", C.c_float), ("ms_link", C.c_float),
                 ("ms_decode", C.c_float), ("ms_epilogue", C.c_float), ("ms_md5", C.c_float), ("ms_total", C.c_float)]
 

@@ -34,6 +34,8 @@ std::mutex g_mutex;
 struct DeviceCtx {
     bool ready = false;
     cudaStream_t stream = nullptr;
+    cudaStream_t side = nullptr;  // diagnostics that overlap the main pipeline (per-frame CRC-16)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 DeviceCtx g_ctx[64];
 
@@ -70,6 +72,9 @@ int ensure_device(int device, int *resolved) {
             return ZFLACB200_CUDA_ERROR;
         }
         CU_CHECK(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+        CU_CHECK(cudaStreamCreateWithFlags(&c.side, cudaStreamNonBlocking));
+        CU_CHECK(cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming));
+        CU_CHECK(cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming));
         CU_CHECK(scan_init_constants());
         cudaMemPool_t pool;
         CU_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
@@ -378,6 +383,12 @@ struct zflacb200_stream {
     uint64_t pcm_bytes = 0;
     zflacb200_info info;
     std::vector<zflacb200_frame> frames;
+    // fast path: the frame table stays on the device until zflacb200_frames() asks for it
+    FrameRec *d_recs = nullptr;
+    FrameOut *d_outs = nullptr;
+    uint8_t *d_frame_ok = nullptr;
+    uint32_t n_recs = 0;
+    bool frames_on_device = false;
 };
 
 namespace {
@@ -399,6 +410,156 @@ struct DevBuf {  // stream-ordered allocation released on scope exit
         if (p) cudaFreeAsync(p, st);
     }
 };
+
+constexpr int kFastFallback = -1;  // not an error: the hinted chain was not accepted, walk it on the host
+
+struct FastArgs {
+    int device;
+    cudaStream_t st;
+    const uint8_t *d_stream;
+    uint64_t len;
+    const Streaminfo *si;
+    uint64_t audio_offset;
+    const Cand *d_cands;
+    uint32_t n_cand;
+    bool wide;
+    uint32_t container_bytes, aligned_depth, msb_shift;
+    bool do_md5;
+    Events *ev;
+};
+
+// Fast path: hinted frame records for every candidate -> K2 over all of them -> K3,
+// with the chain rules verified on the device from the decoded frame ends and the per-frame CRC-16
+// on a side stream. One host synchronisation at the very end. Returns ZFLACB200_OK with *out set,
+// kFastFallback when the stream needs the robust host-walked chain, or a CUDA-level error.
+int fast_path(const FastArgs &a, zflacb200_stream **out, zflacb200_info *info) {
+    cudaStream_t st = a.st;
+    DeviceCtx &ctx = g_ctx[a.device];
+    const uint32_t n = a.n_cand;
+    const uint32_t C = a.si->channels_m1 + 1;
+    const uint64_t total = a.si->total;
+    const uint64_t n_samples = total * C;
+    const uint64_t pcm_bytes = n_samples * a.container_bytes;
+    const uint64_t scratch_elems = (uint64_t)C * (((total + 7) & ~7ull) + 8) + 64ull * n + 64;
+    const uint32_t window = 16;
+
+    StreamDesc sd;
+    memset(&sd, 0, sizeof(sd));
+    sd.begin = 0;
+    sd.end = a.len;
+    sd.audio_begin = a.audio_offset;
+    sd.total = total;
+    sd.pcm_base = 0;
+    sd.scratch_base = 0;
+    sd.si_sample_rate = a.si->sample_rate;
+    sd.si_channels = (uint8_t)C;
+    sd.si_depth = (uint8_t)(a.si->depth_m1 + 1);
+
+    DevBuf b_sd, b_recs, b_outs, b_scratch, b_pcm, b_sum, b_ok, b_flag, b_jobs, b_digest;
+    if (b_sd.alloc(sizeof(sd), st) || b_recs.alloc(sizeof(FrameRec) * (size_t)n, st) || b_outs.alloc(sizeof(FrameOut) * (size_t)n, st) ||
+        b_scratch.alloc(scratch_elems * (a.wide ? 8 : 4), st) || b_pcm.alloc(pcm_bytes + 64, st) ||
+        b_sum.alloc(sizeof(StreamSummary), st) || b_ok.alloc(n, st) || b_flag.alloc(sizeof(uint32_t), st) ||
+        b_jobs.alloc(sizeof(Md5Job), st) || b_digest.alloc(16, st))
+        return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(cudaMemcpyAsync(b_sd.p, &sd, sizeof(sd), cudaMemcpyHostToDevice, st));
+    CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary), st));
+    CU_CHECK(cudaMemsetAsync(b_ok.p, 2, n, st));  // 2 = not checked
+    CU_CHECK(cudaMemsetAsync(b_flag.p, 0, sizeof(uint32_t), st));
+    CU_CHECK(cudaMemsetAsync(b_outs.p, 0xFF, sizeof(FrameOut) * (size_t)n, st));  // dropped slots: status != OK
+
+    CU_CHECK(launch_hint_chain(a.d_cands, n, (const StreamDesc *)b_sd.p, 1, (FrameRec *)b_recs.p, window, st));
+    CU_CHECK(cudaEventRecord(a.ev->e[3], st));
+    CU_CHECK(cudaEventRecord(a.ev->e[4], st));
+    CU_CHECK(launch_decode_frames(a.d_stream, (const FrameRec *)b_recs.p, n, b_scratch.p, a.wide, (FrameOut *)b_outs.p, true, st));
+    CU_CHECK(cudaEventRecord(a.ev->e[5], st));
+
+    // side stream: CRC-16 of every decoded frame, overlapping K3 (+K4)
+    CU_CHECK(cudaEventRecord(ctx.ev_fork, st));
+    CU_CHECK(cudaStreamWaitEvent(ctx.side, ctx.ev_fork, 0));
+    CU_CHECK(launch_crc16_frames(a.d_stream, (const FrameRec *)b_recs.p, (const FrameOut *)b_outs.p, n, (StreamSummary *)b_sum.p,
+                                 (uint8_t *)b_ok.p, ctx.side));
+    CU_CHECK(cudaEventRecord(ctx.ev_join, ctx.side));
+
+    CU_CHECK(launch_verify_chain(a.d_cands, n, (const StreamDesc *)b_sd.p, 1, (const FrameRec *)b_recs.p, (const FrameOut *)b_outs.p,
+                                 (StreamSummary *)b_sum.p, window, st));
+    EpilogueParams ep;
+    ep.frames = (const FrameRec *)b_recs.p;
+    ep.n_frames = n;
+    // records are per candidate, block sizes are only known on the device: size the grid from STREAMINFO (any value is correct)
+    ep.max_block_size = a.si->max_block >= 16 ? a.si->max_block : 4096;
+    ep.scratch = b_scratch.p;
+    ep.wide_scratch = a.wide;
+    ep.pcm = b_pcm.p;
+    ep.container_bytes = a.container_bytes;
+    ep.msb_shift = a.msb_shift;
+    ep.lossy_flag = (uint32_t *)b_flag.p;
+    CU_CHECK(launch_epilogue(ep, st));
+    CU_CHECK(cudaEventRecord(a.ev->e[6], st));
+
+    StreamSummary sum;
+    uint32_t lossy = 0;
+    if (a.do_md5) {
+        if (a.msb_shift) {  // a sample wider than the STREAMINFO depth loses bits in the shift (Q5): hash before shifting
+            CU_CHECK(cudaMemcpyAsync(&lossy, b_flag.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CU_CHECK(cudaStreamSynchronize(st));
+            if (lossy) {
+                ep.msb_shift = 0;
+                CU_CHECK(launch_epilogue(ep, st));
+            }
+        }
+        Md5Job job;
+        job.pcm = b_pcm.p;
+        job.n_samples = n_samples;
+        job.container_bytes = a.container_bytes;
+        job.hash_bytes = a.aligned_depth == 24 ? 3 : a.container_bytes;  // :268-277
+        job.unshift = lossy ? 0 : a.msb_shift;
+        job.pad = 0;
+        CU_CHECK(cudaMemcpyAsync(b_jobs.p, &job, sizeof(job), cudaMemcpyHostToDevice, st));
+        CU_CHECK(launch_md5((const Md5Job *)b_jobs.p, 1, (uint8_t *)b_digest.p, st));
+        if (lossy) CU_CHECK(launch_shift_inplace(b_pcm.p, n_samples, a.container_bytes, a.msb_shift, st));
+        CU_CHECK(cudaMemcpyAsync(info->md5_computed, b_digest.p, 16, cudaMemcpyDeviceToHost, st));
+    }
+    CU_CHECK(cudaEventRecord(a.ev->e[7], st));
+    CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));
+    CU_CHECK(cudaMemcpyAsync(&sum, b_sum.p, sizeof(sum), cudaMemcpyDeviceToHost, st));
+    CU_CHECK(cudaStreamSynchronize(st));
+
+    if (sum.fail || !sum.first_ok || sum.n_samples != n_samples || sum.channels != C) return kFastFallback;
+
+    info->ms_scan = ev_ms(a.ev->e[1], a.ev->e[2]);
+    info->ms_link = ev_ms(a.ev->e[2], a.ev->e[3]);
+    info->ms_decode = ev_ms(a.ev->e[4], a.ev->e[5]);
+    info->ms_epilogue = ev_ms(a.ev->e[5], a.ev->e[6]);
+    info->ms_md5 = ev_ms(a.ev->e[6], a.ev->e[7]);
+    info->ms_total = ev_ms(a.ev->e[0], a.ev->e[7]);
+    info->md5_checked = a.do_md5 ? 1 : 0;
+    if (a.do_md5 && memcmp(info->md5_computed, a.si->md5, 16) != 0) return ZFLACB200_INVALID_CHECKSUM;  // :279-280
+
+    info->channels = sum.channels;
+    info->bits_per_sample = sum.bps;
+    info->sample_rate = sum.sample_rate;
+    info->n_samples = n_samples;
+    info->pcm_bytes = pcm_bytes;
+    info->n_frames = sum.n_frames;
+    info->n_candidates = n;
+    info->n_probed_frames = 0;
+    info->fast_path = 1;
+    info->n_crc16_mismatch = sum.n_crc16_mismatch;
+    info->audio_bytes = sum.end_offset - a.audio_offset;
+
+    zflacb200_stream *h = new zflacb200_stream();
+    h->device = a.device;
+    h->pcm_bytes = pcm_bytes;
+    h->d_pcm = b_pcm.release();
+    h->d_recs = (FrameRec *)b_recs.release();
+    h->d_outs = (FrameOut *)b_outs.release();
+    h->d_frame_ok = (uint8_t *)b_ok.release();
+    h->n_recs = n;
+    h->frames_on_device = true;
+    h->info = *info;
+    *out = h;
+    return ZFLACB200_OK;
+}
 
 int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info) {
     if (!data || !out || !info) {
@@ -477,7 +638,42 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
         }
     }
     CU_CHECK(cudaEventRecord(ev.e[2], st));
+    info->n_candidates = n_cand;
 
+    {   // a 32 bps stream (side channel: 33 bits) runs on the int64 scratch; bps is latched by the first frame
+        Hdr h0;
+        if (host_parse_header(pl.src, pl.audio_offset, h0) == ZFLACB200_OK)
+            pl.wide = (h0.bd_code == 0 ? depth : kBps[h0.bd_code]) == 32;
+    }
+    uint32_t msb_shift = 0;  // :287-306, keyed on the STREAMINFO depth
+    if (depth >= 9 && depth <= 15) msb_shift = 16 - depth;
+    else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
+    const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0;
+
+    // ---- fast path: device-side hinted chain, verified after decoding (no host walk, no CRC-16 pre-pass)
+    if (n_cand > 0 && pl.si.total > 0 && (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0 &&
+        pl.si.total * (pl.si.channels_m1 + 1) < (1ull << 40)) {
+        FastArgs fa;
+        fa.device = device;
+        fa.st = st;
+        fa.d_stream = pl.d_stream;
+        fa.len = len;
+        fa.si = &pl.si;
+        fa.audio_offset = pl.audio_offset;
+        fa.d_cands = (const Cand *)b_cands.p;
+        fa.n_cand = n_cand;
+        fa.wide = pl.wide;
+        fa.container_bytes = container_bytes;
+        fa.aligned_depth = aligned;
+        fa.msb_shift = msb_shift;
+        fa.do_md5 = do_md5;
+        fa.ev = &ev;
+        const int r = fast_path(fa, out, info);
+        if (r != kFastFallback) return r;
+        info->fast_path = 0;
+    }
+
+    // ---- robust path: the host walks the chain like the reference's frame loop
     // ---- K1b: CRC-16 links between neighbouring candidates
     if (b_link.alloc(sizeof(uint32_t) * std::max<uint32_t>(n_cand, 1), st)) return ZFLACB200_CUDA_ERROR;
     pl.cands.resize(n_cand);
@@ -499,11 +695,6 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     std::vector<FrameOut> outs;
     int final_status = ZFLACB200_OK;
     bool decoded_ok = false;
-    {   // a 32 bps stream (side channel: 33 bits) runs on the int64 scratch; bps is latched by the first frame
-        Hdr h0;
-        if (host_parse_header(pl.src, pl.audio_offset, h0) == ZFLACB200_OK)
-            pl.wide = (h0.bd_code == 0 ? depth : kBps[h0.bd_code]) == 32;
-    }
     for (int round = 0; round < 64 && !decoded_ok; ++round) {
         if (round == 63) pl.use_links = false;  // give up on links: probe everything (always consistent)
         {
@@ -558,9 +749,6 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     if (b_pcm.alloc(pcm_bytes + 64, st)) return ZFLACB200_CUDA_ERROR;
 
     // ---- K3: decorrelate + shift + interleave
-    uint32_t msb_shift = 0;  // :287-306, keyed on the STREAMINFO depth
-    if (depth >= 9 && depth <= 15) msb_shift = 16 - depth;
-    else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
     DevBuf b_flag, b_jobs, b_digest;
     if (b_flag.alloc(sizeof(uint32_t), st) || b_jobs.alloc(sizeof(Md5Job), st) || b_digest.alloc(16, st)) return ZFLACB200_CUDA_ERROR;
     CU_CHECK(cudaMemsetAsync(b_flag.p, 0, sizeof(uint32_t), st));
@@ -578,7 +766,6 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     CU_CHECK(cudaEventRecord(ev.e[6], st));
 
     // ---- K4: MD5 gate
-    const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0;
     uint32_t lossy = 0;
     if (do_md5) {
         if (msb_shift) {
@@ -695,6 +882,9 @@ void zflacb200_shutdown(void) {
         if (g_ctx[d].ready) {
             cudaSetDevice(d);
             cudaStreamDestroy(g_ctx[d].stream);
+            cudaStreamDestroy(g_ctx[d].side);
+            cudaEventDestroy(g_ctx[d].ev_fork);
+            cudaEventDestroy(g_ctx[d].ev_join);
             g_ctx[d] = DeviceCtx();
         }
 }
@@ -755,6 +945,9 @@ void zflacb200_close(zflacb200_stream *s) {
     std::lock_guard<std::mutex> lock(g_mutex);
     cudaSetDevice(s->device);
     if (s->d_pcm) cudaFreeAsync(s->d_pcm, g_ctx[s->device].stream);
+    if (s->d_recs) cudaFreeAsync(s->d_recs, g_ctx[s->device].stream);
+    if (s->d_outs) cudaFreeAsync(s->d_outs, g_ctx[s->device].stream);
+    if (s->d_frame_ok) cudaFreeAsync(s->d_frame_ok, g_ctx[s->device].stream);
     delete s;
 }
 
@@ -782,6 +975,31 @@ int zflacb200_open_batch(const uint8_t *const *datas, const size_t *lens, size_t
 
 int zflacb200_frames(zflacb200_stream *s, zflacb200_frame *dst, size_t capacity, size_t *n_frames) {
     if (!s || !n_frames) return ZFLACB200_INVALID_ARGUMENT;
+    if (s->frames_on_device) {  // fast path: build the table from the device records on first use
+        std::lock_guard<std::mutex> lock(g_mutex);
+        CU_CHECK(cudaSetDevice(s->device));
+        std::vector<FrameRec> recs(s->n_recs);
+        std::vector<FrameOut> outs(s->n_recs);
+        std::vector<uint8_t> ok(s->n_recs);
+        CU_CHECK(cudaMemcpy(recs.data(), s->d_recs, sizeof(FrameRec) * s->n_recs, cudaMemcpyDeviceToHost));
+        CU_CHECK(cudaMemcpy(outs.data(), s->d_outs, sizeof(FrameOut) * s->n_recs, cudaMemcpyDeviceToHost));
+        CU_CHECK(cudaMemcpy(ok.data(), s->d_frame_ok, s->n_recs, cudaMemcpyDeviceToHost));
+        s->frames.clear();
+        for (uint32_t i = 0; i < s->n_recs; ++i) {
+            if (recs[i].block_size == 0) continue;
+            zflacb200_frame f;
+            f.offset = recs[i].offset;
+            f.end_offset = outs[i].end_offset;
+            f.sample_offset = recs[i].sample_base;
+            f.block_size = recs[i].block_size;
+            f.header_len = recs[i].header_len;
+            f.channel_code = recs[i].ch_code;
+            f.crc16_ok = ok[i];
+            f.probed = 0;
+            s->frames.push_back(f);
+        }
+        s->frames_on_device = false;
+    }
     *n_frames = s->frames.size();
     if (dst) memcpy(dst, s->frames.data(), sizeof(zflacb200_frame) * std::min(capacity, s->frames.size()));
     return ZFLACB200_OK;

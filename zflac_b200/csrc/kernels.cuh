@@ -20,6 +20,16 @@ cudaError_t launch_frame_link(const uint8_t *d_stream, uint64_t len, const Cand 
 cudaError_t launch_crc16_ranges(const uint8_t *d_stream, const uint64_t *d_begin, const uint64_t *d_end, uint32_t n,
                                 uint16_t *d_crc, cudaStream_t st);
 
+cudaError_t launch_crc16_frames(const uint8_t *d_stream, const FrameRec *d_recs, const FrameOut *d_outs, uint32_t n,
+                                StreamSummary *d_sums, uint8_t *d_frame_ok, cudaStream_t st);
+
+// chain.cu
+cudaError_t launch_hint_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
+                              FrameRec *d_recs, uint32_t window, cudaStream_t st);
+cudaError_t launch_verify_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
+                                const FrameRec *d_recs, const FrameOut *d_outs, StreamSummary *d_sums, uint32_t window,
+                                cudaStream_t st);
+
 // decode.cu
 cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, void *d_scratch,
                                  bool wide_scratch, FrameOut *d_outs, bool write_samples, cudaStream_t st);

@@ -42,6 +42,9 @@ __device__ bool parse_header_at(const uint8_t *__restrict__ s, uint64_t p, uint6
     const uint32_t ones = __clz((int)((~c0 & 0xFFu) << 24 | 0x00800000u));  // leading ones of c0 (0..8)
     if (c0 == 0xFF || ones == 1) return false;
     int n = 4 + (ones == 0 ? 1 : (int)ones);
+    // value of the UTF-8-like number (:203-214 checks the lead byte only; continuation bytes are taken as they are)
+    uint64_t number = ones == 0 ? c0 : (c0 & (0x7Fu >> ones));
+    for (int i = 5; i < n; ++i) number = (number << 6) | (b[i] & 0x3Fu);
     uint32_t block_size;
     if (bs_code == 6) {
         block_size = (uint32_t)b[n] + 1;
@@ -80,7 +83,9 @@ __device__ bool parse_header_at(const uint8_t *__restrict__ s, uint64_t p, uint6
     c.ch_code = (uint8_t)ch_code;
     c.bd_code = (uint8_t)bd_code;
     c.sr_code = (uint8_t)sr_code;
-    c.pad = 0;
+    c.number = number;
+    c.strategy = (uint8_t)(b[1] & 1u);
+    c.pad[0] = c.pad[1] = c.pad[2] = 0;
     return true;
 }
 
@@ -376,6 +381,27 @@ k_crc16_ranges(const uint8_t *__restrict__ s, const uint64_t *__restrict__ begin
     if ((threadIdx.x & 31) == 0) crc_out[k] = (uint16_t)st;
 }
 
+// CRC-16 of every decoded frame of a launch against the value K2 read at its end (:548-551; the
+// reference reads it and moves on, Q1 — here it is counted per stream as a diagnostic).
+__global__ void __launch_bounds__(kLinkThreads)
+k_crc16_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ recs, const FrameOut *__restrict__ outs, uint32_t n,
+               StreamSummary *__restrict__ sums, uint8_t *__restrict__ frame_ok) {
+    __shared__ CrcTables tab;
+    build_crc_tables(tab);
+    const uint32_t k = blockIdx.x * (kLinkThreads / 32) + (threadIdx.x >> 5);
+    if (k >= n) return;
+    const FrameRec fr = recs[k];
+    if (fr.block_size == 0) return;
+    const FrameOut o = outs[k];
+    if (o.status != ST_OK || o.end_offset < fr.offset + 2) return;
+    const uint32_t st = warp_crc16(tab, s, fr.offset, o.end_offset - 2);
+    if ((threadIdx.x & 31) == 0) {
+        const bool ok = st == (o.stored_crc16 & 0xFFFFu);
+        if (frame_ok) frame_ok[k] = ok ? 1 : 0;
+        if (!ok) atomicAdd(&sums[fr.stream_id].n_crc16_mismatch, 1u);
+    }
+}
+
 // ------------------------------------------------------------------ host launchers
 static uint32_t host_pow_x(uint64_t bits) {  // x^bits mod P
     uint32_t r = 1, base = 2;  // base = x
@@ -438,6 +464,15 @@ cudaError_t launch_crc16_ranges(const uint8_t *d_stream, const uint64_t *d_begin
     const uint32_t per_block = kLinkThreads / 32;
     ZF_COUNT_LAUNCH();
     k_crc16_ranges<<<(n + per_block - 1) / per_block, kLinkThreads, 0, st>>>(d_stream, d_begin, d_end, n, d_crc);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_crc16_frames(const uint8_t *d_stream, const FrameRec *d_recs, const FrameOut *d_outs, uint32_t n,
+                                StreamSummary *d_sums, uint8_t *d_frame_ok, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const uint32_t per_block = kLinkThreads / 32;
+    ZF_COUNT_LAUNCH();
+    k_crc16_frames<<<(n + per_block - 1) / per_block, kLinkThreads, 0, st>>>(d_stream, d_recs, d_outs, n, d_sums, d_frame_ok);
     return cudaGetLastError();
 }
 
