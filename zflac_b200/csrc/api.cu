@@ -413,93 +413,104 @@ struct DevBuf {  // stream-ordered allocation released on scope exit
 
 constexpr int kFastFallback = -1;  // not an error: the hinted chain was not accepted, walk it on the host
 
-struct FastArgs {
-    int device;
-    cudaStream_t st;
-    const uint8_t *d_stream;
-    uint64_t len;
-    const Streaminfo *si;
-    uint64_t audio_offset;
-    const Cand *d_cands;
-    uint32_t n_cand;
-    bool wide;
-    uint32_t container_bytes, aligned_depth, msb_shift;
-    bool do_md5;
-    Events *ev;
+// One launch group of the fast path: streams that share the scratch element type (wide), the
+// container type and the MSB-align shift, packed in one device buffer.
+struct FastGroup {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    const uint8_t *d_blob = nullptr;
+    uint64_t blob_len = 0;
+    const Cand *d_cands = nullptr;
+    uint32_t n_cand = 0;
+    bool wide = false;
+    uint32_t container_bytes = 2, msb_shift = 0, max_block = 4096;
+    bool do_md5 = true;
+    std::vector<StreamDesc> streams;      // pcm_base / scratch_base filled by plan()
+    std::vector<uint32_t> hash_bytes;     // per stream: bytes of each sample that enter the MD5 (Q4)
+    uint64_t pcm_elems = 0, scratch_elems = 0;
+    // results
+    std::vector<StreamSummary> sums;
+    std::vector<uint8_t> digests;         // 16 bytes per stream
+    DevBuf b_pcm, b_recs, b_outs, b_ok;
+    float ms_hint = 0, ms_decode = 0, ms_epilogue = 0, ms_md5 = 0;
+
+    void plan() {  // output and scratch slots from the STREAMINFO totals (host-known)
+        pcm_elems = scratch_elems = 0;
+        for (auto &sd : streams) {
+            const uint64_t C = sd.si_channels;
+            sd.pcm_base = pcm_elems;
+            sd.scratch_base = scratch_elems;
+            pcm_elems += (sd.total * C + 15) & ~15ull;  // 16-element slots keep the vector stores aligned
+            scratch_elems += C * (((sd.total + 7) & ~7ull) + 8);
+        }
+        scratch_elems += 64ull * n_cand + 64;
+    }
+    bool accepted(size_t i) const {
+        const StreamSummary &m = sums[i];
+        const StreamDesc &sd = streams[i];
+        return !m.fail && m.first_ok && m.n_samples == sd.total * sd.si_channels && m.channels == sd.si_channels;
+    }
 };
 
 // Fast path: hinted frame records for every candidate -> K2 over all of them -> K3,
-// with the chain rules verified on the device from the decoded frame ends and the per-frame CRC-16
-// on a side stream. One host synchronisation at the very end. Returns ZFLACB200_OK with *out set,
-// kFastFallback when the stream needs the robust host-walked chain, or a CUDA-level error.
-int fast_path(const FastArgs &a, zflacb200_stream **out, zflacb200_info *info) {
-    cudaStream_t st = a.st;
-    DeviceCtx &ctx = g_ctx[a.device];
-    const uint32_t n = a.n_cand;
-    const uint32_t C = a.si->channels_m1 + 1;
-    const uint64_t total = a.si->total;
-    const uint64_t n_samples = total * C;
-    const uint64_t pcm_bytes = n_samples * a.container_bytes;
-    const uint64_t scratch_elems = (uint64_t)C * (((total + 7) & ~7ull) + 8) + 64ull * n + 64;
+// the chain rules verified on the device from the decoded frame ends, the per-frame CRC-16 on a side
+// stream, K4 per stream. One host synchronisation at the very end (two when an MSB-aligned stream
+// is hashed). Returns a CUDA-level status; per-stream acceptance is g.accepted(i).
+int run_fast_group(FastGroup &g, Events &ev) {
+    cudaStream_t st = g.st;
+    DeviceCtx &ctx = g_ctx[g.device];
+    const uint32_t n = g.n_cand;
+    const uint32_t ns = (uint32_t)g.streams.size();
     const uint32_t window = 16;
+    g.plan();
 
-    StreamDesc sd;
-    memset(&sd, 0, sizeof(sd));
-    sd.begin = 0;
-    sd.end = a.len;
-    sd.audio_begin = a.audio_offset;
-    sd.total = total;
-    sd.pcm_base = 0;
-    sd.scratch_base = 0;
-    sd.si_sample_rate = a.si->sample_rate;
-    sd.si_channels = (uint8_t)C;
-    sd.si_depth = (uint8_t)(a.si->depth_m1 + 1);
-
-    DevBuf b_sd, b_recs, b_outs, b_scratch, b_pcm, b_sum, b_ok, b_flag, b_jobs, b_digest;
-    if (b_sd.alloc(sizeof(sd), st) || b_recs.alloc(sizeof(FrameRec) * (size_t)n, st) || b_outs.alloc(sizeof(FrameOut) * (size_t)n, st) ||
-        b_scratch.alloc(scratch_elems * (a.wide ? 8 : 4), st) || b_pcm.alloc(pcm_bytes + 64, st) ||
-        b_sum.alloc(sizeof(StreamSummary), st) || b_ok.alloc(n, st) || b_flag.alloc(sizeof(uint32_t), st) ||
-        b_jobs.alloc(sizeof(Md5Job), st) || b_digest.alloc(16, st))
+    DevBuf b_sd, b_scratch, b_sum, b_flag, b_jobs, b_digest;
+    if (b_sd.alloc(sizeof(StreamDesc) * ns, st) || g.b_recs.alloc(sizeof(FrameRec) * (size_t)n, st) ||
+        g.b_outs.alloc(sizeof(FrameOut) * (size_t)n, st) || b_scratch.alloc(g.scratch_elems * (g.wide ? 8 : 4), st) ||
+        g.b_pcm.alloc(g.pcm_elems * g.container_bytes + 64, st) || b_sum.alloc(sizeof(StreamSummary) * ns, st) ||
+        g.b_ok.alloc(n, st) || b_flag.alloc(sizeof(uint32_t), st) || b_jobs.alloc(sizeof(Md5Job) * ns, st) ||
+        b_digest.alloc(16 * (size_t)ns, st))
         return ZFLACB200_CUDA_ERROR;
-    CU_CHECK(cudaMemcpyAsync(b_sd.p, &sd, sizeof(sd), cudaMemcpyHostToDevice, st));
-    CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary), st));
-    CU_CHECK(cudaMemsetAsync(b_ok.p, 2, n, st));  // 2 = not checked
+    CU_CHECK(cudaMemcpyAsync(b_sd.p, g.streams.data(), sizeof(StreamDesc) * ns, cudaMemcpyHostToDevice, st));
+    CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary) * ns, st));
+    CU_CHECK(cudaMemsetAsync(g.b_ok.p, 2, n, st));  // 2 = not checked
     CU_CHECK(cudaMemsetAsync(b_flag.p, 0, sizeof(uint32_t), st));
-    CU_CHECK(cudaMemsetAsync(b_outs.p, 0xFF, sizeof(FrameOut) * (size_t)n, st));  // dropped slots: status != OK
+    CU_CHECK(cudaMemsetAsync(g.b_outs.p, 0xFF, sizeof(FrameOut) * (size_t)n, st));  // dropped slots: status != OK
+    const StreamDesc *d_sd = (const StreamDesc *)b_sd.p;
+    FrameRec *d_recs = (FrameRec *)g.b_recs.p;
+    FrameOut *d_outs = (FrameOut *)g.b_outs.p;
+    StreamSummary *d_sum = (StreamSummary *)b_sum.p;
 
-    CU_CHECK(launch_hint_chain(a.d_cands, n, (const StreamDesc *)b_sd.p, 1, (FrameRec *)b_recs.p, window, st));
-    CU_CHECK(cudaEventRecord(a.ev->e[3], st));
-    CU_CHECK(cudaEventRecord(a.ev->e[4], st));
-    CU_CHECK(launch_decode_frames(a.d_stream, (const FrameRec *)b_recs.p, n, b_scratch.p, a.wide, (FrameOut *)b_outs.p, true, st));
-    CU_CHECK(cudaEventRecord(a.ev->e[5], st));
+    CU_CHECK(launch_hint_chain(g.d_cands, n, d_sd, ns, d_recs, window, st));
+    CU_CHECK(cudaEventRecord(ev.e[3], st));
+    CU_CHECK(cudaEventRecord(ev.e[4], st));
+    CU_CHECK(launch_decode_frames(g.d_blob, d_recs, n, b_scratch.p, g.wide, d_outs, true, st));
+    CU_CHECK(cudaEventRecord(ev.e[5], st));
 
     // side stream: CRC-16 of every decoded frame, overlapping K3 (+K4)
     CU_CHECK(cudaEventRecord(ctx.ev_fork, st));
     CU_CHECK(cudaStreamWaitEvent(ctx.side, ctx.ev_fork, 0));
-    CU_CHECK(launch_crc16_frames(a.d_stream, (const FrameRec *)b_recs.p, (const FrameOut *)b_outs.p, n, (StreamSummary *)b_sum.p,
-                                 (uint8_t *)b_ok.p, ctx.side));
+    CU_CHECK(launch_crc16_frames(g.d_blob, d_recs, d_outs, n, d_sum, (uint8_t *)g.b_ok.p, ctx.side));
     CU_CHECK(cudaEventRecord(ctx.ev_join, ctx.side));
 
-    CU_CHECK(launch_verify_chain(a.d_cands, n, (const StreamDesc *)b_sd.p, 1, (const FrameRec *)b_recs.p, (const FrameOut *)b_outs.p,
-                                 (StreamSummary *)b_sum.p, window, st));
+    CU_CHECK(launch_verify_chain(g.d_cands, n, d_sd, ns, d_recs, d_outs, d_sum, window, st));
     EpilogueParams ep;
-    ep.frames = (const FrameRec *)b_recs.p;
+    ep.frames = d_recs;
     ep.n_frames = n;
-    // records are per candidate, block sizes are only known on the device: size the grid from STREAMINFO (any value is correct)
-    ep.max_block_size = a.si->max_block >= 16 ? a.si->max_block : 4096;
+    ep.max_block_size = g.max_block;  // sizes the grid only (block sizes are known on the device); any value is correct
     ep.scratch = b_scratch.p;
-    ep.wide_scratch = a.wide;
-    ep.pcm = b_pcm.p;
-    ep.container_bytes = a.container_bytes;
-    ep.msb_shift = a.msb_shift;
+    ep.wide_scratch = g.wide;
+    ep.pcm = g.b_pcm.p;
+    ep.container_bytes = g.container_bytes;
+    ep.msb_shift = g.msb_shift;
     ep.lossy_flag = (uint32_t *)b_flag.p;
     CU_CHECK(launch_epilogue(ep, st));
-    CU_CHECK(cudaEventRecord(a.ev->e[6], st));
+    CU_CHECK(cudaEventRecord(ev.e[6], st));
 
-    StreamSummary sum;
-    uint32_t lossy = 0;
-    if (a.do_md5) {
-        if (a.msb_shift) {  // a sample wider than the STREAMINFO depth loses bits in the shift (Q5): hash before shifting
+    g.digests.assign(16 * (size_t)ns, 0);
+    if (g.do_md5) {
+        uint32_t lossy = 0;
+        if (g.msb_shift) {  // a sample wider than the STREAMINFO depth loses bits in the shift (Q5): hash before shifting
             CU_CHECK(cudaMemcpyAsync(&lossy, b_flag.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
             CU_CHECK(cudaStreamSynchronize(st));
             if (lossy) {
@@ -507,57 +518,31 @@ int fast_path(const FastArgs &a, zflacb200_stream **out, zflacb200_info *info) {
                 CU_CHECK(launch_epilogue(ep, st));
             }
         }
-        Md5Job job;
-        job.pcm = b_pcm.p;
-        job.n_samples = n_samples;
-        job.container_bytes = a.container_bytes;
-        job.hash_bytes = a.aligned_depth == 24 ? 3 : a.container_bytes;  // :268-277
-        job.unshift = lossy ? 0 : a.msb_shift;
-        job.pad = 0;
-        CU_CHECK(cudaMemcpyAsync(b_jobs.p, &job, sizeof(job), cudaMemcpyHostToDevice, st));
-        CU_CHECK(launch_md5((const Md5Job *)b_jobs.p, 1, (uint8_t *)b_digest.p, st));
-        if (lossy) CU_CHECK(launch_shift_inplace(b_pcm.p, n_samples, a.container_bytes, a.msb_shift, st));
-        CU_CHECK(cudaMemcpyAsync(info->md5_computed, b_digest.p, 16, cudaMemcpyDeviceToHost, st));
+        std::vector<Md5Job> jobs(ns);
+        for (uint32_t i = 0; i < ns; ++i) {
+            const StreamDesc &sd = g.streams[i];
+            jobs[i].pcm = (const uint8_t *)g.b_pcm.p + sd.pcm_base * g.container_bytes;
+            jobs[i].n_samples = sd.total * sd.si_channels;
+            jobs[i].container_bytes = g.container_bytes;
+            jobs[i].hash_bytes = g.hash_bytes[i];
+            jobs[i].unshift = lossy ? 0 : g.msb_shift;
+            jobs[i].pad = 0;
+        }
+        CU_CHECK(cudaMemcpyAsync(b_jobs.p, jobs.data(), sizeof(Md5Job) * ns, cudaMemcpyHostToDevice, st));
+        CU_CHECK(cudaStreamSynchronize(st));  // `jobs` is a pageable temporary
+        CU_CHECK(launch_md5((const Md5Job *)b_jobs.p, ns, (uint8_t *)b_digest.p, st));
+        if (lossy) CU_CHECK(launch_shift_inplace(g.b_pcm.p, g.pcm_elems, g.container_bytes, g.msb_shift, st));
+        CU_CHECK(cudaMemcpyAsync(g.digests.data(), b_digest.p, 16 * (size_t)ns, cudaMemcpyDeviceToHost, st));
     }
-    CU_CHECK(cudaEventRecord(a.ev->e[7], st));
+    CU_CHECK(cudaEventRecord(ev.e[7], st));
     CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));
-    CU_CHECK(cudaMemcpyAsync(&sum, b_sum.p, sizeof(sum), cudaMemcpyDeviceToHost, st));
+    g.sums.resize(ns);
+    CU_CHECK(cudaMemcpyAsync(g.sums.data(), b_sum.p, sizeof(StreamSummary) * ns, cudaMemcpyDeviceToHost, st));
     CU_CHECK(cudaStreamSynchronize(st));
-
-    if (sum.fail || !sum.first_ok || sum.n_samples != n_samples || sum.channels != C) return kFastFallback;
-
-    info->ms_scan = ev_ms(a.ev->e[1], a.ev->e[2]);
-    info->ms_link = ev_ms(a.ev->e[2], a.ev->e[3]);
-    info->ms_decode = ev_ms(a.ev->e[4], a.ev->e[5]);
-    info->ms_epilogue = ev_ms(a.ev->e[5], a.ev->e[6]);
-    info->ms_md5 = ev_ms(a.ev->e[6], a.ev->e[7]);
-    info->ms_total = ev_ms(a.ev->e[0], a.ev->e[7]);
-    info->md5_checked = a.do_md5 ? 1 : 0;
-    if (a.do_md5 && memcmp(info->md5_computed, a.si->md5, 16) != 0) return ZFLACB200_INVALID_CHECKSUM;  // :279-280
-
-    info->channels = sum.channels;
-    info->bits_per_sample = sum.bps;
-    info->sample_rate = sum.sample_rate;
-    info->n_samples = n_samples;
-    info->pcm_bytes = pcm_bytes;
-    info->n_frames = sum.n_frames;
-    info->n_candidates = n;
-    info->n_probed_frames = 0;
-    info->fast_path = 1;
-    info->n_crc16_mismatch = sum.n_crc16_mismatch;
-    info->audio_bytes = sum.end_offset - a.audio_offset;
-
-    zflacb200_stream *h = new zflacb200_stream();
-    h->device = a.device;
-    h->pcm_bytes = pcm_bytes;
-    h->d_pcm = b_pcm.release();
-    h->d_recs = (FrameRec *)b_recs.release();
-    h->d_outs = (FrameOut *)b_outs.release();
-    h->d_frame_ok = (uint8_t *)b_ok.release();
-    h->n_recs = n;
-    h->frames_on_device = true;
-    h->info = *info;
-    *out = h;
+    g.ms_hint = ev_ms(ev.e[2], ev.e[3]);
+    g.ms_decode = ev_ms(ev.e[4], ev.e[5]);
+    g.ms_epilogue = ev_ms(ev.e[5], ev.e[6]);
+    g.ms_md5 = ev_ms(ev.e[6], ev.e[7]);
     return ZFLACB200_OK;
 }
 
@@ -653,23 +638,67 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     // ---- fast path: device-side hinted chain, verified after decoding (no host walk, no CRC-16 pre-pass)
     if (n_cand > 0 && pl.si.total > 0 && (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0 &&
         pl.si.total * (pl.si.channels_m1 + 1) < (1ull << 40)) {
-        FastArgs fa;
-        fa.device = device;
-        fa.st = st;
-        fa.d_stream = pl.d_stream;
-        fa.len = len;
-        fa.si = &pl.si;
-        fa.audio_offset = pl.audio_offset;
-        fa.d_cands = (const Cand *)b_cands.p;
-        fa.n_cand = n_cand;
-        fa.wide = pl.wide;
-        fa.container_bytes = container_bytes;
-        fa.aligned_depth = aligned;
-        fa.msb_shift = msb_shift;
-        fa.do_md5 = do_md5;
-        fa.ev = &ev;
-        const int r = fast_path(fa, out, info);
-        if (r != kFastFallback) return r;
+        FastGroup g;
+        g.device = device;
+        g.st = st;
+        g.d_blob = pl.d_stream;
+        g.blob_len = len;
+        g.d_cands = (const Cand *)b_cands.p;
+        g.n_cand = n_cand;
+        g.wide = pl.wide;
+        g.container_bytes = container_bytes;
+        g.msb_shift = msb_shift;
+        g.max_block = pl.si.max_block >= 16 ? pl.si.max_block : 4096;
+        g.do_md5 = do_md5;
+        StreamDesc sd;
+        memset(&sd, 0, sizeof(sd));
+        sd.begin = 0;
+        sd.end = len;
+        sd.audio_begin = pl.audio_offset;
+        sd.total = pl.si.total;
+        sd.si_sample_rate = pl.si.sample_rate;
+        sd.si_channels = (uint8_t)(pl.si.channels_m1 + 1);
+        sd.si_depth = (uint8_t)depth;
+        g.streams.push_back(sd);
+        g.hash_bytes.push_back(aligned == 24 ? 3 : container_bytes);  // :268-277
+        {
+            const int r = run_fast_group(g, ev);
+            if (r != ZFLACB200_OK) return r;
+        }
+        if (g.accepted(0)) {
+            const StreamSummary &sum = g.sums[0];
+            info->ms_scan = ev_ms(ev.e[1], ev.e[2]);
+            info->ms_link = g.ms_hint;
+            info->ms_decode = g.ms_decode;
+            info->ms_epilogue = g.ms_epilogue;
+            info->ms_md5 = g.ms_md5;
+            info->ms_total = ev_ms(ev.e[0], ev.e[7]);
+            info->md5_checked = do_md5 ? 1 : 0;
+            memcpy(info->md5_computed, g.digests.data(), 16);
+            if (do_md5 && memcmp(info->md5_computed, pl.si.md5, 16) != 0) return ZFLACB200_INVALID_CHECKSUM;  // :279-280
+            info->channels = sum.channels;
+            info->bits_per_sample = sum.bps;
+            info->sample_rate = sum.sample_rate;
+            info->n_samples = sum.n_samples;
+            info->pcm_bytes = sum.n_samples * container_bytes;
+            info->n_frames = sum.n_frames;
+            info->n_probed_frames = 0;
+            info->fast_path = 1;
+            info->n_crc16_mismatch = sum.n_crc16_mismatch;
+            info->audio_bytes = sum.end_offset - pl.audio_offset;
+            zflacb200_stream *h = new zflacb200_stream();
+            h->device = device;
+            h->pcm_bytes = info->pcm_bytes;
+            h->d_pcm = g.b_pcm.release();
+            h->d_recs = (FrameRec *)g.b_recs.release();
+            h->d_outs = (FrameOut *)g.b_outs.release();
+            h->d_frame_ok = (uint8_t *)g.b_ok.release();
+            h->n_recs = n_cand;
+            h->frames_on_device = true;
+            h->info = *info;
+            *out = h;
+            return ZFLACB200_OK;
+        }
         info->fast_path = 0;
     }
 

@@ -29,7 +29,7 @@ __constant__ uint32_t c_rate_table[16] = {0, 88200, 176400, 192000, 8000, 16000,
 
 // Full header check at byte position p. Returns true and fills `c` when the bytes at p are a
 // frame header the reference would accept (grammar) AND the CRC-8 matches.
-__device__ bool parse_header_at(const uint8_t *__restrict__ s, uint64_t p, uint64_t len, Cand &c) {
+__device__ __noinline__ bool parse_header_at(const uint8_t *__restrict__ s, uint64_t p, uint64_t len, Cand &c) {
     if (p + 6 > len) return false;
     uint8_t b[16];
     const int avail = (len - p) < 16 ? (int)(len - p) : 16;
@@ -107,7 +107,7 @@ __device__ __forceinline__ uint32_t sync_mask4(uint32_t cur, uint32_t nxt) {
     return ((m & 0x01010101u) * 0x01020408u) >> 24;  // 4-bit mask, bit i <-> byte i
 }
 
-__global__ void __launch_bounds__(kScanThreads)
+__global__ void __launch_bounds__(kScanThreads, 6)
 k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t len, uint64_t tile0, uint32_t n_tiles,
             Cand *__restrict__ out, uint32_t cap, uint32_t *__restrict__ total_out,
             unsigned long long *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
