@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define ZFLACB200_ABI_VERSION 1
+#define ZFLACB200_ABI_VERSION 2
 
 /* One value per Zig error name decode() can return; the shim maps
  * them 1:1 onto the Zig error set. */
@@ -132,12 +132,29 @@ void zflacb200_close(zflacb200_stream *s);
 int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *opt,
                      void *dst, size_t dst_capacity, zflacb200_info *info);
 
-/* File-parallel batch (BASELINE config 5): n independent streams decoded in one
- * pipeline pass on one device. statuses[i]/infos[i]/outs[i] are per stream. Returns
- * ZFLACB200_OK if the batch ran (individual streams may still carry errors). */
-int zflacb200_open_batch(const uint8_t *const *datas, const size_t *lens, size_t n,
-                         const zflacb200_options *opt, zflacb200_stream **outs,
-                         zflacb200_info *infos, int *statuses);
+/* File-parallel batch (BASELINE config 5): n independent streams decoded in ONE pipeline pass
+ * on one device — one sync scan over the packed bytes, one K2 / K3 launch over the frames of all
+ * streams, one MD5 chain per stream running side by side. Each stream is what one call of the
+ * reference's decode() (src/zflac.zig:217) would get; statuses[i] / infos[i] are what that call
+ * would return. `blob` holds the streams back to back (any gaps allowed): stream i is
+ * blob[offsets[i] .. offsets[i] + lens[i]). `blob` is host memory (pinned memory makes the upload
+ * run at full PCIe speed); `device_blob`, if not NULL, is a device copy of the same bytes and
+ * skips the upload (bench: inputs resident in HBM). Streams the device-side chain cannot take
+ * (no stated total, inconsistent numbering, damage, every error case) are decoded one by one
+ * through the same path as zflacb200_open(). Returns ZFLACB200_OK if the batch ran. */
+typedef struct zflacb200_batch zflacb200_batch;
+int zflacb200_batch_open(const uint8_t *blob, const uint8_t *device_blob, const uint64_t *offsets,
+                         const uint64_t *lens, size_t n, const zflacb200_options *opt,
+                         zflacb200_batch **out, zflacb200_info *infos, int *statuses);
+/* Bytes zflacb200_batch_read_all() writes: the PCM of all streams that decoded, 64-byte aligned each. */
+int zflacb200_batch_pcm_bytes(zflacb200_batch *b, uint64_t *bytes);
+/* Copies every decoded stream's PCM into `dst` (host) with a few large device-to-host copies;
+ * pcm_offsets[i] receives the byte offset of stream i inside dst (UINT64_MAX if it did not decode). */
+int zflacb200_batch_read_all(zflacb200_batch *b, void *dst, size_t dst_bytes, uint64_t *pcm_offsets);
+/* One stream's PCM (host destination) / its device pointer (valid until close). */
+int zflacb200_batch_read_stream(zflacb200_batch *b, size_t i, void *dst, size_t dst_bytes);
+int zflacb200_batch_device_pcm(zflacb200_batch *b, size_t i, void **dev_ptr, size_t *bytes);
+void zflacb200_batch_close(zflacb200_batch *b);
 
 /* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
 typedef struct zflacb200_frame {

@@ -17,7 +17,7 @@ def declared_symbols():
 
 def test_header_declares_the_expected_entry_points():
     syms = declared_symbols()
-    for s in ("zflacb200_open", "zflacb200_read", "zflacb200_close", "zflacb200_decode", "zflacb200_open_batch"):
+    for s in ("zflacb200_open", "zflacb200_read", "zflacb200_close", "zflacb200_decode", "zflacb200_batch_open", "zflacb200_batch_read_all", "zflacb200_batch_close"):
         assert s in syms
 
 
@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for s in declared_symbols():
         assert hasattr(lib, s), f"{s} declared in include/zflacb200.h but not exported"
     assert sorted(_native.EXPORTS) == declared_symbols()
-    assert lib.zflacb200_abi_version() == 1
+    assert lib.zflacb200_abi_version() == 2
 
 
 def test_status_names_match_zig_error_names():

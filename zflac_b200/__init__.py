@@ -23,7 +23,8 @@ import numpy as np
 from . import _native
 from ._native import INPUT_ON_DEVICE, NO_CRC_ACCEL, NO_FAST_PATH, SKIP_MD5, VERIFY_MD5  # noqa: F401
 
-__all__ = ["decode", "decode_into", "DecodedFLAC", "ZflacError", "CudaError", "open_device", "DeviceStream"]
+__all__ = ["decode", "decode_into", "decode_batch", "open_batch", "DeviceBatch", "pack_streams", "DecodedFLAC", "ZflacError",
+           "CudaError", "open_device", "DeviceStream"]
 
 
 class ZflacError(Exception):
@@ -191,3 +192,119 @@ def open_device(dev_ptr: int, nbytes: int, *, device: int = -1, stream: int | No
     if st != 0:
         _raise(st)
     return DeviceStream(handle, info)
+
+
+# --------------------------------------------------------------------------------------------------
+# File-parallel batch (BASELINE config 5): many independent streams, one pipeline pass per device.
+# --------------------------------------------------------------------------------------------------
+def pack_streams(streams, align: int = 16):
+    """Packs byte strings / uint8 arrays back to back (each start `align`-byte aligned) into one blob.
+    Returns (blob uint8 ndarray, offsets uint64 ndarray, lens uint64 ndarray)."""
+    arrs = [_as_u8(x) for x in streams]
+    lens = np.array([a.size for a in arrs], dtype=np.uint64)
+    padded = (lens + np.uint64(align - 1)) // np.uint64(align) * np.uint64(align)
+    offsets = np.zeros(len(arrs), dtype=np.uint64)
+    if len(arrs) > 1:
+        offsets[1:] = np.cumsum(padded[:-1])
+    blob = np.zeros(int(padded.sum()) if len(arrs) else 0, dtype=np.uint8)
+    for a, o in zip(arrs, offsets):
+        blob[int(o):int(o) + a.size] = a
+    return blob, offsets, lens
+
+
+class DeviceBatch:
+    """Result of zflacb200_batch_open: per-stream statuses / infos, PCM resident in HBM."""
+
+    def __init__(self, handle, infos, statuses, n):
+        self._h = handle
+        self.n = n
+        self.statuses = [int(x) for x in statuses]
+        self.errors = [None if st == 0 else _native.load().zflacb200_status_name(st).decode() for st in self.statuses]
+        self.infos = [_info_dict(infos[i]) for i in range(n)]
+        self._raw_infos = infos
+
+    def pcm_bytes(self) -> int:
+        v = C.c_uint64()
+        _native.load().zflacb200_batch_pcm_bytes(self._h, C.byref(v))
+        return int(v.value)
+
+    def read_all(self, dst: np.ndarray | None = None):
+        """One bulk transfer of every decoded stream's PCM. Returns (uint8 buffer, byte offsets; 2**64-1 = no data)."""
+        if dst is None:
+            dst = np.empty(self.pcm_bytes(), dtype=np.uint8)
+        offs = np.zeros(self.n, dtype=np.uint64)
+        st = _native.load().zflacb200_batch_read_all(self._h, dst.ctypes.data, dst.nbytes, offs.ctypes.data_as(C.POINTER(C.c_uint64)))
+        if st != 0:
+            _raise(st)
+        return dst, offs
+
+    def stream(self, i: int) -> DecodedFLAC:
+        """Stream i as the reference's decode() would have returned it (raises its error otherwise)."""
+        if self.statuses[i] != 0:
+            _raise(self.statuses[i])
+        inf = self._raw_infos[i]
+        out = np.empty(int(inf.n_samples), dtype=_DTYPES[inf.container_bytes])
+        st = _native.load().zflacb200_batch_read_stream(self._h, i, out.ctypes.data, out.nbytes)
+        if st != 0:
+            _raise(st)
+        return DecodedFLAC(inf.channels, inf.sample_rate, inf.bits_per_sample, out, self.infos[i])
+
+    def streams_from(self, buf: np.ndarray, offs: np.ndarray):
+        """Views of the per-stream sample arrays inside a read_all() buffer (None where a stream failed)."""
+        out = []
+        for i in range(self.n):
+            if self.statuses[i] != 0 or int(offs[i]) == 2**64 - 1:
+                out.append(None)
+                continue
+            inf = self._raw_infos[i]
+            o = int(offs[i])
+            out.append(buf[o:o + int(inf.pcm_bytes)].view(_DTYPES[inf.container_bytes]))
+        return out
+
+    def close(self):
+        if self._h:
+            _native.load().zflacb200_batch_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+
+def open_batch(blob, offsets, lens, *, device_blob_ptr: int = 0, device: int = -1, stream: int | None = None,
+               verify_md5: bool = True, use_fast_path: bool = True) -> DeviceBatch:
+    """zflacb200_batch_open over a packed blob (see pack_streams). `device_blob_ptr`: device copy of the blob, if any."""
+    lib = _native.load()
+    blob = _as_u8(blob)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    lens = np.ascontiguousarray(lens, dtype=np.uint64)
+    n = int(offsets.size)
+    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_fast_path else NO_FAST_PATH)
+    opt = _options(flags, device, stream)
+    infos = (_native.Info * max(n, 1))()
+    statuses = (C.c_int * max(n, 1))()
+    handle = C.c_void_p()
+    st = lib.zflacb200_batch_open(blob.ctypes.data, device_blob_ptr or None, offsets.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                  lens.ctypes.data_as(C.POINTER(C.c_uint64)), n, C.byref(opt), C.byref(handle), infos, statuses)
+    if st != 0:
+        _raise(st)
+    return DeviceBatch(handle, infos, statuses, n)
+
+
+def decode_batch(streams, *, device: int = -1, verify_md5: bool = True, use_fast_path: bool = True):
+    """Decodes a list of independent streams in one pipeline pass. Returns a list with, per stream, a DecodedFLAC
+    or the ZflacError instance the reference's decode() would have raised."""
+    blob, offsets, lens = pack_streams(streams)
+    b = open_batch(blob, offsets, lens, device=device, verify_md5=verify_md5, use_fast_path=use_fast_path)
+    try:
+        buf, offs = b.read_all()
+        views = b.streams_from(buf, offs)
+        out = []
+        for i in range(b.n):
+            if b.statuses[i] != 0:
+                out.append(_ERRORS.get(b.statuses[i], ZflacError)(b.errors[i]))
+            else:
+                inf = b._raw_infos[i]
+                out.append(DecodedFLAC(inf.channels, inf.sample_rate, inf.bits_per_sample, views[i].copy(), b.infos[i]))
+        return out
+    finally:
+        b.close()

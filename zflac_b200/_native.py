@@ -18,7 +18,9 @@ NO_FAST_PATH = 0x10
 EXPORTS = [
     "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown",
     "zflacb200_status_name", "zflacb200_last_error", "zflacb200_kernel_launches", "zflacb200_open", "zflacb200_read",
-    "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_open_batch", "zflacb200_frames",
+    "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_frames", "zflacb200_batch_open",
+    "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
+    "zflacb200_batch_close",
 ]
 
 
@@ -74,9 +76,19 @@ def load():
     lib.zflacb200_close.restype = None
     lib.zflacb200_decode.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.c_void_p, C.c_size_t, C.POINTER(Info)]
     lib.zflacb200_decode.restype = C.c_int
-    lib.zflacb200_open_batch.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_size_t, C.POINTER(Options),
-                                         C.POINTER(C.c_void_p), C.POINTER(Info), C.POINTER(C.c_int)]
-    lib.zflacb200_open_batch.restype = C.c_int
+    lib.zflacb200_batch_open.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_size_t,
+                                         C.POINTER(Options), C.POINTER(C.c_void_p), C.POINTER(Info), C.POINTER(C.c_int)]
+    lib.zflacb200_batch_open.restype = C.c_int
+    lib.zflacb200_batch_pcm_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+    lib.zflacb200_batch_pcm_bytes.restype = C.c_int
+    lib.zflacb200_batch_read_all.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]
+    lib.zflacb200_batch_read_all.restype = C.c_int
+    lib.zflacb200_batch_read_stream.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    lib.zflacb200_batch_read_stream.restype = C.c_int
+    lib.zflacb200_batch_device_pcm.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+    lib.zflacb200_batch_device_pcm.restype = C.c_int
+    lib.zflacb200_batch_close.argtypes = [C.c_void_p]
+    lib.zflacb200_batch_close.restype = None
     lib.zflacb200_frames.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_size_t, C.POINTER(C.c_size_t)]
     lib.zflacb200_frames.restype = C.c_int
     _lib = lib

@@ -391,6 +391,19 @@ struct zflacb200_stream {
     bool frames_on_device = false;
 };
 
+struct zflacb200_batch {
+    int device = 0;
+    struct Group { void *d_pcm = nullptr; uint64_t bytes = 0; };
+    struct Item {
+        int group = -1;              // launch group whose PCM buffer holds the stream, -1 = none
+        uint64_t byte_off = 0, bytes = 0;
+        zflacb200_stream *solo = nullptr;  // stream decoded on its own (robust path)
+    };
+    std::vector<Group> groups;
+    std::vector<Item> items;
+    uint64_t read_all_bytes = 0;
+};
+
 namespace {
 
 struct DevBuf {  // stream-ordered allocation released on scope exit
@@ -887,6 +900,229 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     return ZFLACB200_OK;
 }
 
+
+// File-parallel batch: metadata walk per stream on the host, ONE sync scan over the packed bytes,
+// then one fast-path launch group per (scratch type, container, MSB shift) class — usually one.
+int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint64_t *offsets, const uint64_t *lens, size_t n,
+                    const zflacb200_options *opt, zflacb200_batch **out, zflacb200_info *infos, int *statuses) {
+    if (!blob || !offsets || !lens || !out || !infos || !statuses) {
+        g_last_error = "null argument";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    *out = nullptr;
+    const uint32_t flags = opt ? opt->flags : 0;
+    int device = -1;
+    {
+        const int e = ensure_device(opt ? opt->device : -1, &device);
+        if (e != ZFLACB200_OK) return e;
+    }
+    cudaStream_t st = (opt && opt->stream) ? (cudaStream_t)opt->stream : g_ctx[device].stream;
+    const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0;
+
+    struct Item {
+        Streaminfo si;
+        uint64_t audio_offset = 0;  // relative to the stream
+        uint32_t depth = 0, aligned = 0, container = 0, msb_shift = 0;
+        bool wide = false, eligible = false;
+        int group = -1;
+        uint32_t slot = 0;  // index inside the group
+    };
+    std::vector<Item> items(n);
+    uint64_t blob_len = 0, scan_begin = ~0ull;
+    std::vector<uint32_t> keys;  // distinct (wide, container, shift) classes
+    for (size_t i = 0; i < n; ++i) {
+        memset(&infos[i], 0, sizeof(zflacb200_info));
+        blob_len = std::max(blob_len, offsets[i] + lens[i]);
+        Item &it = items[i];
+        ByteSource src;
+        src.host = blob + offsets[i];
+        src.len = lens[i];
+        statuses[i] = parse_metadata(src, it.si, it.audio_offset);
+        if (statuses[i] != ZFLACB200_OK) continue;
+        it.depth = it.si.depth_m1 + 1;
+        it.aligned = (it.depth + 7u) & ~7u;
+        it.container = it.aligned == 8 ? 1 : it.aligned == 16 ? 2 : 4;
+        if (it.depth >= 9 && it.depth <= 15) it.msb_shift = 16 - it.depth;
+        else if (it.depth >= 17 && it.depth <= 31) it.msb_shift = 32 - it.depth;
+        memcpy(infos[i].md5_streaminfo, it.si.md5, 16);
+        infos[i].audio_offset = it.audio_offset;
+        infos[i].container_bytes = (uint8_t)it.container;
+        Hdr h0;
+        if (host_parse_header(src, it.audio_offset, h0) == ZFLACB200_OK)
+            it.wide = (h0.bd_code == 0 ? it.depth : kBps[h0.bd_code]) == 32;
+        it.eligible = it.si.total > 0 && it.si.total * (it.si.channels_m1 + 1) < (1ull << 40) &&
+                      (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0;
+        if (it.eligible) {
+            const uint32_t key = (it.wide ? 1u << 16 : 0u) | (it.container << 8) | it.msb_shift;
+            size_t g = 0;
+            while (g < keys.size() && keys[g] != key) ++g;
+            if (g == keys.size()) keys.push_back(key);
+            it.group = (int)g;
+            scan_begin = std::min(scan_begin, offsets[i] + it.audio_offset);
+        }
+    }
+
+    zflacb200_batch *b = new zflacb200_batch();
+    b->device = device;
+    b->items.resize(n);
+    struct Cleanup {  // on an early CUDA error nothing is returned
+        zflacb200_batch *b;
+        bool armed = true;
+        ~Cleanup() {
+            if (armed) {
+                for (auto &it : b->items)
+                    if (it.solo) { cudaFreeAsync(it.solo->d_pcm, nullptr); delete it.solo; }
+                for (auto &g : b->groups)
+                    if (g.d_pcm) cudaFreeAsync(g.d_pcm, nullptr);
+                delete b;
+            }
+        }
+    } cleanup{b};
+
+    if (!keys.empty()) {
+        Events ev;
+        if (ev.init() != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+        CU_CHECK(cudaEventRecord(ev.e[0], st));
+        DevBuf b_blob;
+        const uint8_t *d_blob = device_blob;
+        if (!d_blob) {
+            if (b_blob.alloc(((blob_len + 15) & ~15ull) + 64, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+            CU_CHECK(cudaMemcpyAsync(b_blob.p, blob, blob_len, cudaMemcpyHostToDevice, st));
+            d_blob = (const uint8_t *)b_blob.p;
+        }
+        // ---- K1 once over the packed bytes
+        CU_CHECK(cudaEventRecord(ev.e[1], st));
+        uint32_t n_cand = 0;
+        DevBuf b_cands, b_total, b_tiles, b_ticket;
+        {
+            const uint32_t n_tiles = scan_tile_count(scan_begin, blob_len);
+            uint32_t cap = (uint32_t)std::min<uint64_t>(blob_len / 256 + 4096 + 4 * n, 0x7FFFFFFFull);
+            if (b_total.alloc(sizeof(uint32_t), st) || b_ticket.alloc(sizeof(uint32_t), st) ||
+                b_tiles.alloc(sizeof(unsigned long long) * std::max<uint32_t>(n_tiles, 1), st))
+                return ZFLACB200_CUDA_ERROR;
+            for (int attempt = 0; attempt < 2; ++attempt) {
+                if (b_cands.p) { cudaFreeAsync(b_cands.p, st); b_cands.p = nullptr; }
+                if (b_cands.alloc(sizeof(Cand) * (size_t)cap, st)) return ZFLACB200_CUDA_ERROR;
+                CU_CHECK(launch_sync_scan(d_blob, scan_begin, blob_len, (Cand *)b_cands.p, cap, (uint32_t *)b_total.p,
+                                          (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
+                CU_CHECK(cudaMemcpyAsync(&n_cand, b_total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                CU_CHECK(cudaStreamSynchronize(st));
+                if (n_cand <= cap) break;
+                cap = n_cand;
+            }
+        }
+        CU_CHECK(cudaEventRecord(ev.e[2], st));
+
+        // ---- one launch group per class
+        for (size_t gi = 0; gi < keys.size() && n_cand > 0; ++gi) {
+            FastGroup g;
+            g.device = device;
+            g.st = st;
+            g.d_blob = d_blob;
+            g.blob_len = blob_len;
+            g.d_cands = (const Cand *)b_cands.p;
+            g.n_cand = n_cand;
+            g.wide = (keys[gi] >> 16) & 1;
+            g.container_bytes = (keys[gi] >> 8) & 0xFF;
+            g.msb_shift = keys[gi] & 0xFF;
+            g.do_md5 = do_md5;
+            g.max_block = 16;
+            std::vector<size_t> members;
+            for (size_t i = 0; i < n; ++i) {  // streams in blob order (the device searches them by offset)
+                if (items[i].group != (int)gi) continue;
+                members.push_back(i);
+            }
+            std::sort(members.begin(), members.end(), [&](size_t x, size_t y) { return offsets[x] < offsets[y]; });
+            for (size_t i : members) {
+                Item &it = items[i];
+                StreamDesc sd;
+                memset(&sd, 0, sizeof(sd));
+                sd.begin = offsets[i];
+                sd.end = offsets[i] + lens[i];
+                sd.audio_begin = offsets[i] + it.audio_offset;
+                sd.total = it.si.total;
+                sd.si_sample_rate = it.si.sample_rate;
+                sd.si_channels = (uint8_t)(it.si.channels_m1 + 1);
+                sd.si_depth = (uint8_t)it.depth;
+                it.slot = (uint32_t)g.streams.size();
+                g.streams.push_back(sd);
+                g.hash_bytes.push_back(it.aligned == 24 ? 3 : it.container);
+                g.max_block = std::max<uint32_t>(g.max_block, it.si.max_block >= 16 ? it.si.max_block : 4096);
+            }
+            {
+                const int r = run_fast_group(g, ev);
+                if (r != ZFLACB200_OK) return r;
+            }
+            const float ms_total = ev_ms(ev.e[0], ev.e[7]);
+            zflacb200_batch::Group grp;
+            grp.bytes = g.pcm_elems * g.container_bytes;
+            grp.d_pcm = g.b_pcm.release();
+            b->groups.push_back(grp);
+            for (size_t i : members) {
+                Item &it = items[i];
+                if (!g.accepted(it.slot)) {  // the host walks this one
+                    it.eligible = false;
+                    continue;
+                }
+                const StreamSummary &sum = g.sums[it.slot];
+                const StreamDesc &sd = g.streams[it.slot];
+                zflacb200_info &inf = infos[i];
+                inf.md5_checked = do_md5 ? 1 : 0;
+                memcpy(inf.md5_computed, g.digests.data() + 16 * (size_t)it.slot, 16);
+                inf.ms_scan = ev_ms(ev.e[1], ev.e[2]);
+                inf.ms_link = g.ms_hint;
+                inf.ms_decode = g.ms_decode;
+                inf.ms_epilogue = g.ms_epilogue;
+                inf.ms_md5 = g.ms_md5;
+                inf.ms_total = ms_total;
+                if (do_md5 && memcmp(inf.md5_computed, it.si.md5, 16) != 0) {
+                    statuses[i] = ZFLACB200_INVALID_CHECKSUM;  // :279-280: no data is returned
+                    continue;
+                }
+                inf.channels = sum.channels;
+                inf.bits_per_sample = sum.bps;
+                inf.sample_rate = sum.sample_rate;
+                inf.n_samples = sum.n_samples;
+                inf.pcm_bytes = sum.n_samples * g.container_bytes;
+                inf.n_frames = sum.n_frames;
+                inf.n_candidates = n_cand;
+                inf.fast_path = 1;
+                inf.n_crc16_mismatch = sum.n_crc16_mismatch;
+                inf.audio_bytes = sum.end_offset - sd.audio_begin;
+                zflacb200_batch::Item &bi = b->items[i];
+                bi.group = (int)b->groups.size() - 1;
+                bi.byte_off = sd.pcm_base * g.container_bytes;
+                bi.bytes = inf.pcm_bytes;
+            }
+        }
+    }
+
+    // ---- everything the device-side chain did not take: one by one, chain walked on the host
+    zflacb200_options solo_opt;
+    solo_opt.struct_size = sizeof(solo_opt);
+    solo_opt.flags = (flags | ZFLACB200_NO_FAST_PATH) & ~ZFLACB200_INPUT_ON_DEVICE;
+    solo_opt.device = device;
+    solo_opt.stream = opt ? opt->stream : nullptr;
+    for (size_t i = 0; i < n; ++i) {
+        if (statuses[i] != ZFLACB200_OK || b->items[i].group >= 0) continue;
+        zflacb200_stream *h = nullptr;
+        statuses[i] = open_impl(blob + offsets[i], lens[i], &solo_opt, &h, &infos[i]);
+        if (statuses[i] == ZFLACB200_CUDA_ERROR) return ZFLACB200_CUDA_ERROR;
+        if (statuses[i] == ZFLACB200_OK) {
+            b->items[i].solo = h;
+            b->items[i].bytes = h->pcm_bytes;
+        }
+    }
+    uint64_t total = 0;
+    for (auto &g : b->groups) total += (g.bytes + 63) & ~63ull;
+    for (auto &it : b->items)
+        if (it.solo) total += (it.bytes + 63) & ~63ull;
+    b->read_all_bytes = total;
+    cleanup.armed = false;
+    *out = b;
+    return ZFLACB200_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -991,15 +1227,88 @@ int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *o
     return r;
 }
 
-int zflacb200_open_batch(const uint8_t *const *datas, const size_t *lens, size_t n, const zflacb200_options *opt,
-                         zflacb200_stream **outs, zflacb200_info *infos, int *statuses) {
-    if (!datas || !lens || !outs || !infos || !statuses) return ZFLACB200_INVALID_ARGUMENT;
-    int worst = ZFLACB200_OK;
-    for (size_t i = 0; i < n; ++i) {
-        statuses[i] = zflacb200_open(datas[i], lens[i], opt, &outs[i], &infos[i]);
-        if (statuses[i] == ZFLACB200_CUDA_ERROR) worst = ZFLACB200_CUDA_ERROR;
+int zflacb200_batch_open(const uint8_t *blob, const uint8_t *device_blob, const uint64_t *offsets, const uint64_t *lens,
+                         size_t n, const zflacb200_options *opt, zflacb200_batch **out, zflacb200_info *infos, int *statuses) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    g_last_error.clear();
+    return batch_open_impl(blob, device_blob, offsets, lens, n, opt, out, infos, statuses);
+}
+
+int zflacb200_batch_pcm_bytes(zflacb200_batch *b, uint64_t *bytes) {
+    if (!b || !bytes) return ZFLACB200_INVALID_ARGUMENT;
+    *bytes = b->read_all_bytes;
+    return ZFLACB200_OK;
+}
+
+int zflacb200_batch_read_all(zflacb200_batch *b, void *dst, size_t dst_bytes, uint64_t *pcm_offsets) {
+    if (!b || !pcm_offsets || (!dst && b->read_all_bytes)) return ZFLACB200_INVALID_ARGUMENT;
+    if (dst_bytes < b->read_all_bytes) {
+        g_last_error = "destination smaller than zflacb200_batch_pcm_bytes()";
+        return ZFLACB200_INVALID_ARGUMENT;
     }
-    return worst;
+    std::lock_guard<std::mutex> lock(g_mutex);
+    CU_CHECK(cudaSetDevice(b->device));
+    cudaStream_t st = g_ctx[b->device].stream;
+    uint64_t pos = 0;
+    std::vector<uint64_t> group_pos(b->groups.size());
+    for (size_t gi = 0; gi < b->groups.size(); ++gi) {  // one large copy per launch group
+        group_pos[gi] = pos;
+        if (b->groups[gi].bytes)
+            CU_CHECK(cudaMemcpyAsync((uint8_t *)dst + pos, b->groups[gi].d_pcm, b->groups[gi].bytes, cudaMemcpyDeviceToHost, st));
+        pos += (b->groups[gi].bytes + 63) & ~63ull;
+    }
+    for (size_t i = 0; i < b->items.size(); ++i) {
+        const zflacb200_batch::Item &it = b->items[i];
+        if (it.group >= 0) {
+            pcm_offsets[i] = group_pos[it.group] + it.byte_off;
+        } else if (it.solo) {
+            pcm_offsets[i] = pos;
+            if (it.bytes) CU_CHECK(cudaMemcpyAsync((uint8_t *)dst + pos, it.solo->d_pcm, it.bytes, cudaMemcpyDeviceToHost, st));
+            pos += (it.bytes + 63) & ~63ull;
+        } else {
+            pcm_offsets[i] = ~0ull;
+        }
+    }
+    CU_CHECK(cudaStreamSynchronize(st));
+    return ZFLACB200_OK;
+}
+
+static int batch_item_ptr(zflacb200_batch *b, size_t i, void **p, size_t *bytes) {
+    if (!b || i >= b->items.size()) return ZFLACB200_INVALID_ARGUMENT;
+    const zflacb200_batch::Item &it = b->items[i];
+    if (it.group >= 0) *p = (uint8_t *)b->groups[it.group].d_pcm + it.byte_off;
+    else if (it.solo) *p = it.solo->d_pcm;
+    else return ZFLACB200_INVALID_ARGUMENT;
+    *bytes = it.bytes;
+    return ZFLACB200_OK;
+}
+
+int zflacb200_batch_read_stream(zflacb200_batch *b, size_t i, void *dst, size_t dst_bytes) {
+    void *p = nullptr;
+    size_t bytes = 0;
+    const int e = batch_item_ptr(b, i, &p, &bytes);
+    if (e != ZFLACB200_OK) return e;
+    if (dst_bytes < bytes || (!dst && bytes)) return ZFLACB200_INVALID_ARGUMENT;
+    std::lock_guard<std::mutex> lock(g_mutex);
+    CU_CHECK(cudaSetDevice(b->device));
+    if (bytes) CU_CHECK(cudaMemcpy(dst, p, bytes, cudaMemcpyDeviceToHost));
+    return ZFLACB200_OK;
+}
+
+int zflacb200_batch_device_pcm(zflacb200_batch *b, size_t i, void **dev_ptr, size_t *bytes) {
+    if (!dev_ptr || !bytes) return ZFLACB200_INVALID_ARGUMENT;
+    return batch_item_ptr(b, i, dev_ptr, bytes);
+}
+
+void zflacb200_batch_close(zflacb200_batch *b) {
+    if (!b) return;
+    for (auto &it : b->items)
+        if (it.solo) zflacb200_close(it.solo);
+    std::lock_guard<std::mutex> lock(g_mutex);
+    cudaSetDevice(b->device);
+    for (auto &g : b->groups)
+        if (g.d_pcm) cudaFreeAsync(g.d_pcm, g_ctx[b->device].stream);
+    delete b;
 }
 
 int zflacb200_frames(zflacb200_stream *s, zflacb200_frame *dst, size_t capacity, size_t *n_frames) {
