@@ -212,16 +212,38 @@ def pack_streams(streams, align: int = 16):
     return blob, offsets, lens
 
 
+class _LazyInfos:
+    """Sequence view over the C info array; element i becomes a dict when it is read."""
+
+    def __init__(self, raw, n):
+        self._raw, self._n = raw, n
+
+    def __len__(self):
+        return self._n
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [_info_dict(self._raw[k]) for k in range(*i.indices(self._n))]
+        if i < 0:
+            i += self._n
+        if not 0 <= i < self._n:
+            raise IndexError(i)
+        return _info_dict(self._raw[i])
+
+    def __iter__(self):
+        return (_info_dict(self._raw[k]) for k in range(self._n))
+
+
 class DeviceBatch:
     """Result of zflacb200_batch_open: per-stream statuses / infos, PCM resident in HBM."""
 
     def __init__(self, handle, infos, statuses, n):
         self._h = handle
         self.n = n
-        self.statuses = [int(x) for x in statuses]
+        self.statuses = np.frombuffer(statuses, dtype=np.int32, count=n).tolist() if n else []
         self.errors = [None if st == 0 else _native.load().zflacb200_status_name(st).decode() for st in self.statuses]
-        self.infos = [_info_dict(infos[i]) for i in range(n)]
         self._raw_infos = infos
+        self.infos = _LazyInfos(infos, n)  # dicts are built on access: 10k eager conversions cost more than the decode
 
     def pcm_bytes(self) -> int:
         v = C.c_uint64()

@@ -10,7 +10,9 @@
 #include "../../include/zflacb200.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -49,6 +51,30 @@ DeviceCtx g_ctx[64];
             return ZFLACB200_CUDA_ERROR;                                                        \
         }                                                                                       \
     } while (0)
+
+// Host-side phase timer: ZFLACB200_TRACE=1 prints where the HOST spends its time inside a call (stderr).
+struct HostTrace {
+    bool on;
+    const char *what;
+    std::chrono::steady_clock::time_point t0, last;
+    std::string log;
+    explicit HostTrace(const char *w) : on(getenv("ZFLACB200_TRACE") != nullptr), what(w) {
+        if (on) t0 = last = std::chrono::steady_clock::now();
+    }
+    void mark(const char *name) {
+        if (!on) return;
+        const auto t = std::chrono::steady_clock::now();
+        char b[96];
+        snprintf(b, sizeof(b), " %s=%.3f", name, std::chrono::duration<double, std::milli>(t - last).count());
+        log += b;
+        last = t;
+    }
+    ~HostTrace() {
+        if (!on) return;
+        const auto t = std::chrono::steady_clock::now();
+        fprintf(stderr, "[zflacb200 trace] %s total=%.3f ms:%s\n", what, std::chrono::duration<double, std::milli>(t - t0).count(), log.c_str());
+    }
+};
 
 int ensure_device(int device, int *resolved) {
     int count = 0;
@@ -475,7 +501,9 @@ int run_fast_group(FastGroup &g, Events &ev) {
     const uint32_t n = g.n_cand;
     const uint32_t ns = (uint32_t)g.streams.size();
     const uint32_t window = 16;
+    HostTrace tr("run_fast_group");
     g.plan();
+    tr.mark("plan");
 
     DevBuf b_sd, b_scratch, b_sum, b_flag, b_jobs, b_digest;
     if (b_sd.alloc(sizeof(StreamDesc) * ns, st) || g.b_recs.alloc(sizeof(FrameRec) * (size_t)n, st) ||
@@ -484,6 +512,7 @@ int run_fast_group(FastGroup &g, Events &ev) {
         g.b_ok.alloc(n, st) || b_flag.alloc(sizeof(uint32_t), st) || b_jobs.alloc(sizeof(Md5Job) * ns, st) ||
         b_digest.alloc(16 * (size_t)ns, st))
         return ZFLACB200_CUDA_ERROR;
+    tr.mark("alloc");
     CU_CHECK(cudaMemcpyAsync(b_sd.p, g.streams.data(), sizeof(StreamDesc) * ns, cudaMemcpyHostToDevice, st));
     CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary) * ns, st));
     CU_CHECK(cudaMemsetAsync(g.b_ok.p, 2, n, st));  // 2 = not checked
@@ -519,6 +548,7 @@ int run_fast_group(FastGroup &g, Events &ev) {
     ep.lossy_flag = (uint32_t *)b_flag.p;
     CU_CHECK(launch_epilogue(ep, st));
     CU_CHECK(cudaEventRecord(ev.e[6], st));
+    tr.mark("launches");
 
     g.digests.assign(16 * (size_t)ns, 0);
     if (g.do_md5) {
@@ -551,7 +581,9 @@ int run_fast_group(FastGroup &g, Events &ev) {
     CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));
     g.sums.resize(ns);
     CU_CHECK(cudaMemcpyAsync(g.sums.data(), b_sum.p, sizeof(StreamSummary) * ns, cudaMemcpyDeviceToHost, st));
+    tr.mark("md5_setup");
     CU_CHECK(cudaStreamSynchronize(st));
+    tr.mark("final_sync");
     g.ms_hint = ev_ms(ev.e[2], ev.e[3]);
     g.ms_decode = ev_ms(ev.e[4], ev.e[5]);
     g.ms_epilogue = ev_ms(ev.e[5], ev.e[6]);
@@ -927,6 +959,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         int group = -1;
         uint32_t slot = 0;  // index inside the group
     };
+    HostTrace tr("batch_open");
     std::vector<Item> items(n);
     uint64_t blob_len = 0, scan_begin = ~0ull;
     std::vector<uint32_t> keys;  // distinct (wide, container, shift) classes
@@ -962,6 +995,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         }
     }
 
+    tr.mark("metadata");
     zflacb200_batch *b = new zflacb200_batch();
     b->device = device;
     b->items.resize(n);
@@ -1012,6 +1046,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
             }
         }
         CU_CHECK(cudaEventRecord(ev.e[2], st));
+        tr.mark("h2d+scan");
 
         // ---- one launch group per class
         for (size_t gi = 0; gi < keys.size() && n_cand > 0; ++gi) {
@@ -1049,11 +1084,14 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
                 g.hash_bytes.push_back(it.aligned == 24 ? 3 : it.container);
                 g.max_block = std::max<uint32_t>(g.max_block, it.si.max_block >= 16 ? it.si.max_block : 4096);
             }
+            tr.mark("group_setup");
             {
                 const int r = run_fast_group(g, ev);
                 if (r != ZFLACB200_OK) return r;
             }
+            tr.mark("run_fast_group");
             const float ms_total = ev_ms(ev.e[0], ev.e[7]);
+            const float ms_scan = ev_ms(ev.e[1], ev.e[2]);  // once: an event query per stream costs more than the decode
             zflacb200_batch::Group grp;
             grp.bytes = g.pcm_elems * g.container_bytes;
             grp.d_pcm = g.b_pcm.release();
@@ -1069,7 +1107,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
                 zflacb200_info &inf = infos[i];
                 inf.md5_checked = do_md5 ? 1 : 0;
                 memcpy(inf.md5_computed, g.digests.data() + 16 * (size_t)it.slot, 16);
-                inf.ms_scan = ev_ms(ev.e[1], ev.e[2]);
+                inf.ms_scan = ms_scan;
                 inf.ms_link = g.ms_hint;
                 inf.ms_decode = g.ms_decode;
                 inf.ms_epilogue = g.ms_epilogue;
@@ -1097,6 +1135,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         }
     }
 
+    tr.mark("collect");
     // ---- everything the device-side chain did not take: one by one, chain walked on the host
     zflacb200_options solo_opt;
     solo_opt.struct_size = sizeof(solo_opt);
