@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "../../zflac_b200/csrc/decode_core.cuh"
+#include "../../zflac_b200/csrc/parse_core.cuh"
 
 namespace {
 
@@ -69,6 +70,49 @@ int zf_host_decode_frame(const uint8_t *stream, const zf::FrameRec *fr, void *sc
     if (g_rollbacks) *g_rollbacks += br.src.rollbacks;
     return br.src.violations;
 }
+
+// Pass A of the two-pass decoder on the host: residuals / warm-up / verbatim samples into the int32
+// scratch, one SubRec per channel into subs[0..8). Returns the unchecked-read violations (must be 0).
+int zf_host_parse_frame(const uint8_t *stream, const zf::FrameRec *fr, int32_t *scratch, zf::SubRec *subs, int write_samples,
+                        zf::FrameOut *out) {
+    const uint64_t start = fr->offset + fr->header_len;
+    const uint64_t origin = start & ~3ull;
+    const uint64_t bytes = fr->stream_end > origin ? fr->stream_end - origin : 0;
+    zf::BitReader<HostSrc> br;
+    br.src.g = stream + origin;
+    br.src.avail = bytes;
+    br.src.guaranteed = 0;
+    br.src.consumed_below = 0;
+    br.src.violations = 0;
+    br.src.rollbacks = 0;
+    br.init((uint32_t)(start & 3));
+    uint32_t max_order = 0;
+    zf::parse_frame(br, *fr, scratch, subs, bytes * 8, write_samples != 0, origin, *out, max_order);
+    if (g_rollbacks) *g_rollbacks += br.src.rollbacks;
+    return br.src.violations;
+}
+
+// Scalar restatement of what pass B (predict.cu) does to one scratch plane: predictor recurrence in
+// place, then the wasted-bits shift. Test-side stand-in for the CUDA kernel (the -m gpu tests pin the kernel).
+void zf_host_predict_plane(const zf::SubRec *sub, int32_t *plane, uint32_t block_size) {
+    for (uint32_t i = 0; i < block_size; ++i) {
+        int32_t v;
+        if (sub->kind == zf::kSubConst) {
+            v = sub->constant;
+        } else {
+            v = plane[i];
+            if (sub->kind == zf::kSubPred && i >= sub->order) {
+                int64_t acc = 0;
+                for (uint32_t j = 0; j < sub->order; ++j) acc += (int64_t)sub->coef[j] * (int64_t)plane[i - 1 - j];
+                v += (int32_t)(acc >> sub->shift);
+            }
+        }
+        plane[i] = v;
+    }
+    for (uint32_t i = 0; i < block_size; ++i) plane[i] = (int32_t)((uint32_t)plane[i] << sub->wasted);
+}
+
+int zf_host_subrec_size(void) { return (int)sizeof(zf::SubRec); }
 
 void zf_host_set_rollback_counter(long long *p) { g_rollbacks = p; }
 

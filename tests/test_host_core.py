@@ -21,7 +21,8 @@ import synth_cases
 HERE = os.path.join(ROOT, "tests", "host_core")
 LIB = os.path.join(HERE, "_build", "libzf_host_core.so")
 SRC = os.path.join(HERE, "host_core.cu")
-DEPS = [SRC, os.path.join(ROOT, "zflac_b200", "csrc", "decode_core.cuh"), os.path.join(ROOT, "zflac_b200", "csrc", "common.cuh")]
+DEPS = [SRC, os.path.join(ROOT, "zflac_b200", "csrc", "decode_core.cuh"), os.path.join(ROOT, "zflac_b200", "csrc", "parse_core.cuh"),
+        os.path.join(ROOT, "zflac_b200", "csrc", "common.cuh")]
 
 FRAME_REC = np.dtype([("offset", "<u8"), ("stream_end", "<u8"), ("sample_base", "<u8"), ("scratch_base", "<u8"),
                       ("block_size", "<u4"), ("scratch_pitch", "<u4"), ("header_len", "u1"), ("ch_code", "u1"),
@@ -41,11 +42,17 @@ def core():
     lib.zf_host_decode_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.zf_host_decode_frame.restype = C.c_int
     assert lib.zf_host_framerec_size() == FRAME_REC.itemsize
+    lib.zf_host_parse_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    lib.zf_host_parse_frame.restype = C.c_int
+    lib.zf_host_predict_plane.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    lib.zf_host_predict_plane.restype = None
+    assert lib.zf_host_subrec_size() == 80
     return lib
 
 
-def host_decode(lib, data: bytes, ref):
-    """Decode all frames of the oracle's frame trace with the host core; return interleaved PCM like the reference's."""
+def host_decode(lib, data: bytes, ref, two_pass: bool = False):
+    """Decode all frames of the oracle's frame trace with the host core; return interleaved PCM like the reference's.
+    two_pass: pass A (parse_core.cuh) + a scalar restatement of pass B instead of the single-pass decoder."""
     arr = np.frombuffer(data, dtype=np.uint8)
     ch, bps = ref.channels, ref.bits_per_sample
     wide = bps == 32
@@ -62,7 +69,15 @@ def host_decode(lib, data: bytes, ref):
         rec["header_len"], rec["ch_code"], rec["channels"], rec["bps"] = fr["header_len"], fr["channel_code"], ch, bps
         scratch = np.zeros(pitch * ch, dtype=np.int64 if wide else np.int32)
         out = np.zeros(1, dtype=FRAME_OUT)
-        viol = lib.zf_host_decode_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, int(wide), 1, out.ctypes.data)
+        if two_pass:
+            assert not wide
+            subs = np.zeros(8 * 80, dtype=np.uint8)
+            viol = lib.zf_host_parse_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, subs.ctypes.data, 1, out.ctypes.data)
+            if int(out["status"][0]) == 0:
+                for c in range(ch):
+                    lib.zf_host_predict_plane(subs.ctypes.data + 80 * c, scratch.ctypes.data + 4 * pitch * c, bs)
+        else:
+            viol = lib.zf_host_decode_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, int(wide), 1, out.ctypes.data)
         assert viol == 0, "unchecked word read beyond the top_up guarantee"
         assert int(out["status"][0]) == 0, (int(fr["offset"]), int(out["status"][0]))
         assert int(out["end_offset"][0]) == int(fr["end_offset"]), int(fr["offset"])
@@ -96,6 +111,32 @@ def test_host_core_corpus(core, entry):
     if ref.error != "OK":
         pytest.skip(f"oracle: {ref.error}")
     got = host_decode(core, data, ref)
+    assert np.array_equal(got, ref.samples)
+
+
+@pytest.mark.parametrize("entry", [e for e in corpus_entries() if not e["expect_error"]],
+                         ids=[i for i, e in zip(corpus_ids(), corpus_entries()) if not e["expect_error"]])
+def test_host_parse_core_corpus(core, entry):
+    """Pass A (parse_core.cuh: residuals + SubRec) followed by the recurrence == the oracle, frame ends included."""
+    data = corpus_bytes(entry)
+    ref = oracle.decode(data, trace_frames=True)
+    if ref.error != "OK":
+        pytest.skip(f"oracle: {ref.error}")
+    if ref.bits_per_sample == 32:
+        pytest.skip("32 bps streams stay on the single-pass int64 decoder")
+    got = host_decode(core, data, ref, two_pass=True)
+    assert np.array_equal(got, ref.samples)
+
+
+@pytest.mark.parametrize("name", sorted(synth_cases.CASES))
+def test_host_parse_core_synth(core, name):
+    s = synth_cases.make(name)
+    data = s.flac.tobytes()
+    ref = oracle.decode(data, trace_frames=True)
+    assert ref.error == "OK"
+    if ref.bits_per_sample == 32:
+        pytest.skip("32 bps streams stay on the single-pass int64 decoder")
+    got = host_decode(core, data, ref, two_pass=True)
     assert np.array_equal(got, ref.samples)
 
 

@@ -76,6 +76,15 @@ struct HostTrace {
     }
 };
 
+// Diagnostics: ZFLACB200_EXTRA_FLAGS=<hex> is OR-ed into every call's option flags (A/B runs of the bench).
+uint32_t env_flags() {
+    static const uint32_t v = [] {
+        const char *e = getenv("ZFLACB200_EXTRA_FLAGS");
+        return e ? (uint32_t)strtoul(e, nullptr, 16) : 0u;
+    }();
+    return v;
+}
+
 int ensure_device(int device, int *resolved) {
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
@@ -450,7 +459,53 @@ struct DevBuf {  // stream-ordered allocation released on scope exit
     }
 };
 
-constexpr int kFastFallback = -1;  // not an error: the hinted chain was not accepted, walk it on the host
+// Subframe decode + epilogue over a set of frame records. Streams with <= 31 bits per sample run the
+// two-pass decoder (K2a parse_frames: the serial bit chain, one lane per frame; K3p predict_epilogue:
+// predictor recurrence + decorrelation + interleave, one lane per subframe); 32 bps streams (int64
+// scratch) and ZFLACB200_SINGLE_PASS run the fused single-pass K2 + K3.
+struct SubframeStage {
+    bool two_pass = false;
+    DevBuf b_subs, b_big;
+    int prepare(bool wide, uint32_t flags, uint32_t n_recs, cudaStream_t st) {
+        two_pass = !wide && (flags & ZFLACB200_SINGLE_PASS) == 0;
+        if (!two_pass) return ZFLACB200_OK;
+        if (b_subs.p) { cudaFreeAsync(b_subs.p, st); b_subs.p = nullptr; }
+        if (b_big.p) { cudaFreeAsync(b_big.p, st); b_big.p = nullptr; }
+        if (b_subs.alloc(kSubRecBytes * 8 * (size_t)std::max<uint32_t>(n_recs, 1), st) || b_big.alloc(sizeof(uint32_t), st))
+            return ZFLACB200_CUDA_ERROR;
+        CU_CHECK(cudaMemsetAsync(b_big.p, 0, sizeof(uint32_t), st));
+        return ZFLACB200_OK;
+    }
+    int decode(const uint8_t *d_stream, const FrameRec *d_recs, uint32_t n, void *d_scratch, bool wide, FrameOut *d_outs, bool write,
+               cudaStream_t st) {
+        if (two_pass)
+            CU_CHECK(launch_parse_frames(d_stream, d_recs, n, (int32_t *)d_scratch, (SubRec *)b_subs.p, d_outs, (uint32_t *)b_big.p, write, st));
+        else
+            CU_CHECK(launch_decode_frames(d_stream, d_recs, n, d_scratch, wide, d_outs, write, st));
+        return ZFLACB200_OK;
+    }
+    int epilogue(const EpilogueParams &ep, const FrameOut *d_outs, uint32_t max_channels, cudaStream_t st) {
+        if (!two_pass) {
+            CU_CHECK(launch_epilogue(ep, st));
+            return ZFLACB200_OK;
+        }
+        PredictParams pp;
+        pp.frames = ep.frames;
+        pp.outs = d_outs;
+        pp.n_frames = ep.n_frames;
+        pp.max_channels = max_channels;
+        pp.scratch = ep.scratch;
+        pp.subs = b_subs.p;
+        pp.pcm = ep.pcm;
+        pp.container_bytes = ep.container_bytes;
+        pp.msb_shift = ep.msb_shift;
+        pp.lossy_flag = ep.lossy_flag;
+        pp.big_orders = (const uint32_t *)b_big.p;
+        CU_CHECK(launch_predict_epilogue(pp, st));
+        return ZFLACB200_OK;
+    }
+};
+
 
 // One launch group of the fast path: streams that share the scratch element type (wide), the
 // container type and the MSB-align shift, packed in one device buffer.
@@ -464,6 +519,7 @@ struct FastGroup {
     bool wide = false;
     uint32_t container_bytes = 2, msb_shift = 0, max_block = 4096;
     bool do_md5 = true;
+    uint32_t flags = 0;                   // zflacb200_options.flags of the call
     std::vector<StreamDesc> streams;      // pcm_base / scratch_base filled by plan()
     std::vector<uint32_t> hash_bytes;     // per stream: bytes of each sample that enter the MD5 (Q4)
     uint64_t pcm_elems = 0, scratch_elems = 0;
@@ -506,6 +562,10 @@ int run_fast_group(FastGroup &g, Events &ev) {
     tr.mark("plan");
 
     DevBuf b_sd, b_scratch, b_sum, b_flag, b_jobs, b_digest;
+    SubframeStage stage;
+    if (stage.prepare(g.wide, g.flags, n, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    uint32_t max_channels = 1;
+    for (const auto &sd : g.streams) max_channels = std::max<uint32_t>(max_channels, sd.si_channels);
     if (b_sd.alloc(sizeof(StreamDesc) * ns, st) || g.b_recs.alloc(sizeof(FrameRec) * (size_t)n, st) ||
         g.b_outs.alloc(sizeof(FrameOut) * (size_t)n, st) || b_scratch.alloc(g.scratch_elems * (g.wide ? 8 : 4), st) ||
         g.b_pcm.alloc(g.pcm_elems * g.container_bytes + 64, st) || b_sum.alloc(sizeof(StreamSummary) * ns, st) ||
@@ -526,7 +586,7 @@ int run_fast_group(FastGroup &g, Events &ev) {
     CU_CHECK(launch_hint_chain(g.d_cands, n, d_sd, ns, d_recs, window, st));
     CU_CHECK(cudaEventRecord(ev.e[3], st));
     CU_CHECK(cudaEventRecord(ev.e[4], st));
-    CU_CHECK(launch_decode_frames(g.d_blob, d_recs, n, b_scratch.p, g.wide, d_outs, true, st));
+    if (stage.decode(g.d_blob, d_recs, n, b_scratch.p, g.wide, d_outs, true, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
     CU_CHECK(cudaEventRecord(ev.e[5], st));
 
     // side stream: CRC-16 of every decoded frame, overlapping K3 (+K4)
@@ -546,7 +606,7 @@ int run_fast_group(FastGroup &g, Events &ev) {
     ep.container_bytes = g.container_bytes;
     ep.msb_shift = g.msb_shift;
     ep.lossy_flag = (uint32_t *)b_flag.p;
-    CU_CHECK(launch_epilogue(ep, st));
+    if (stage.epilogue(ep, d_outs, max_channels, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
     CU_CHECK(cudaEventRecord(ev.e[6], st));
     tr.mark("launches");
 
@@ -558,7 +618,7 @@ int run_fast_group(FastGroup &g, Events &ev) {
             CU_CHECK(cudaStreamSynchronize(st));
             if (lossy) {
                 ep.msb_shift = 0;
-                CU_CHECK(launch_epilogue(ep, st));
+                if (stage.epilogue(ep, d_outs, max_channels, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
             }
         }
         std::vector<Md5Job> jobs(ns);
@@ -598,7 +658,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     }
     *out = nullptr;
     memset(info, 0, sizeof(*info));
-    const uint32_t flags = opt ? opt->flags : 0;
+    const uint32_t flags = (opt ? opt->flags : 0) | env_flags();
     int device = -1;
     {
         const int e = ensure_device(opt ? opt->device : -1, &device);
@@ -695,6 +755,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
         g.msb_shift = msb_shift;
         g.max_block = pl.si.max_block >= 16 ? pl.si.max_block : 4096;
         g.do_md5 = do_md5;
+        g.flags = flags;
         StreamDesc sd;
         memset(&sd, 0, sizeof(sd));
         sd.begin = 0;
@@ -766,6 +827,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     // ---- chain + K2, repeated only if a decoded frame end contradicts a CRC-16 link
     Chain chain;
     DevBuf b_frames, b_outs, b_scratch, b_pcm;
+    SubframeStage stage;
     std::vector<FrameOut> outs;
     int final_status = ZFLACB200_OK;
     bool decoded_ok = false;
@@ -785,12 +847,14 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
         if (b_frames.alloc(sizeof(FrameRec) * std::max<uint32_t>(nf, 1), st) || b_outs.alloc(sizeof(FrameOut) * std::max<uint32_t>(nf, 1), st))
             return ZFLACB200_CUDA_ERROR;
         if (write && b_scratch.alloc(chain.scratch_elems * (pl.wide ? 8 : 4), st)) return ZFLACB200_CUDA_ERROR;
+        if (stage.prepare(pl.wide, write ? flags : (flags | ZFLACB200_SINGLE_PASS), nf, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
         outs.resize(nf);
         if (nf) {
             CU_CHECK(cudaMemcpyAsync(b_frames.p, recs.data(), sizeof(FrameRec) * nf, cudaMemcpyHostToDevice, st));
             CU_CHECK(cudaEventRecord(ev.e[4], st));
-            CU_CHECK(launch_decode_frames(pl.d_stream, (const FrameRec *)b_frames.p, nf, b_scratch.p, pl.wide,
-                                          (FrameOut *)b_outs.p, write, st));
+            if (stage.decode(pl.d_stream, (const FrameRec *)b_frames.p, nf, b_scratch.p, pl.wide, (FrameOut *)b_outs.p, write, st) !=
+                ZFLACB200_OK)
+                return ZFLACB200_CUDA_ERROR;
             CU_CHECK(cudaEventRecord(ev.e[5], st));
             CU_CHECK(cudaMemcpyAsync(outs.data(), b_outs.p, sizeof(FrameOut) * nf, cudaMemcpyDeviceToHost, st));
             CU_CHECK(cudaStreamSynchronize(st));
@@ -836,7 +900,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     ep.container_bytes = container_bytes;
     ep.msb_shift = msb_shift;
     ep.lossy_flag = (uint32_t *)b_flag.p;
-    CU_CHECK(launch_epilogue(ep, st));
+    if (stage.epilogue(ep, (const FrameOut *)b_outs.p, chain.channels, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
     CU_CHECK(cudaEventRecord(ev.e[6], st));
 
     // ---- K4: MD5 gate
@@ -847,7 +911,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
             CU_CHECK(cudaStreamSynchronize(st));
             if (lossy) {  // a sample exceeds the STREAMINFO depth (Q5): hash the unshifted values, shift afterwards
                 ep.msb_shift = 0;
-                CU_CHECK(launch_epilogue(ep, st));
+                if (stage.epilogue(ep, (const FrameOut *)b_outs.p, chain.channels, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
             }
         }
         Md5Job job;
@@ -942,7 +1006,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         return ZFLACB200_INVALID_ARGUMENT;
     }
     *out = nullptr;
-    const uint32_t flags = opt ? opt->flags : 0;
+    const uint32_t flags = (opt ? opt->flags : 0) | env_flags();
     int device = -1;
     {
         const int e = ensure_device(opt ? opt->device : -1, &device);
@@ -962,7 +1026,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
     HostTrace tr("batch_open");
     std::vector<Item> items(n);
     uint64_t blob_len = 0, scan_begin = ~0ull;
-    std::vector<uint32_t> keys;  // distinct (wide, container, shift) classes
+    std::vector<uint32_t> keys;  // distinct (channels, wide, container, shift) classes
     for (size_t i = 0; i < n; ++i) {
         memset(&infos[i], 0, sizeof(zflacb200_info));
         blob_len = std::max(blob_len, offsets[i] + lens[i]);
@@ -986,7 +1050,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         it.eligible = it.si.total > 0 && it.si.total * (it.si.channels_m1 + 1) < (1ull << 40) &&
                       (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0;
         if (it.eligible) {
-            const uint32_t key = (it.wide ? 1u << 16 : 0u) | (it.container << 8) | it.msb_shift;
+            const uint32_t key = ((uint32_t)it.si.channels_m1 << 20) | (it.wide ? 1u << 16 : 0u) | (it.container << 8) | it.msb_shift;
             size_t g = 0;
             while (g < keys.size() && keys[g] != key) ++g;
             if (g == keys.size()) keys.push_back(key);
@@ -1061,6 +1125,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
             g.container_bytes = (keys[gi] >> 8) & 0xFF;
             g.msb_shift = keys[gi] & 0xFF;
             g.do_md5 = do_md5;
+            g.flags = flags;
             g.max_block = 16;
             std::vector<size_t> members;
             for (size_t i = 0; i < n; ++i) {  // streams in blob order (the device searches them by offset)

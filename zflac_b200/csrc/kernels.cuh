@@ -34,6 +34,26 @@ cudaError_t launch_verify_chain(const Cand *d_cands, uint32_t n, const StreamDes
 cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, void *d_scratch,
                                  bool wide_scratch, FrameOut *d_outs, bool write_samples, cudaStream_t st);
 
+// parse.cu + predict.cu: the two-pass decoder for streams with <= 31 bits per sample
+struct SubRec;  // parse_core.cuh
+constexpr size_t kSubRecBytes = 80;  // sizeof(SubRec); 8 slots per frame record
+cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, int32_t *d_scratch,
+                                SubRec *d_subs, FrameOut *d_outs, uint32_t *d_big_orders, bool write_samples, cudaStream_t st);
+struct PredictParams {
+    const FrameRec *frames;
+    const FrameOut *outs;      // frames whose status is not ST_OK are skipped
+    uint32_t n_frames;
+    uint32_t max_channels;     // largest channel count among the frames (sizes the lane groups)
+    const void *scratch;       // int32 planes written by launch_parse_frames
+    const void *subs;          // SubRec[8 * n_frames]
+    void *pcm;
+    uint32_t container_bytes;  // 1, 2, 4
+    uint32_t msb_shift;
+    uint32_t *lossy_flag;
+    const uint32_t *big_orders;  // written by launch_parse_frames: != 0 iff some subframe has an order above 12
+};
+cudaError_t launch_predict_epilogue(const PredictParams &p, cudaStream_t st);
+
 // epilogue.cu
 struct EpilogueParams {
     const FrameRec *frames;

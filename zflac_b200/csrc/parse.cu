@@ -1,0 +1,46 @@
+// parse.cu — K2a parse_frames (sm_100a): pass A of the two-pass subframe decoder. One lane per
+// frame walks the frame's serial bit chain (subframe headers, warm-up samples, coefficients, Rice
+// partitions; reference src/zflac.zig:425-551, :614-666 and src/bit_reader.zig) and leaves the raw
+// material of every subframe in HBM: residuals / warm-up / verbatim samples in the planar int32
+// scratch, one SubRec per subframe. The predictor recurrence itself runs in pass B (predict.cu),
+// one lane per subframe. The logic is parse_core.cuh; the word source is the cp.async ring of
+// ring_src.cuh.
+#include "kernels.cuh"
+#include "parse_core.cuh"
+#include "ring_src.cuh"
+
+namespace zf {
+
+__global__ void __launch_bounds__(kDecodeThreads)
+k_parse_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frames, uint32_t n_frames,
+               int32_t *__restrict__ scratch, SubRec *__restrict__ subs, FrameOut *__restrict__ outs,
+               uint32_t *__restrict__ big_orders, int write_samples) {
+    const uint32_t f = blockIdx.x * kDecodeThreads + threadIdx.x;
+    if (f >= n_frames) return;
+    const FrameRec fr = frames[f];
+    if (fr.block_size == 0) return;  // dropped candidate slot
+    const uint64_t start = fr.offset + fr.header_len;  // first subframe header
+    const uint64_t origin = start & ~3ull;             // word 0 of the lane's source
+    BitReader<RingSrc<kDecodeThreads>> br;
+    br.src.init(s + origin, fr.stream_end > origin ? fr.stream_end - origin : 0, threadIdx.x);
+    br.init((uint32_t)(start & 3));
+    const uint64_t len_bits = (fr.stream_end > origin ? fr.stream_end - origin : 0) * 8;
+    FrameOut o;
+    uint32_t max_order = 0;
+    parse_frame(br, fr, scratch, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order);
+    if (max_order > 12 && write_samples) *big_orders = 1u;  // pass B then also runs its 32-tap kernel
+    asm volatile("cp.async.wait_group 0;" ::: "memory");  // nothing may land in the ring after the CTA retires
+    outs[f] = o;
+}
+
+cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, int32_t *d_scratch,
+                                SubRec *d_subs, FrameOut *d_outs, uint32_t *d_big_orders, bool write_samples, cudaStream_t st) {
+    if (n_frames == 0) return cudaSuccess;
+    const uint32_t blocks = (n_frames + kDecodeThreads - 1) / kDecodeThreads;
+    ZF_COUNT_LAUNCH();
+    k_parse_frames<<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(
+        d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_big_orders, write_samples ? 1 : 0);
+    return cudaGetLastError();
+}
+
+}  // namespace zf

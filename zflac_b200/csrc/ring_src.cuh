@@ -1,0 +1,100 @@
+// ring_src.cuh — the device word source of the frame-serial kernels (K2 decode_frames, K2a parse_frames).
+//
+// Lane L of a CTA owns column L of a ring of kRingWords rows x NT columns of 32-bit words: stream
+// word w of the lane's frame sits at ring[w % kRingWords][L]. Every shared load of the bit reader
+// is therefore bank-conflict free whatever the lanes' cursors are (a lane only ever touches bank
+// L % 32), and the fill is a 4-byte cp.async.ca per word — L1 keeps the 32-byte sector, so DRAM
+// sees every compressed byte once. Fills happen at a uniform cadence (before each 8-row body) so
+// the warp does not diverge on "my queue is empty"; completion is tracked with cp.async groups: a
+// commit per refill, boundaries of the three newest groups remembered, and a wait_group cascade
+// that only blocks on groups old enough to have landed.
+#pragma once
+#include "decode_core.cuh"
+
+namespace zf {
+
+constexpr int kDecodeThreads = 128;
+constexpr uint32_t kRingWords = 32;  // 128 B per lane ahead of the cursor (~130 rows of 16-bit audio)
+
+// Block until words < need have landed, waiting on as few (= as old) cp.async groups as possible.
+// By-value in and out so that the ring bookkeeping stays in registers at the call sites.
+static __device__ __noinline__ uint32_t ring_wait(uint32_t need, uint32_t ready, uint32_t h0, uint32_t h1, uint32_t h2, uint32_t filled) {
+    asm volatile("cp.async.wait_group 3;" ::: "memory");
+    ready = max(ready, h2);
+    if (ready >= need) return ready;
+    asm volatile("cp.async.wait_group 2;" ::: "memory");
+    ready = max(ready, h1);
+    if (ready >= need) return ready;
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    ready = max(ready, h0);
+    if (ready >= need) return ready;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    return filled;
+}
+
+extern __shared__ uint32_t zf_ring[];  // kRingWords x NT words
+
+template <int NT>
+struct RingSrc {
+    const uint8_t *g;    // global address of word 0 (4-byte aligned)
+    uint32_t avail;      // bytes readable from g (stream end), clamped
+    uint32_t col;        // shared-space byte address of zf_ring[lane column]: word w lives (w % kRingWords) * NT words further
+    uint32_t filled;     // words < filled have been issued
+    uint32_t ready;      // words < ready have landed
+    uint32_t h0, h1, h2; // `filled` before the newest / 2nd newest / 3rd newest committed group
+
+    __device__ __forceinline__ void init(const uint8_t *base, uint64_t bytes, uint32_t column) {
+        g = base;
+        avail = bytes > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)bytes;
+        col = (uint32_t)__cvta_generic_to_shared(&zf_ring[column]);
+        filled = ready = h0 = h1 = h2 = 0;
+    }
+    __device__ __forceinline__ uint32_t slot(uint32_t w) const { return col + (w & (kRingWords - 1)) * (NT * 4); }
+    __device__ __forceinline__ void issue(uint32_t w) {
+        const uint32_t dst = slot(w);
+        if (w < (avail >> 2)) {  // a whole word inside the stream: the hot case
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(g + (size_t)w * 4u) : "memory");
+        } else {                 // bytes past the stream end are zero-filled
+            const uint32_t off = w * 4u;
+            const uint32_t n = off < avail ? avail - off : 0u;  // 0..3
+            const uint8_t *src = g + (n ? off : 0u);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(n) : "memory");
+        }
+    }
+    // words < cur are consumed: issue everything the ring has room for
+    __device__ __forceinline__ void fill(uint32_t cur) {
+        if (filled < cur + kRingWords) {
+            const uint32_t before = filled;
+#pragma unroll 1
+            do {
+                issue(filled);
+                ++filled;
+            } while (filled < cur + kRingWords);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            h2 = h1;
+            h1 = h0;
+            h0 = before;
+        }
+    }
+    __device__ __forceinline__ void wait_for(uint32_t need) { ready = ring_wait(need, ready, h0, h1, h2, filled); }
+    __device__ __forceinline__ void top_up(uint32_t cur) {
+        fill(cur);
+        if (ready < cur + kFastWords) wait_for(cur + kFastWords);
+    }
+    __device__ __forceinline__ uint32_t word(uint32_t w) const {
+        uint32_t v;  // volatile: stays ordered against the cp.async / wait_group statements
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(slot(w)));
+        return v;
+    }
+    __device__ __forceinline__ void note_rollback() {}
+    static __device__ __forceinline__ uint32_t fix(uint32_t raw) { return __byte_perm(raw, 0, 0x0123); }
+    __device__ __forceinline__ uint32_t word_checked(uint32_t w) {
+        if (w >= ready) {
+            fill(w);
+            wait_for(w + 1);
+        }
+        return word(w);
+    }
+};
+
+}  // namespace zf
