@@ -31,6 +31,8 @@ struct HostSrc {
         if (w >= guaranteed || w < consumed_below) ++violations;
         return raw(w);
     }
+    static constexpr uint32_t kWordScale = 512;  // like the device ring of a 128-thread CTA
+    __host__ __device__ uint32_t word_scaled(uint32_t ws) { return word(ws / kWordScale); }
     __host__ __device__ uint32_t word_checked(uint32_t w) {
         if (w > consumed_below) consumed_below = w;  // the device refills with `words < w are consumed`
         return raw(w);
@@ -94,13 +96,16 @@ int zf_host_parse_frame(const uint8_t *stream, const zf::FrameRec *fr, int32_t *
 
 // Scalar restatement of what pass B (predict.cu) does to one scratch plane: predictor recurrence in
 // place, then the wasted-bits shift. Test-side stand-in for the CUDA kernel (the -m gpu tests pin the kernel).
-void zf_host_predict_plane(const zf::SubRec *sub, int32_t *plane, uint32_t block_size) {
+// `frame` is the frame's scratch in the sub_idx() layout of parse_core.cuh; the result goes to plane[0..block_size).
+void zf_host_predict_plane(const zf::SubRec *sub, const int32_t *frame, uint32_t ch, uint32_t channels, uint32_t block_size,
+                           int32_t *plane) {
+    const uint32_t c8 = 8 * channels;
     for (uint32_t i = 0; i < block_size; ++i) {
         int32_t v;
         if (sub->kind == zf::kSubConst) {
             v = sub->constant;
         } else {
-            v = plane[i];
+            v = frame[ch * 8 + zf::sub_idx(i, c8)];
             if (sub->kind == zf::kSubPred && i >= sub->order) {
                 int64_t acc = 0;
                 for (uint32_t j = 0; j < sub->order; ++j) acc += (int64_t)sub->coef[j] * (int64_t)plane[i - 1 - j];

@@ -44,7 +44,7 @@ def core():
     assert lib.zf_host_framerec_size() == FRAME_REC.itemsize
     lib.zf_host_parse_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     lib.zf_host_parse_frame.restype = C.c_int
-    lib.zf_host_predict_plane.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    lib.zf_host_predict_plane.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
     lib.zf_host_predict_plane.restype = None
     assert lib.zf_host_subrec_size() == 80
     return lib
@@ -74,8 +74,10 @@ def host_decode(lib, data: bytes, ref, two_pass: bool = False):
             subs = np.zeros(8 * 80, dtype=np.uint8)
             viol = lib.zf_host_parse_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, subs.ctypes.data, 1, out.ctypes.data)
             if int(out["status"][0]) == 0:
+                planar = np.zeros(pitch * ch, dtype=np.int32)
                 for c in range(ch):
-                    lib.zf_host_predict_plane(subs.ctypes.data + 80 * c, scratch.ctypes.data + 4 * pitch * c, bs)
+                    lib.zf_host_predict_plane(subs.ctypes.data + 80 * c, scratch.ctypes.data, c, ch, bs, planar.ctypes.data + 4 * pitch * c)
+                scratch = planar
         else:
             viol = lib.zf_host_decode_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, int(wide), 1, out.ctypes.data)
         assert viol == 0, "unchecked word read beyond the top_up guarantee"

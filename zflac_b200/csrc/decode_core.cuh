@@ -46,6 +46,16 @@ ZF_HD uint32_t clz32(uint32_t v) {
     return v ? (uint32_t)__builtin_clz(v) : 32u;
 #endif
 }
+// leading zeros as a shift amount; 0xFFFFFFFF for v == 0 (one FLO.SH instead of FLO + subtract)
+ZF_HD uint32_t clz_sh(uint32_t v) {
+#ifdef __CUDA_ARCH__
+    uint32_t r;
+    asm("bfind.shiftamt.u32 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+#else
+    return v ? (uint32_t)__builtin_clz(v) : 0xFFFFFFFFu;
+#endif
+}
 ZF_HD uint32_t shr_c(uint32_t v, uint32_t n) {  // n >= 32 -> 0
 #ifdef __CUDA_ARCH__
     uint32_t r;
@@ -74,7 +84,15 @@ ZF_HD uint32_t funnel_hi(uint32_t hi, uint32_t lo, uint32_t s) {
 #endif
 }
 ZF_HD uint32_t ceil_log2(uint32_t v) { return v <= 1 ? 0 : 32 - clz32(v - 1); }
-ZF_HD int32_t zigzag(uint32_t u) { return (int32_t)((u >> 1) ^ (0u - (u & 1u))); }
+ZF_HD int32_t zigzag(uint32_t u) {
+#ifdef __CUDA_ARCH__
+    int32_t m;  // sign-extend bit 0: one SGXT instead of AND + negate
+    asm("bfe.s32 %0, %1, 0, 1;" : "=r"(m) : "r"(u));
+    return (int32_t)(u >> 1) ^ m;
+#else
+    return (int32_t)((u >> 1) ^ (0u - (u & 1u)));
+#endif
+}
 
 // ---------------------------------------------------------------------------------------
 // Src concept (word index w counts 32-bit big-endian stream words from the source origin):
@@ -102,6 +120,14 @@ struct BitReader {
         N = src.word_checked(2);
         next = 3;
         o = 8 * skip_bytes;
+    }
+    ZF_HD void init_at(uint32_t skip_bytes) {  // any byte offset from word 0
+        const uint32_t w = skip_bytes >> 2;
+        A = Src::fix(src.word_checked(w));
+        B = Src::fix(src.word_checked(w + 1));
+        N = src.word_checked(w + 2);
+        next = w + 3;
+        o = 8 * (skip_bytes & 3u);
     }
     ZF_HD uint64_t pos_bits() const { return (uint64_t)(next - 3) * 32 + o; }
     ZF_HD uint32_t peek() const { return funnel_hi(A, B, o); }
@@ -158,6 +184,32 @@ struct BitReader {
             skip<true>(32);
             if (pos_bits() > len_bits) return 0xFFFFFFFFu;
         }
+    }
+    // Branch-free advance of the fast 8-row bodies, n < 2^31 (garbage lengths of a body that is rolled
+    // back included): one word step at most, every update a predicated single instruction. Inside a
+    // body the word cursor is carried pre-scaled for the source's ring (ws = (next - 1) * Src::kWordScale):
+    // enter_fast() / leave_fast() convert.
+    ZF_HD uint32_t enter_fast() const { return (next - 1) * Src::kWordScale; }
+    ZF_HD void leave_fast(uint32_t ws) { next = ws / Src::kWordScale + 1; }
+    ZF_HD void skip_fast(uint32_t n, uint32_t &ws) {
+        o += n;
+#ifdef __CUDA_ARCH__
+        asm("{\n\t.reg .pred p;\n\t"
+            "setp.gt.u32 p, %0, 31;\n\t"
+            "and.b32 %0, %0, 31;\n\t"
+            "@p mov.b32 %1, %2;\n\t"
+            "@p prmt.b32 %2, %3, 0, 0x0123;\n\t"
+            "@p add.u32 %4, %4, %5;\n\t}"
+            : "+r"(o), "+r"(A), "+r"(B), "+r"(N), "+r"(ws)
+            : "n"(Src::kWordScale));
+#else
+        const bool wrap = o >= 32;
+        o &= 31u;
+        A = wrap ? B : A;
+        B = wrap ? Src::fix(N) : B;
+        ws = wrap ? ws + Src::kWordScale : ws;
+#endif
+        N = src.word_scaled(ws);
     }
     ZF_HD void align_byte() { skip<true>((8u - (o & 7u)) & 7u); }  // word starts are byte aligned
     // N (word next-1) is re-read by the branch-free skip: it still counts as live

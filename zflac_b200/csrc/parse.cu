@@ -3,8 +3,7 @@
 // partitions; reference src/zflac.zig:425-551, :614-666 and src/bit_reader.zig) and leaves the raw
 // material of every subframe in HBM: residuals / warm-up / verbatim samples in the planar int32
 // scratch, one SubRec per subframe. The predictor recurrence itself runs in pass B (predict.cu),
-// one lane per subframe. The logic is parse_core.cuh; the word source is the cp.async ring of
-// ring_src.cuh.
+// one lane per subframe. The logic is parse_core.cuh; the word source is StagedSrc of ring_src.cuh.
 #include "kernels.cuh"
 #include "parse_core.cuh"
 #include "ring_src.cuh"
@@ -20,16 +19,18 @@ k_parse_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frame
     const FrameRec fr = frames[f];
     if (fr.block_size == 0) return;  // dropped candidate slot
     const uint64_t start = fr.offset + fr.header_len;  // first subframe header
-    const uint64_t origin = start & ~3ull;             // word 0 of the lane's source
-    BitReader<RingSrc<kDecodeThreads>> br;
-    br.src.init(s + origin, fr.stream_end > origin ? fr.stream_end - origin : 0, threadIdx.x);
-    br.init((uint32_t)(start & 3));
-    const uint64_t len_bits = (fr.stream_end > origin ? fr.stream_end - origin : 0) * 8;
+    // word 0 of the lane's source: the 16-byte aligned ADDRESS at or below the first subframe header
+    const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(s + start) & 15u);
+    const uint64_t origin = start - lead;  // may reach up to 15 bytes below offset 0 of an unaligned buffer (same allocation)
+    const uint64_t span = fr.stream_end > start ? fr.stream_end - start + lead : 0;
+    BitReader<StagedSrc<kDecodeThreads>> br;
+    br.src.init(s + start - lead, span, threadIdx.x);
+    br.init_at(lead);
+    const uint64_t len_bits = span * 8;
     FrameOut o;
     uint32_t max_order = 0;
     parse_frame(br, fr, scratch, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order);
     if (max_order > 12 && write_samples) *big_orders = 1u;  // pass B then also runs its 32-tap kernel
-    asm volatile("cp.async.wait_group 0;" ::: "memory");  // nothing may land in the ring after the CTA retires
     outs[f] = o;
 }
 

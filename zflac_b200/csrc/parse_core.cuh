@@ -32,10 +32,18 @@ struct SubRec {
 static_assert(sizeof(SubRec) == 80, "SubRec layout");
 enum : uint8_t { kSubRaw = 0, kSubConst = 1, kSubPred = 2 };
 
+// Scratch layout of the two-pass path: per frame, groups of 8 time steps; inside a group the
+// channels one after another, 8 consecutive values each:
+//     element(frame, ch, i) = scratch_base + (i / 8) * 8 * C + ch * 8 + (i % 8)
+// Pass A writes 32 bytes (one sector) per lane and 8-row body either way; in pass B the C lanes of a
+// frame then read C adjacent sectors per step instead of C far-apart ones. Same size as C planes of
+// pitch roundup8(block_size).
+ZF_HD uint32_t sub_idx(uint32_t i, uint32_t c8) { return (i >> 3) * c8 + (i & 7u); }
+
 // Residual of a FIXED / LPC subframe (:614-666) into out[order .. block_size): the Rice loop of
 // decode_core.cuh without the predictor.
 template <class Src>
-ZF_HDI uint32_t parse_residual(BitReader<Src> &br, int32_t *__restrict__ out, uint32_t order, uint32_t block_size,
+ZF_HDI uint32_t parse_residual(BitReader<Src> &br, int32_t *__restrict__ out, uint32_t c8, uint32_t order, uint32_t block_size,
                                uint64_t len_bits, bool wr) {
     const uint32_t method = br.read(2);
     if (method >= 2) return ST_INVALID_RESIDUAL_CODING_METHOD;
@@ -54,39 +62,46 @@ ZF_HDI uint32_t parse_residual(BitReader<Src> &br, int32_t *__restrict__ out, ui
 #pragma unroll 1
             for (; i < end; ++i) {
                 const int32_t r = esc ? br.read_signed(esc) : 0;
-                if (wr) out[i] = r;
+                if (wr) out[sub_idx(i, c8)] = r;
                 if ((i & 255u) == 255u && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
             }
         } else {
-            const uint32_t k = param, kp1 = param + 1, rsh = 32 - param;
+            const uint32_t k = param, kp1 = param + 1;
+            uint32_t pk = 1u << param;
+#ifdef __CUDA_ARCH__
+            asm("" : "+r"(pk));  // keep z * pk an IMAD (FMA pipe): the ALU pipe carries the bit chain
+#endif
             uint32_t force_single = 0;
 #pragma unroll 1
             while (i < end) {
                 if (force_single == 0 && (i & 7u) == 0 && i + 8 <= end) {
                     // 8 codewords, speculative and branch-free; a codeword longer than the 32-bit window
-                    // (rare) only raises nmax: the body is rolled back and redone row by row
+                    // (rare) only raises zmax: the body is rolled back and redone row by row
                     br.prepare_fast();
-                    const uint32_t sA = br.A, sB = br.B, sN = br.N, so = br.o, snext = br.next;
-                    uint32_t nmax = 0;
+                    const uint32_t sA = br.A, sB = br.B, sN = br.N, so = br.o;
+                    uint32_t ws = br.enter_fast();
+                    uint32_t zmax = 0;
                     int32_t r[8];
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {
                         const uint32_t win = br.peek();
-                        const uint32_t z = clz32(win);
-                        const uint32_t n = z + kp1;
-                        nmax = nmax > n ? nmax : n;
-                        const uint32_t cw = (z << k) | shr_c(shl_c(win, z + 1), rsh);
-                        br.template skip<false>(n & 63u);
+                        const uint32_t z = clz_sh(win);                                   // unary part (0xFFFFFFFF: no stop bit in sight)
+                        zmax = zmax > z ? zmax : z;
+                        const uint32_t low = funnel_hi(0u, shl_c(win, z + 1), k);        // the k bits after the stop bit
+                        const uint32_t cw = z * pk + low;                                 // (z << k) | low on the IMAD pipe
+                        br.skip_fast(z + kp1, ws);
                         r[u] = zigzag(cw);
                     }
-                    if (nmax <= 32u) {
+                    if (zmax <= 31u - k) {  // every codeword fitted the 32-bit window
                         if (wr) {
-                            *reinterpret_cast<int4 *>(out + i) = make_int4(r[0], r[1], r[2], r[3]);
-                            *reinterpret_cast<int4 *>(out + i + 4) = make_int4(r[4], r[5], r[6], r[7]);
+                            int32_t *dst = out + (size_t)(i >> 3) * c8;  // i is a multiple of 8
+                            *reinterpret_cast<int4 *>(dst) = make_int4(r[0], r[1], r[2], r[3]);
+                            *reinterpret_cast<int4 *>(dst + 4) = make_int4(r[4], r[5], r[6], r[7]);
                         }
+                        br.leave_fast(ws);
                         i += 8;
                     } else {
-                        br.A = sA; br.B = sB; br.N = sN; br.o = so; br.next = snext;
+                        br.A = sA; br.B = sB; br.N = sN; br.o = so;
                         br.src.note_rollback();
                         force_single = 8;
                     }
@@ -96,12 +111,12 @@ ZF_HDI uint32_t parse_residual(BitReader<Src> &br, int32_t *__restrict__ out, ui
                     const uint32_t n = z + kp1;
                     uint32_t cw;
                     if (n <= 32) {
-                        cw = (z << k) | shr_c(shl_c(win, z + 1), rsh);
+                        cw = (z << k) | shr_c(shl_c(win, z + 1), 32 - k);
                         br.template skip<true>(n);
                     } else {
                         cw = rice_slow(br, k, len_bits, err);
                     }
-                    if (wr) out[i] = zigzag(cw);
+                    if (wr) out[sub_idx(i, c8)] = zigzag(cw);
                     ++i;
                     if (force_single) --force_single;
                     if (err != ST_OK) return err;
@@ -139,7 +154,8 @@ ZF_HDI void parse_frame(BitReader<Src> &br, const FrameRec &fr, int32_t *__restr
         }
         uint32_t depth = bps;  // :436-441
         if ((fr.ch_code == 8 && ch == 1) || (fr.ch_code == 9 && ch == 0) || (fr.ch_code == 10 && ch == 1)) depth += 1;
-        int32_t *out = scratch + fr.scratch_base + (uint64_t)ch * fr.scratch_pitch;
+        int32_t *out = scratch + fr.scratch_base + ch * 8u;  // sub_idx() layout
+        const uint32_t c8 = 8u * fr.channels;
         SubRec *sub = subs + ch;
         uint32_t kind = kSubRaw, order = 0, shift = 0, wide_acc = 0;
         int32_t constant = 0;
@@ -154,7 +170,7 @@ ZF_HDI void parse_frame(BitReader<Src> &br, const FrameRec &fr, int32_t *__restr
 #pragma unroll 1
             for (uint32_t i = 0; i < bs; ++i) {
                 const int32_t v = br.read_signed(n);
-                if (wr) out[i] = v;
+                if (wr) out[sub_idx(i, c8)] = v;
                 if ((i & 255u) == 255u && br.pos_bits() > len_bits) break;  // ran off the stream
             }
         } else if ((type >= 8 && type <= 12) || type >= 32) {  // FIXED (:466-498) / LPC (:499-541)
@@ -167,7 +183,7 @@ ZF_HDI void parse_frame(BitReader<Src> &br, const FrameRec &fr, int32_t *__restr
 #pragma unroll 1
             for (uint32_t t = 0; t < order; ++t) {  // warm-up samples (:473-479, :501-507)
                 const int32_t v = br.read_signed(eff);
-                if (wr) out[t] = v;
+                if (wr) out[sub_idx(t, c8)] = v;
             }
             if (is_lpc) {
                 const uint32_t precision = br.read(4) + 1;  // :508 (0b1111 is not rejected by the reference)
@@ -185,7 +201,7 @@ ZF_HDI void parse_frame(BitReader<Src> &br, const FrameRec &fr, int32_t *__restr
                     for (int j = 0; j < 4; ++j) sub->coef[j] = (int16_t)fixed_coef(order, j);
                 }
             }
-            status = parse_residual(br, out, order, bs, len_bits, wr);
+            status = parse_residual(br, out, c8, order, bs, len_bits, wr);
         } else {  // reserved (:542)
             status = ST_INVALID_SUBFRAME_HEADER;
         }

@@ -49,6 +49,12 @@ struct RingSrc {
         col = (uint32_t)__cvta_generic_to_shared(&zf_ring[column]);
         filled = ready = h0 = h1 = h2 = 0;
     }
+    static constexpr uint32_t kWordScale = NT * 4;  // byte distance of consecutive words of a lane in the ring
+    __device__ __forceinline__ uint32_t word_scaled(uint32_t ws) const {  // ws = word index * kWordScale
+        uint32_t v;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(col + (ws & ((kRingWords - 1) * kWordScale))));
+        return v;
+    }
     __device__ __forceinline__ uint32_t slot(uint32_t w) const { return col + (w & (kRingWords - 1)) * (NT * 4); }
     __device__ __forceinline__ void issue(uint32_t w) {
         const uint32_t dst = slot(w);
@@ -93,6 +99,76 @@ struct RingSrc {
             fill(w);
             wait_for(w + 1);
         }
+        return word(w);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// StagedSrc — word source of K2a parse_frames. Same ring (word w of lane L at ring[w % kRingWords][L],
+// bank-conflict free), filled 16 bytes at a time THROUGH REGISTERS: one 128-bit global load per four
+// words, issued one refill ahead of its four shared stores, so the bit chain never waits on it and
+// no cp.async group bookkeeping is needed (a lane's shared loads follow its own shared stores in
+// program order). Word 0 sits at a 16-byte aligned global address.
+// ---------------------------------------------------------------------------------------------
+template <int NT>
+struct StagedSrc {
+    const uint8_t *g;    // global address of word 0 (16-byte aligned)
+    uint32_t avail;      // bytes readable from g (stream end), clamped
+    uint32_t col;        // shared-space byte address of zf_ring[lane column]
+    uint32_t staged;     // words < staged are in the ring; words [staged, staged + 4) are in q (possibly still in flight)
+    uint4 q;
+
+    static constexpr uint32_t kWordScale = NT * 4;  // byte distance of consecutive words of a lane in the ring
+    __device__ __forceinline__ uint32_t word_scaled(uint32_t ws) const {  // ws = word index * kWordScale
+        uint32_t v;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(col + (ws & ((kRingWords - 1) * kWordScale))) : "memory");
+        return v;
+    }
+    __device__ __forceinline__ uint32_t slot(uint32_t w) const { return col + (w & (kRingWords - 1)) * (NT * 4); }
+    __device__ __forceinline__ void load_quad(uint32_t w) {  // words [w, w + 4) -> q; bytes past the stream end read as zero
+        const uint32_t off = w * 4u;
+        if (off + 16u <= avail) {
+            q = __ldg(reinterpret_cast<const uint4 *>(g + off));
+        } else {
+            uint32_t v[4] = {0, 0, 0, 0};
+            for (uint32_t b = 0; b < 16; ++b)
+                if (off + b < avail) v[b >> 2] |= (uint32_t)g[off + b] << (8 * (b & 3));
+            q = make_uint4(v[0], v[1], v[2], v[3]);
+        }
+    }
+    __device__ __forceinline__ void init(const uint8_t *base, uint64_t bytes, uint32_t column) {
+        g = base;
+        avail = bytes > 0xFFFFFFE0ull ? 0xFFFFFFE0u : (uint32_t)bytes;
+        col = (uint32_t)__cvta_generic_to_shared(&zf_ring[column]);
+        staged = 0;
+        load_quad(0);
+    }
+    __device__ __forceinline__ void flush_and_load() {  // q -> ring, then start loading the next four words
+        const uint32_t a = slot(staged);  // staged is a multiple of 4: the four slots do not wrap
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(q.x) : "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(a + NT * 4), "r"(q.y) : "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(a + NT * 8), "r"(q.z) : "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(a + NT * 12), "r"(q.w) : "memory");
+        staged += 4;
+        load_quad(staged);
+    }
+    // words < cur are consumed; afterwards words [cur, cur + kFastWords) are resident
+    __device__ __forceinline__ void top_up(uint32_t cur) {
+        if (staged + 4 <= cur + kRingWords && staged < cur + 24) flush_and_load();
+        if (staged + 4 <= cur + kRingWords && staged < cur + 16) flush_and_load();
+#pragma unroll 1
+        while (staged < cur + kFastWords) flush_and_load();
+    }
+    __device__ __forceinline__ uint32_t word(uint32_t w) const {
+        uint32_t v;  // volatile: stays ordered against the shared stores of flush_and_load
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(slot(w)) : "memory");
+        return v;
+    }
+    __device__ __forceinline__ void note_rollback() {}
+    static __device__ __forceinline__ uint32_t fix(uint32_t raw) { return __byte_perm(raw, 0, 0x0123); }
+    __device__ __forceinline__ uint32_t word_checked(uint32_t w) {
+#pragma unroll 1
+        while (w >= staged) flush_and_load();
         return word(w);
     }
 };
