@@ -199,15 +199,16 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
 #pragma unroll
         for (int u = 0; u < 8; ++u) o[u] = (int32_t)((uint32_t)y[u] << wasted);
         if (stereo) {  // warp-uniform: every lane takes part in the shuffles
+            int32_t p[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const int32_t s = o[u];
-                const int32_t p = __shfl_xor_sync(0xFFFFFFFFu, s, 1);
-                if (!wide_pair) {
-                    o[u] = (da * s + db * p + ((p & mp) | (s & ms))) >> dsh;
-                } else {  // 29..31-bit streams: the mid/side sum needs more than 32 bits
-                    o[u] = (int32_t)(((int64_t)da * s + (int64_t)db * p + (int64_t)((p & mp) | (s & ms))) >> dsh);
-                }
+            for (int u = 0; u < 8; ++u) p[u] = __shfl_xor_sync(0xFFFFFFFFu, o[u], 1);
+            if (!wide_pair) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) o[u] = (da * o[u] + db * p[u] + ((p[u] & mp) | (o[u] & ms))) >> dsh;
+            } else {  // 29..31-bit streams: the mid/side sum needs more than 32 bits
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    o[u] = (int32_t)(((int64_t)da * o[u] + (int64_t)db * p[u] + (int64_t)((p[u] & mp) | (o[u] & ms))) >> dsh);
             }
         }
         if (msb_shift != 0) {

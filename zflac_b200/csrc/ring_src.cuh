@@ -103,6 +103,14 @@ struct RingSrc {
     }
 };
 
+// the last bytes of a stream (rare): byte-wise, zero past the end
+static __device__ __noinline__ uint4 staged_tail_quad(const uint8_t *g, uint32_t off, uint32_t avail) {
+    uint32_t v[4] = {0, 0, 0, 0};
+    for (uint32_t b = 0; b < 16; ++b)
+        if (off + b < avail) v[b >> 2] |= (uint32_t)g[off + b] << (8 * (b & 3));
+    return make_uint4(v[0], v[1], v[2], v[3]);
+}
+
 // ---------------------------------------------------------------------------------------------
 // StagedSrc — word source of K2a parse_frames. Same ring (word w of lane L at ring[w % kRingWords][L],
 // bank-conflict free), filled 16 bytes at a time THROUGH REGISTERS: one 128-bit global load per four
@@ -129,11 +137,11 @@ struct StagedSrc {
         const uint32_t off = w * 4u;
         if (off + 16u <= avail) {
             q = __ldg(reinterpret_cast<const uint4 *>(g + off));
+            // a lane streams through its frame: pull the line two ahead into L1 once per 128-byte line, so the
+            // quad loads above are L1 hits when their turn comes (the ring itself only looks 16..32 bytes ahead)
+            if ((w & 31u) == 0 && off + 384u <= avail) asm volatile("prefetch.global.L1 [%0];" ::"l"(g + off + 256u));
         } else {
-            uint32_t v[4] = {0, 0, 0, 0};
-            for (uint32_t b = 0; b < 16; ++b)
-                if (off + b < avail) v[b >> 2] |= (uint32_t)g[off + b] << (8 * (b & 3));
-            q = make_uint4(v[0], v[1], v[2], v[3]);
+            q = staged_tail_quad(g, off, avail);
         }
     }
     __device__ __forceinline__ void init(const uint8_t *base, uint64_t bytes, uint32_t column) {
@@ -141,6 +149,7 @@ struct StagedSrc {
         avail = bytes > 0xFFFFFFE0ull ? 0xFFFFFFE0u : (uint32_t)bytes;
         col = (uint32_t)__cvta_generic_to_shared(&zf_ring[column]);
         staged = 0;
+        if (avail >= 256u) asm volatile("prefetch.global.L1 [%0];" ::"l"(g + 128u));
         load_quad(0);
     }
     __device__ __forceinline__ void flush_and_load() {  // q -> ring, then start loading the next four words
