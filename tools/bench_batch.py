@@ -218,7 +218,7 @@ def run(args, rank, world, local_rank, metric, ClockSampler, measured_peak):
         "compressed_gbs": round(job_flac / (ms_dev * 1e-3) / 1e9, 3),
         "kernel_ms": {f: round(v, 4) for f, v in k.items()},
         "parity": "every file bit-exact vs the generator's PCM, MD5 == STREAMINFO on the device (checked on this run)",
-        "roofline": {"bound": "hbm", "kernel": {"ms_decode": "k_decode_frames", "ms_epilogue": "k_epilogue", "ms_scan": "k_sync_scan",
+        "roofline": {"bound": "hbm", "kernel": {"ms_decode": "k_parse_frames", "ms_epilogue": "k_predict_epilogue", "ms_scan": "k_sync_scan",
                                                "ms_md5": "k_md5"}[dom],
                      "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": None,
                      "peak_source": peak_src, "algorithmic_bytes": algo_bytes, "kernel_ms": round(k[dom], 4)},

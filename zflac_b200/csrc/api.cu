@@ -38,6 +38,11 @@ struct DeviceCtx {
     cudaStream_t stream = nullptr;
     cudaStream_t side = nullptr;  // diagnostics that overlap the main pipeline (per-frame CRC-16)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // zflacb200_decode pipeline: upload / read-back streams (both PCIe directions at once) and a pinned mailbox
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    static constexpr int kLanes = 8;        // chunks in flight: a chunk's kernels are latency-bound, several run side by side
+    cudaStream_t lane[kLanes] = {};
+    unsigned long long *mailbox = nullptr;  // pinned host: [0] candidates of the chunk, [2 + i] PCM elements ready after chunk i
 };
 DeviceCtx g_ctx[64];
 
@@ -110,6 +115,10 @@ int ensure_device(int device, int *resolved) {
         CU_CHECK(cudaStreamCreateWithFlags(&c.side, cudaStreamNonBlocking));
         CU_CHECK(cudaEventCreateWithFlags(&c.ev_fork, cudaEventDisableTiming));
         CU_CHECK(cudaEventCreateWithFlags(&c.ev_join, cudaEventDisableTiming));
+        CU_CHECK(cudaStreamCreateWithFlags(&c.copy_in, cudaStreamNonBlocking));
+        CU_CHECK(cudaStreamCreateWithFlags(&c.copy_out, cudaStreamNonBlocking));
+        for (auto &l : c.lane) CU_CHECK(cudaStreamCreateWithFlags(&l, cudaStreamNonBlocking));
+        CU_CHECK(cudaHostAlloc((void **)&c.mailbox, 8 * (2 + 4096), cudaHostAllocDefault));
         CU_CHECK(scan_init_constants());
         cudaMemPool_t pool;
         CU_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
@@ -476,15 +485,18 @@ struct SubframeStage {
         CU_CHECK(cudaMemsetAsync(b_big.p, 0, sizeof(uint32_t), st));
         return ZFLACB200_OK;
     }
+    // d_recs / d_outs point at record `first` of the prepared range (chunked decode), n records from there
     int decode(const uint8_t *d_stream, const FrameRec *d_recs, uint32_t n, void *d_scratch, bool wide, FrameOut *d_outs, bool write,
-               cudaStream_t st) {
+               cudaStream_t st, uint32_t first = 0) {
         if (two_pass)
-            CU_CHECK(launch_parse_frames(d_stream, d_recs, n, (int32_t *)d_scratch, (SubRec *)b_subs.p, d_outs, (uint32_t *)b_big.p, write, st));
+            CU_CHECK(launch_parse_frames(d_stream, d_recs, n, (int32_t *)d_scratch,
+                                         (SubRec *)((uint8_t *)b_subs.p + kSubRecBytes * 8 * (size_t)first), d_outs, (uint32_t *)b_big.p,
+                                         write, st));
         else
             CU_CHECK(launch_decode_frames(d_stream, d_recs, n, d_scratch, wide, d_outs, write, st));
         return ZFLACB200_OK;
     }
-    int epilogue(const EpilogueParams &ep, const FrameOut *d_outs, uint32_t max_channels, cudaStream_t st) {
+    int epilogue(const EpilogueParams &ep, const FrameOut *d_outs, uint32_t max_channels, cudaStream_t st, uint32_t first = 0) {
         if (!two_pass) {
             CU_CHECK(launch_epilogue(ep, st));
             return ZFLACB200_OK;
@@ -495,7 +507,7 @@ struct SubframeStage {
         pp.n_frames = ep.n_frames;
         pp.max_channels = max_channels;
         pp.scratch = ep.scratch;
-        pp.subs = b_subs.p;
+        pp.subs = (const uint8_t *)b_subs.p + kSubRecBytes * 8 * (size_t)first;
         pp.pcm = ep.pcm;
         pp.container_bytes = ep.container_bytes;
         pp.msb_shift = ep.msb_shift;
@@ -1227,6 +1239,243 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
     return ZFLACB200_OK;
 }
 
+
+// ------------------------------------------------------------------ zflacb200_decode, pipelined
+// Host stream in, host PCM out: the stream is uploaded in chunks and every chunk runs the fast path
+// (scan -> hinted frame records -> K2a/K3p) as soon as it and its successor have landed, while later
+// chunks are still on the wire and the PCM of earlier chunks already travels back — both PCIe
+// directions and the SMs busy at once. The hinted chain makes chunks independent (a frame's PCM offset
+// comes from its coded number); the chain rules are verified over ALL frames at the end exactly as in
+// run_fast_group, and anything unexpected (chain not accepted, more candidates than planned, a lossy
+// MSB shift, a destination that is too small) returns kNotPipelined: the caller then decodes the
+// stream the plain way, which overwrites whatever was already copied out.
+constexpr int kNotPipelined = -1;
+
+struct EventList {
+    std::vector<cudaEvent_t> v;
+    int make(size_t n) {
+        v.assign(n, nullptr);
+        for (auto &e : v) CU_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        return ZFLACB200_OK;
+    }
+    ~EventList() {
+        for (auto e : v)
+            if (e) cudaEventDestroy(e);
+    }
+};
+
+int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *opt, void *dst, size_t dst_capacity,
+                     zflacb200_info *info) {
+    const uint32_t flags = (opt ? opt->flags : 0) | env_flags();
+    if (flags & (ZFLACB200_INPUT_ON_DEVICE | ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL | ZFLACB200_NO_PIPELINE)) return kNotPipelined;
+    // test knobs: ZFLACB200_PIPELINE_MIN_BYTES (default 48 MiB), ZFLACB200_PIPELINE_CHUNK (default: len / 24, >= 8 MiB)
+    static const uint64_t min_bytes = [] { const char *e = getenv("ZFLACB200_PIPELINE_MIN_BYTES"); return e ? strtoull(e, nullptr, 0) : (48ull << 20); }();
+    static const uint64_t env_chunk = [] { const char *e = getenv("ZFLACB200_PIPELINE_CHUNK"); return e ? strtoull(e, nullptr, 0) : 0ull; }();
+    if (!data || !dst || !info || len < min_bytes || len < 4096) return kNotPipelined;  // short streams: nothing to overlap
+    int device = -1;
+    if (ensure_device(opt ? opt->device : -1, &device) != ZFLACB200_OK) return kNotPipelined;
+    DeviceCtx &ctx = g_ctx[device];
+    cudaStream_t st = (opt && opt->stream) ? (cudaStream_t)opt->stream : ctx.stream;
+    HostTrace tr("decode_pipelined");
+
+    ByteSource src;
+    src.host = data;
+    src.len = len;
+    Streaminfo si;
+    uint64_t audio_offset = 0;
+    if (parse_metadata(src, si, audio_offset) != ZFLACB200_OK) return kNotPipelined;  // the plain path reports the error
+    const uint32_t C = si.channels_m1 + 1;
+    const uint32_t depth = si.depth_m1 + 1, aligned = (depth + 7u) & ~7u;
+    const uint32_t cb = aligned == 8 ? 1 : aligned == 16 ? 2 : 4;
+    uint32_t msb_shift = 0;
+    if (depth >= 9 && depth <= 15) msb_shift = 16 - depth;
+    else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
+    if (si.total == 0 || si.total * C >= (1ull << 40)) return kNotPipelined;
+    const uint64_t n_elems = si.total * C, pcm_bytes = n_elems * cb;
+    if (dst_capacity < pcm_bytes) return kNotPipelined;
+    bool wide = false;
+    {
+        Hdr h0;
+        if (host_parse_header(src, audio_offset, h0) != ZFLACB200_OK) return kNotPipelined;
+        wide = (h0.bd_code == 0 ? depth : kBps[h0.bd_code]) == 32;
+    }
+    const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0;
+
+    // ---- chunks: >= 8 MiB (a frame is < 2.1 MB: one that starts in chunk i ends inside chunk i + 1), about 24 of them
+    uint64_t chunk = std::max<uint64_t>(8ull << 20, (len / 24 + 0xFFFF) & ~0xFFFFull);
+    if (env_chunk >= 4096) chunk = (env_chunk + 15) & ~15ull;  // a frame longer than a chunk only costs the fallback
+    if (audio_offset >= chunk) return kNotPipelined;
+    const uint32_t K = (uint32_t)((len + chunk - 1) / chunk);
+    std::vector<uint64_t> b(K + 1);
+    for (uint32_t i = 0; i <= K; ++i) b[i] = std::min<uint64_t>(len, (uint64_t)i * chunk);
+    b[0] = audio_offset;
+
+    // ---- device buffers for the whole stream
+    const uint32_t min_bs = std::max<uint32_t>(si.min_block, 16);
+    const uint64_t cap64 = (si.total / min_bs + 64) * 5 / 4 + 4096;  // frames by STREAMINFO + room for false candidates
+    if (cap64 > 0x3FFFFFFFull || K > 4096) return kNotPipelined;
+    const uint32_t cap = (uint32_t)cap64;
+    constexpr int S = DeviceCtx::kLanes;
+    const uint32_t chunk_tiles = scan_tile_count(0, chunk + 64) + 2;
+    const uint64_t scratch_elems = (uint64_t)C * (((si.total + 7) & ~7ull) + 8) + 64ull * cap + 64;
+    DevBuf b_stream, b_cands, b_total, b_tiles, b_ticket, b_sd, b_recs, b_outs, b_ok, b_scratch, b_pcm, b_sum, b_flag, b_hi, b_jobs, b_digest;
+    SubframeStage stage;
+    if (b_stream.alloc(((len + 15) & ~15ull) + 64, st) || b_cands.alloc(sizeof(Cand) * (size_t)cap, st) ||
+        b_total.alloc(sizeof(uint32_t), st) || b_tiles.alloc(sizeof(unsigned long long) * chunk_tiles, st) ||
+        b_ticket.alloc(sizeof(uint32_t), st) || b_sd.alloc(sizeof(StreamDesc), st) || b_recs.alloc(sizeof(FrameRec) * (size_t)cap, st) ||
+        b_outs.alloc(sizeof(FrameOut) * (size_t)cap, st) || b_ok.alloc(cap, st) || b_scratch.alloc(scratch_elems * (wide ? 8 : 4), st) ||
+        b_pcm.alloc(((n_elems + 15) & ~15ull) * cb + 64, st) || b_sum.alloc(sizeof(StreamSummary), st) ||
+        b_flag.alloc(sizeof(uint32_t), st) || b_hi.alloc(sizeof(unsigned long long) * K, st) || b_jobs.alloc(sizeof(Md5Job), st) ||
+        b_digest.alloc(16, st) || stage.prepare(wide, flags, cap, st) != ZFLACB200_OK)
+        return ZFLACB200_CUDA_ERROR;
+    StreamDesc sd;
+    memset(&sd, 0, sizeof(sd));
+    sd.begin = 0;
+    sd.end = len;
+    sd.audio_begin = audio_offset;
+    sd.total = si.total;
+    sd.si_sample_rate = si.sample_rate;
+    sd.si_channels = (uint8_t)C;
+    sd.si_depth = (uint8_t)depth;
+    EventList ev_in, ev_hint, ev_done;
+    Events ev;
+    if (ev_in.make(K) || ev_hint.make(K) || ev_done.make(K) || ev.init()) return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(cudaMemcpyAsync(b_sd.p, &sd, sizeof(sd), cudaMemcpyHostToDevice, st));
+    CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary), st));
+    CU_CHECK(cudaMemsetAsync(b_ok.p, 2, cap, st));
+    CU_CHECK(cudaMemsetAsync(b_flag.p, 0, sizeof(uint32_t), st));
+    CU_CHECK(cudaMemsetAsync(b_hi.p, 0, sizeof(unsigned long long) * K, st));
+    CU_CHECK(cudaEventRecord(ev.e[0], st));
+    CU_CHECK(cudaEventRecord(ctx.ev_fork, st));  // the buffers above are stream-ordered allocations of `st`
+    CU_CHECK(cudaStreamWaitEvent(ctx.copy_in, ctx.ev_fork, 0));
+    CU_CHECK(cudaStreamWaitEvent(ctx.copy_out, ctx.ev_fork, 0));
+    for (auto &l : ctx.lane) CU_CHECK(cudaStreamWaitEvent(l, ctx.ev_fork, 0));
+    for (uint32_t i = 0; i < K; ++i) {  // the whole upload is queued at once: the wire never waits for the host
+        const uint64_t lo = i == 0 ? 0 : b[i];
+        CU_CHECK(cudaMemcpyAsync((uint8_t *)b_stream.p + lo, data + lo, b[i + 1] - lo, cudaMemcpyHostToDevice, ctx.copy_in));
+        CU_CHECK(cudaEventRecord(ev_in.v[i], ctx.copy_in));
+    }
+    tr.mark("setup");
+
+    const uint8_t *d_stream = (const uint8_t *)b_stream.p;
+    Cand *d_cands = (Cand *)b_cands.p;
+    FrameRec *d_recs = (FrameRec *)b_recs.p;
+    FrameOut *d_outs = (FrameOut *)b_outs.p;
+    StreamSummary *d_sum = (StreamSummary *)b_sum.p;
+    unsigned long long *d_hi = (unsigned long long *)b_hi.p;
+    const uint32_t window = 16;
+    uint32_t n = 0;          // candidates so far
+    uint64_t copied = 0;     // PCM elements already queued for the trip back
+    bool bail = false;
+    // PCM [copied, upto) leaves once chunk_i is decoded (it holds frames of chunk_i only: earlier chunks end below `copied`)
+    auto copy_out = [&](uint32_t chunk_i, uint64_t upto) -> int {
+        if (upto > n_elems) upto = n_elems;
+        if (upto <= copied) return ZFLACB200_OK;
+        CU_CHECK(cudaStreamWaitEvent(ctx.copy_out, ev_done.v[chunk_i], 0));
+        CU_CHECK(cudaMemcpyAsync((uint8_t *)dst + copied * cb, (const uint8_t *)b_pcm.p + copied * cb, (upto - copied) * cb,
+                                 cudaMemcpyDeviceToHost, ctx.copy_out));
+        copied = upto;
+        return ZFLACB200_OK;
+    };
+    uint32_t launched = 0;  // chunks whose kernels are queued
+    for (uint32_t i = 0; i < K && !bail; ++i) {
+        // scan + hinted records on `st` (short, the host waits for the count); the frame-serial kernels of the
+        // chunk on one of S lanes: they are latency-bound (one lane per frame), so several chunks run side by side
+        cudaStream_t cs = ctx.lane[i % S];
+        CU_CHECK(cudaStreamWaitEvent(st, ev_in.v[std::min(i + 1, K - 1)], 0));
+        const uint64_t readable = i + 2 >= K ? len : b[i + 2];
+        CU_CHECK(launch_sync_scan_range(d_stream, b[i], b[i + 1], readable, d_cands + n, cap - n, (uint32_t *)b_total.p,
+                                        (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
+        CU_CHECK(cudaMemcpyAsync(&ctx.mailbox[0], b_total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        CU_CHECK(cudaStreamSynchronize(st));  // the host needs the count to place the next chunk's records
+        const uint32_t m = (uint32_t)(ctx.mailbox[0] & 0xFFFFFFFFull);
+        if (m > cap - n) {  // denser in valid headers than STREAMINFO suggests
+            bail = true;
+            break;
+        }
+        if (m) {
+            CU_CHECK(launch_hint_chain_range(d_cands, n, n + m, (const StreamDesc *)b_sd.p, 1, d_recs, window, d_hi + i, st));
+            CU_CHECK(cudaMemsetAsync(d_outs + n, 0xFF, sizeof(FrameOut) * (size_t)m, st));  // dropped slots: status != OK
+        }
+        CU_CHECK(cudaMemcpyAsync(&ctx.mailbox[2 + i], d_hi + i, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        CU_CHECK(cudaEventRecord(ev_hint.v[i], st));
+        CU_CHECK(cudaStreamWaitEvent(cs, ev_hint.v[i], 0));
+        if (m) {
+            if (stage.decode(d_stream, d_recs + n, m, b_scratch.p, wide, d_outs + n, true, cs, n) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+            EpilogueParams ep;
+            ep.frames = d_recs + n;
+            ep.n_frames = m;
+            ep.max_block_size = si.max_block >= 16 ? si.max_block : 4096;
+            ep.scratch = b_scratch.p;
+            ep.wide_scratch = wide;
+            ep.pcm = b_pcm.p;
+            ep.container_bytes = cb;
+            ep.msb_shift = msb_shift;
+            ep.lossy_flag = (uint32_t *)b_flag.p;
+            if (stage.epilogue(ep, d_outs + n, C, cs, n) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+        }
+        CU_CHECK(cudaEventRecord(ev_done.v[i], cs));
+        launched = i + 1;
+        n += m;
+        // chunk i-1's PCM range is known since the stream synchronisation above (its records were built before this scan)
+        if (i > 0 && copy_out(i - 1, ctx.mailbox[2 + i - 1]) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    }
+    tr.mark("chunks");
+    for (uint32_t i = launched > (uint32_t)S ? launched - S : 0; i < launched; ++i) CU_CHECK(cudaStreamWaitEvent(st, ev_done.v[i], 0));
+    uint32_t lossy = 0;
+    StreamSummary sum;
+    memset(&sum, 0, sizeof(sum));
+    if (!bail && n > 0) {
+        CU_CHECK(launch_crc16_frames(d_stream, d_recs, d_outs, n, d_sum, (uint8_t *)b_ok.p, st));
+        CU_CHECK(launch_verify_chain(d_cands, n, (const StreamDesc *)b_sd.p, 1, d_recs, d_outs, d_sum, window, st));
+        CU_CHECK(cudaMemcpyAsync(&sum, b_sum.p, sizeof(sum), cudaMemcpyDeviceToHost, st));
+        CU_CHECK(cudaMemcpyAsync(&lossy, b_flag.p, sizeof(lossy), cudaMemcpyDeviceToHost, st));
+        CU_CHECK(cudaEventRecord(ev.e[7], st));
+        if (copy_out(K - 1, n_elems) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+        CU_CHECK(cudaStreamSynchronize(st));
+    } else {
+        CU_CHECK(cudaStreamSynchronize(st));
+    }
+    const bool accepted = !bail && n > 0 && !sum.fail && sum.first_ok && sum.n_samples == n_elems && sum.channels == C &&
+                          !(msb_shift && lossy);
+    memset(info, 0, sizeof(*info));
+    memcpy(info->md5_streaminfo, si.md5, 16);
+    info->audio_offset = audio_offset;
+    info->container_bytes = (uint8_t)cb;
+    int result = ZFLACB200_OK;
+    if (accepted && do_md5) {  // K4 over the device copy while the last PCM chunk is still on its way out
+        Md5Job job;
+        job.pcm = b_pcm.p;
+        job.n_samples = n_elems;
+        job.container_bytes = cb;
+        job.hash_bytes = aligned == 24 ? 3 : cb;  // :268-277
+        job.unshift = msb_shift;
+        job.pad = 0;
+        CU_CHECK(cudaMemcpyAsync(b_jobs.p, &job, sizeof(job), cudaMemcpyHostToDevice, st));
+        CU_CHECK(launch_md5((const Md5Job *)b_jobs.p, 1, (uint8_t *)b_digest.p, st));
+        CU_CHECK(cudaMemcpyAsync(info->md5_computed, b_digest.p, 16, cudaMemcpyDeviceToHost, st));
+        CU_CHECK(cudaStreamSynchronize(st));
+        info->md5_checked = 1;
+        if (memcmp(info->md5_computed, si.md5, 16) != 0) result = ZFLACB200_INVALID_CHECKSUM;  // :279-280
+    }
+    CU_CHECK(cudaStreamSynchronize(ctx.copy_out));
+    CU_CHECK(cudaStreamSynchronize(ctx.copy_in));
+    tr.mark("tail");
+    if (!accepted) return kNotPipelined;
+    info->ms_total = ev_ms(ev.e[0], ev.e[7]);
+    if (result != ZFLACB200_OK) return result;
+    info->channels = sum.channels;
+    info->bits_per_sample = sum.bps;
+    info->sample_rate = sum.sample_rate;
+    info->n_samples = sum.n_samples;
+    info->pcm_bytes = pcm_bytes;
+    info->n_frames = sum.n_frames;
+    info->n_candidates = n;
+    info->fast_path = 1;
+    info->n_crc16_mismatch = sum.n_crc16_mismatch;
+    info->audio_bytes = sum.end_offset - audio_offset;
+    return ZFLACB200_OK;
+}
 }  // namespace
 
 extern "C" {
@@ -1252,6 +1501,10 @@ void zflacb200_shutdown(void) {
             cudaSetDevice(d);
             cudaStreamDestroy(g_ctx[d].stream);
             cudaStreamDestroy(g_ctx[d].side);
+            cudaStreamDestroy(g_ctx[d].copy_in);
+            cudaStreamDestroy(g_ctx[d].copy_out);
+            for (auto &l : g_ctx[d].lane) cudaStreamDestroy(l);
+            cudaFreeHost(g_ctx[d].mailbox);
             cudaEventDestroy(g_ctx[d].ev_fork);
             cudaEventDestroy(g_ctx[d].ev_join);
             g_ctx[d] = DeviceCtx();
@@ -1321,6 +1574,12 @@ void zflacb200_close(zflacb200_stream *s) {
 }
 
 int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *opt, void *dst, size_t dst_capacity, zflacb200_info *info) {
+    {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        g_last_error.clear();
+        const int p = decode_pipelined(data, len, opt, dst, dst_capacity, info);
+        if (p != kNotPipelined) return p;
+    }
     zflacb200_stream *h = nullptr;
     const int e = zflacb200_open(data, len, opt, &h, info);
     if (e != ZFLACB200_OK) return e;

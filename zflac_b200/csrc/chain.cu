@@ -53,9 +53,9 @@ __device__ __forceinline__ bool hint_of(const Cand &c, const Cand &ref, const St
 }
 
 __global__ void __launch_bounds__(kChainThreads)
-k_hint_chain(const Cand *__restrict__ cands, uint32_t n, const StreamDesc *__restrict__ streams, uint32_t n_streams,
-             FrameRec *__restrict__ recs, uint32_t window) {
-    const uint32_t i = blockIdx.x * kChainThreads + threadIdx.x;
+k_hint_chain(const Cand *__restrict__ cands, uint32_t first, uint32_t n, const StreamDesc *__restrict__ streams, uint32_t n_streams,
+             FrameRec *__restrict__ recs, uint32_t window, unsigned long long *__restrict__ pcm_hi) {
+    const uint32_t i = first + blockIdx.x * kChainThreads + threadIdx.x;
     if (i >= n) return;
     const Cand c = cands[i];
     FrameRec fr;
@@ -100,6 +100,7 @@ k_hint_chain(const Cand *__restrict__ cands, uint32_t n, const StreamDesc *__res
                 fr.scratch_base = sd.scratch_base + (uint64_t)C * ((start + 7) & ~7ull) + 64ull * i;
                 fr.channels = (uint8_t)C;
                 fr.bps = (uint8_t)bps;
+                if (pcm_hi) atomicMax(pcm_hi, (unsigned long long)(fr.sample_base + (uint64_t)c.block_size * C));
             }
         }
     }
@@ -152,9 +153,15 @@ k_verify_chain(const Cand *__restrict__ cands, uint32_t n, const StreamDesc *__r
 
 cudaError_t launch_hint_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
                               FrameRec *d_recs, uint32_t window, cudaStream_t st) {
-    if (n == 0) return cudaSuccess;
+    return launch_hint_chain_range(d_cands, 0, n, d_streams, n_streams, d_recs, window, nullptr, st);
+}
+
+cudaError_t launch_hint_chain_range(const Cand *d_cands, uint32_t first, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
+                                    FrameRec *d_recs, uint32_t window, unsigned long long *d_pcm_hi, cudaStream_t st) {
+    if (n <= first) return cudaSuccess;
     ZF_COUNT_LAUNCH();
-    k_hint_chain<<<(n + kChainThreads - 1) / kChainThreads, kChainThreads, 0, st>>>(d_cands, n, d_streams, n_streams, d_recs, window);
+    k_hint_chain<<<(n - first + kChainThreads - 1) / kChainThreads, kChainThreads, 0, st>>>(d_cands, first, n, d_streams, n_streams,
+                                                                                            d_recs, window, d_pcm_hi);
     return cudaGetLastError();
 }
 

@@ -15,6 +15,9 @@ cudaError_t scan_init_constants();
 uint32_t scan_tile_count(uint64_t scan_begin, uint64_t len);
 cudaError_t launch_sync_scan(const uint8_t *d_stream, uint64_t scan_begin, uint64_t len, Cand *d_cands, uint32_t cap,
                              uint32_t *d_total, unsigned long long *d_tile_state, uint32_t *d_ticket, cudaStream_t st);
+cudaError_t launch_sync_scan_range(const uint8_t *d_stream, uint64_t scan_begin, uint64_t scan_end, uint64_t len, Cand *d_cands,
+                                   uint32_t cap, uint32_t *d_total, unsigned long long *d_tile_state, uint32_t *d_ticket,
+                                   cudaStream_t st);
 cudaError_t launch_frame_link(const uint8_t *d_stream, uint64_t len, const Cand *d_cands, uint32_t n, uint32_t *d_link,
                               uint32_t window, uint64_t max_frame_bytes, cudaStream_t st);
 cudaError_t launch_crc16_ranges(const uint8_t *d_stream, const uint64_t *d_begin, const uint64_t *d_end, uint32_t n,
@@ -26,6 +29,10 @@ cudaError_t launch_crc16_frames(const uint8_t *d_stream, const FrameRec *d_recs,
 // chain.cu
 cudaError_t launch_hint_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
                               FrameRec *d_recs, uint32_t window, cudaStream_t st);
+// Chunked variant: records for candidates [first, n) only (earlier ones exist already); *d_pcm_hi is raised to the
+// largest PCM element end among the kept records (what may be copied out once these frames are decoded).
+cudaError_t launch_hint_chain_range(const Cand *d_cands, uint32_t first, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
+                                    FrameRec *d_recs, uint32_t window, unsigned long long *d_pcm_hi, cudaStream_t st);
 cudaError_t launch_verify_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
                                 const FrameRec *d_recs, const FrameOut *d_outs, StreamSummary *d_sums, uint32_t window,
                                 cudaStream_t st);

@@ -108,7 +108,7 @@ __device__ __forceinline__ uint32_t sync_mask4(uint32_t cur, uint32_t nxt) {
 }
 
 __global__ void __launch_bounds__(kScanThreads, 6)
-k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t len, uint64_t tile0, uint32_t n_tiles,
+k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_end, uint64_t len, uint64_t tile0, uint32_t n_tiles,
             Cand *__restrict__ out, uint32_t cap, uint32_t *__restrict__ total_out,
             unsigned long long *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
     __shared__ uint32_t s_tile;
@@ -155,7 +155,7 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t len, ui
             raw &= raw - 1;
             const uint64_t p = pos + b;
             Cand c;
-            if (p >= scan_begin && parse_header_at(s, p, len, c)) ok |= 1u << b;
+            if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) ok |= 1u << b;
         }
         valid[r] = ok;
         counts |= (unsigned long long)__popc(ok) << (16 * r);
@@ -436,14 +436,23 @@ uint32_t scan_tile_count(uint64_t scan_begin, uint64_t len) {
 cudaError_t launch_sync_scan(const uint8_t *d_stream, uint64_t scan_begin, uint64_t len, Cand *d_cands, uint32_t cap,
                              uint32_t *d_total, unsigned long long *d_tile_state, uint32_t *d_ticket,
                              cudaStream_t st) {
-    const uint32_t n_tiles = scan_tile_count(scan_begin, len);
+    return launch_sync_scan_range(d_stream, scan_begin, len, len, d_cands, cap, d_total, d_tile_state, d_ticket, st);
+}
+
+// Candidates whose sync code starts in [scan_begin, scan_end); bytes up to `len` may be read (a header
+// that starts just before scan_end extends past it).
+cudaError_t launch_sync_scan_range(const uint8_t *d_stream, uint64_t scan_begin, uint64_t scan_end, uint64_t len, Cand *d_cands,
+                                   uint32_t cap, uint32_t *d_total, unsigned long long *d_tile_state, uint32_t *d_ticket,
+                                   cudaStream_t st) {
+    if (scan_end > len) scan_end = len;
+    const uint32_t n_tiles = scan_tile_count(scan_begin, scan_end);
     cudaError_t e;
     if ((e = cudaMemsetAsync(d_total, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
     if (n_tiles == 0) return cudaSuccess;
     if ((e = cudaMemsetAsync(d_tile_state, 0, sizeof(unsigned long long) * n_tiles, st)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(d_ticket, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
     ZF_COUNT_LAUNCH();
-    k_sync_scan<<<n_tiles, kScanThreads, 0, st>>>(d_stream, scan_begin, len, scan_begin & ~15ull, n_tiles, d_cands, cap,
+    k_sync_scan<<<n_tiles, kScanThreads, 0, st>>>(d_stream, scan_begin, scan_end, len, scan_begin & ~15ull, n_tiles, d_cands, cap,
                                                   d_total, d_tile_state, d_ticket);
     return cudaGetLastError();
 }
