@@ -37,6 +37,22 @@ def test_batch_of_short_files(z):
     assert all(r.info["fast_path"] == 1 for r in res)
 
 
+def test_batch_large_enough_for_lane_md5(z):
+    """>= 256 streams: the MD5 gate runs one chain per LANE (k_md5_lanes); odd lengths exercise its padding blocks."""
+    ps = []
+    for i in range(300):
+        p = fg.c5_file(i)
+        p.n_samples = 4096 + 257 * i  # a frame or a few, every length different
+        ps.append(p)
+    streams = [fg.generate(p, want_pcm=False).flac for p in ps]
+    res = z.decode_batch(streams)
+    check_against_oracle(z, streams, res)
+    bad = [s.copy() for s in streams]
+    bad[7][bad[7].size - 9] ^= 0x01  # flips a residual bit: only the MD5 gate can notice
+    res = z.decode_batch(bad)
+    check_against_oracle(z, bad, res)
+
+
 def test_mixed_batch_containers_errors_and_fallbacks(z):
     names = ["c5_file_0", "bps8_fixed_lowprec", "bps24_stereo_leftside", "unknown_total", "c4_32bit_rice2_escapes",
              "bps12_midside", "ch6_mixed", "c4_variable_blocksize", "c5_file_1", "bps20_mono_rice2", "tiny_blocks_16"]
