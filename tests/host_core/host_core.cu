@@ -37,6 +37,7 @@ struct HostSrc {
         if (w > consumed_below) consumed_below = w;  // the device refills with `words < w are consumed`
         return raw(w);
     }
+    __host__ __device__ void top_up(uint32_t cur, uint32_t) { top_up(cur); }
     __host__ __device__ void top_up(uint32_t cur) {
         guaranteed = cur + zf::kFastWords;
         if (cur > consumed_below) consumed_below = cur;

@@ -214,6 +214,8 @@ struct BitReader {
     ZF_HD void align_byte() { skip<true>((8u - (o & 7u)) & 7u); }  // word starts are byte aligned
     // N (word next-1) is re-read by the branch-free skip: it still counts as live
     ZF_HD void prepare_fast() { src.top_up(next - 1); }
+    // `tick`: a value converged lanes share (the body index): sources that refill every other body key on it
+    ZF_HD void prepare_fast(uint32_t tick) { src.top_up(next - 1, tick); }
 };
 
 ZF_HD int32_t fixed_coef(uint32_t order, int j) {  // :481-490 {1; 2,-1; 3,-3,1; 4,-6,4,-1}

@@ -10,7 +10,11 @@
 
 namespace zf {
 
-__global__ void __launch_bounds__(kDecodeThreads)
+// SRC = StagedSrc (16-word warp-synchronous refills, 64-word ring, 116 registers: 4 CTAs per SM) or QuadSrc (4-word
+// refills, 32-word ring, 72 registers: 7 CTAs per SM). The kernel is latency-bound, so what counts is that ALL frames of
+// a launch are resident at once: the launcher picks QuadSrc when the frames do not fit one wave of the first.
+template <class SRC>
+__global__ void __launch_bounds__(kDecodeThreads, SRC::kMinBlocks)
 k_parse_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frames, uint32_t n_frames,
                int32_t *__restrict__ scratch, SubRec *__restrict__ subs, FrameOut *__restrict__ outs,
                uint32_t *__restrict__ big_orders, int write_samples) {
@@ -23,7 +27,7 @@ k_parse_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frame
     const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(s + start) & 15u);
     const uint64_t origin = start - lead;  // may reach up to 15 bytes below offset 0 of an unaligned buffer (same allocation)
     const uint64_t span = fr.stream_end > start ? fr.stream_end - start + lead : 0;
-    BitReader<StagedSrc<kDecodeThreads>> br;
+    BitReader<SRC> br;
     br.src.init(s + start - lead, span, threadIdx.x);
     br.init_at(lead);
     const uint64_t len_bits = span * 8;
@@ -39,8 +43,19 @@ cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frame
     if (n_frames == 0) return cudaSuccess;
     const uint32_t blocks = (n_frames + kDecodeThreads - 1) / kDecodeThreads;
     ZF_COUNT_LAUNCH();
-    k_parse_frames<<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(
-        d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_big_orders, write_samples ? 1 : 0);
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    if (blocks <= (uint32_t)sms * 4u)
+        k_parse_frames<StagedSrc<kDecodeThreads>><<<blocks, kDecodeThreads, kStagedRing * kDecodeThreads * sizeof(uint32_t), st>>>(
+            d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_big_orders, write_samples ? 1 : 0);
+    else
+        k_parse_frames<QuadSrc<kDecodeThreads>><<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(
+            d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_big_orders, write_samples ? 1 : 0);
     return cudaGetLastError();
 }
 

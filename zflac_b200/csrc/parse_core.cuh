@@ -77,7 +77,7 @@ ZF_HDI uint32_t parse_residual(BitReader<Src> &br, int32_t *__restrict__ out, ui
                 if (force_single == 0 && (i & 7u) == 0 && i + 8 <= end) {
                     // 8 codewords, speculative and branch-free; a codeword longer than the 32-bit window
                     // (rare) only raises zmax: the body is rolled back and redone row by row
-                    br.prepare_fast();
+                    br.prepare_fast(i >> 3);
                     const uint32_t sA = br.A, sB = br.B, sN = br.N, so = br.o;
                     uint32_t ws = br.enter_fast();
                     uint32_t zmax = 0;

@@ -112,14 +112,106 @@ static __device__ __noinline__ uint4 staged_tail_quad(const uint8_t *g, uint32_t
 }
 
 // ---------------------------------------------------------------------------------------------
-// StagedSrc — word source of K2a parse_frames. Same ring (word w of lane L at ring[w % kRingWords][L],
+// StagedSrc — word source of K2a parse_frames. Ring of kStagedRing words per lane (word w of lane L at
+// ring[w % kStagedRing][L], bank-conflict free), filled 64 bytes at a time THROUGH REGISTERS: four
+// 128-bit global loads per sixteen words, issued one refill ahead of their sixteen shared stores.
+//
+// The scoreboard is per warp REGISTER: a shared store of the staging registers waits for the newest
+// global load into them by ANY lane. So refills are not left to each lane's own rhythm (some lane
+// would refill before almost every body and every body would wait for the previous body's loads):
+// all lanes refill on the same bodies — every other one, keyed on the body index converged lanes
+// share — which puts two bodies of work between a load and the store that needs it. A lane whose
+// ring has no room just skips that turn. 16 words per turn cover the worst case of 8 words per body.
+// Word 0 sits at a 16-byte aligned global address.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kStagedRing = 64;
+
+template <int NT>
+struct StagedSrc {
+    static constexpr int kMinBlocks = 4;  // CTAs per SM the kernel is compiled for
+    const uint8_t *g;    // global address of word 0 (16-byte aligned)
+    uint32_t avail;      // bytes readable from g (stream end), clamped
+    uint32_t col;        // shared-space byte address of zf_ring[lane column]
+    uint32_t staged;     // words < staged are in the ring; words [staged, staged + 16) are in q[] (possibly still in flight)
+    uint4 q[4];
+
+    static constexpr uint32_t kWordScale = NT * 4;  // byte distance of consecutive words of a lane in the ring
+    __device__ __forceinline__ uint32_t word_scaled(uint32_t ws) const {  // ws = word index * kWordScale
+        uint32_t v;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(col + (ws & ((kStagedRing - 1) * kWordScale))) : "memory");
+        return v;
+    }
+    __device__ __forceinline__ uint32_t slot(uint32_t w) const { return col + (w & (kStagedRing - 1)) * (NT * 4); }
+    __device__ __forceinline__ void load16(uint32_t w) {  // words [w, w + 16) -> q; bytes past the stream end read as zero
+        const uint32_t off = w * 4u;
+        if (off + 64u <= avail) {
+            const uint4 *p = reinterpret_cast<const uint4 *>(g + off);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q[k] = __ldg(p + k);
+            // DRAM latency here is ~3000 cycles, more than the two bodies between a load and its store: ask L2 for
+            // the bytes ~8 refills ahead so that the loads above are L2 hits
+            if (off + 1024u <= avail) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + off + 576u));
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q[k] = staged_tail_quad(g, off + 16u * k, avail);
+        }
+    }
+    __device__ __forceinline__ void store16() {  // q -> slots of words [staged, staged + 16); staged % 16 == 0: no wrap inside
+        const uint32_t a = slot(staged);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(a + NT * 4 * (4 * k + 0)), "r"(q[k].x) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(a + NT * 4 * (4 * k + 1)), "r"(q[k].y) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(a + NT * 4 * (4 * k + 2)), "r"(q[k].z) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(a + NT * 4 * (4 * k + 3)), "r"(q[k].w) : "memory");
+        }
+    }
+    __device__ __forceinline__ void flush_and_load() {
+        store16();
+        staged += 16;
+        load16(staged);
+    }
+    __device__ __forceinline__ void init(const uint8_t *base, uint64_t bytes, uint32_t column) {
+        g = base;
+        avail = bytes > 0xFFFFFF80ull ? 0xFFFFFF80u : (uint32_t)bytes;
+        col = (uint32_t)__cvta_generic_to_shared(&zf_ring[column]);
+        staged = 0;
+        load16(0);
+#pragma unroll 1
+        for (int k = 0; k < 3; ++k) flush_and_load();  // a frame starts with 48 words in the ring and 16 on their way
+    }
+    // words < cur are consumed; afterwards words [cur, cur + kFastWords) are resident
+    __device__ __forceinline__ void top_up(uint32_t cur, uint32_t tick) {
+        if ((tick & 1u) == 0 && staged + 16u <= cur + kStagedRing) flush_and_load();
+#pragma unroll 1
+        while (staged < cur + kFastWords) flush_and_load();  // only after slow-path rows that ran ahead of the refills
+    }
+    __device__ __forceinline__ void top_up(uint32_t cur) { top_up(cur, 0u); }
+    __device__ __forceinline__ uint32_t word(uint32_t w) const {
+        uint32_t v;  // volatile: stays ordered against the shared stores of the refills
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(slot(w)) : "memory");
+        return v;
+    }
+    __device__ __forceinline__ void note_rollback() {}
+    static __device__ __forceinline__ uint32_t fix(uint32_t raw) { return __byte_perm(raw, 0, 0x0123); }
+    __device__ __forceinline__ uint32_t word_checked(uint32_t w) {
+#pragma unroll 1
+        while (w >= staged) flush_and_load();
+        return word(w);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// QuadSrc — word source of K2a parse_frames for launches with more frames than one wave of the StagedSrc kernel holds
+// (fewer registers: 7 CTAs per SM instead of 4). Same ring (word w of lane L at ring[w % kRingWords][L],
 // bank-conflict free), filled 16 bytes at a time THROUGH REGISTERS: one 128-bit global load per four
 // words, issued one refill ahead of its four shared stores, so the bit chain never waits on it and
 // no cp.async group bookkeeping is needed (a lane's shared loads follow its own shared stores in
 // program order). Word 0 sits at a 16-byte aligned global address.
 // ---------------------------------------------------------------------------------------------
 template <int NT>
-struct StagedSrc {
+struct QuadSrc {
+    static constexpr int kMinBlocks = 7;  // CTAs per SM the kernel is compiled for
     const uint8_t *g;    // global address of word 0 (16-byte aligned)
     uint32_t avail;      // bytes readable from g (stream end), clamped
     uint32_t col;        // shared-space byte address of zf_ring[lane column]
@@ -162,6 +254,7 @@ struct StagedSrc {
         load_quad(staged);
     }
     // words < cur are consumed; afterwards words [cur, cur + kFastWords) are resident
+    __device__ __forceinline__ void top_up(uint32_t cur, uint32_t) { top_up(cur); }
     __device__ __forceinline__ void top_up(uint32_t cur) {
         if (staged + 4 <= cur + kRingWords && staged < cur + 24) flush_and_load();
         if (staged + 4 <= cur + kRingWords && staged < cur + 16) flush_and_load();
@@ -181,5 +274,6 @@ struct StagedSrc {
         return word(w);
     }
 };
+
 
 }  // namespace zf
