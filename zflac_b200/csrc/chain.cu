@@ -146,9 +146,28 @@ k_verify_chain(const Cand *__restrict__ cands, uint32_t n, const StreamDesc *__r
         s.channels = fr.channels;
         s.first_ok = (fr.sample_base == sd.pcm_base) ? 1u : 0u;
     }
-    if (!ok) atomicOr(&sums[sid].fail, 1u);
-    atomicAdd(&sums[sid].n_frames, 1u);
-    atomicAdd((unsigned long long *)&sums[sid].n_samples, (unsigned long long)fr.block_size * C);
+    // one atomic per warp and stream instead of one per frame (a 1-hour stream: 38 760 frames on ONE summary)
+    const uint32_t active = __activemask();
+    const uint32_t peers = __match_any_sync(active, sid);
+    const int leader = __ffs(peers) - 1;
+    const int lane = threadIdx.x & 31;
+    uint32_t bad = ok ? 0u : 1u, frames = 1u;
+    unsigned long long samples = (unsigned long long)fr.block_size * C;
+    for (uint32_t rest = peers & ~(1u << leader); rest; rest &= rest - 1) {  // leader gathers its peers' values
+        const int src = __ffs(rest) - 1;
+        const uint32_t b2 = __shfl_sync(peers, bad, src);
+        const unsigned long long s2 = __shfl_sync(peers, samples, src);
+        if (lane == leader) {
+            bad |= b2;
+            frames += 1u;
+            samples += s2;
+        }
+    }
+    if (lane == leader) {
+        if (bad) atomicOr(&sums[sid].fail, 1u);
+        atomicAdd(&sums[sid].n_frames, frames);
+        atomicAdd((unsigned long long *)&sums[sid].n_samples, samples);
+    }
 }
 
 cudaError_t launch_hint_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
