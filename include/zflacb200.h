@@ -158,6 +158,18 @@ int zflacb200_batch_read_stream(zflacb200_batch *b, size_t i, void *dst, size_t 
 int zflacb200_batch_device_pcm(zflacb200_batch *b, size_t i, void **dev_ptr, size_t *bytes);
 void zflacb200_batch_close(zflacb200_batch *b);
 
+/* One-call variant, host blob in, host PCM out (the batch counterpart of zflacb200_decode): the
+ * batch is cut into a few contiguous sub-batches; while sub-batch k is decoded, sub-batch k+1 is
+ * still being uploaded and the PCM of k-1 already travels back — both PCIe directions and the SMs
+ * busy at once. pcm_offsets[i] receives the byte offset of stream i inside dst (UINT64_MAX if it did
+ * not decode; ZFLACB200_OUT_OF_MEMORY in statuses[i] if dst had no room left for it).
+ * zflacb200_batch_pcm_bound() says how large dst must be, from the STREAMINFO totals (host only;
+ * streams without a stated total count as 0: give them extra room or use the two-phase calls). */
+int zflacb200_batch_pcm_bound(const uint8_t *blob, const uint64_t *offsets, const uint64_t *lens, size_t n, uint64_t *bytes);
+int zflacb200_batch_decode(const uint8_t *blob, const uint64_t *offsets, const uint64_t *lens, size_t n,
+                           const zflacb200_options *opt, void *dst, size_t dst_bytes, uint64_t *pcm_offsets,
+                           zflacb200_info *infos, int *statuses);
+
 /* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
 typedef struct zflacb200_frame {
     uint64_t offset;        /* byte offset of the sync code */

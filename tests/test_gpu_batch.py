@@ -88,3 +88,30 @@ def test_batch_device_resident_and_read_all(z):
         assert np.array_equal(v, s.pcm)
     assert np.array_equal(b.stream(5).samples, streams[5].pcm)
     b.close()
+
+
+def test_batch_decode_one_call_pipelined(z):
+    """zflacb200_batch_decode (sub-batches overlapped over both PCIe directions) == the oracle, stream by stream; a stream
+    the device chain refuses and a bad signature ride along; a destination that is too small says OutOfMemory."""
+    from oracle import oracle
+    streams = [fg.generate(fg.c5_file(200 + i), want_pcm=False).flac for i in range(80)]     # ~9.6 MB: one sub-batch
+    streams.insert(17, make("unknown_total").flac)
+    streams.insert(40, np.frombuffer(b"fLaX" + bytes(60), dtype=np.uint8))
+    blob, offs, lens = z.pack_streams(streams)
+    blob = np.concatenate([blob, np.zeros(24 << 20, dtype=np.uint8)])  # trailing bytes: >= 3 sub-batches by size
+    bound = z.batch_pcm_bound(blob, offs, lens)
+    dst = np.zeros(bound + (4 << 20), dtype=np.uint8)
+    res = z.decode_batch_into(blob, offs, lens, dst)
+    for i, data in enumerate(streams):
+        ref = oracle.decode(data)
+        if ref.error != "OK":
+            assert res.statuses[i] != 0 and res.samples(i) is None
+            continue
+        assert res.statuses[i] == 0, (i, res.statuses[i])
+        assert np.array_equal(res.samples(i), ref.samples), i
+        assert res.infos[i]["md5_computed"] == ref.md5_computed
+    small = np.zeros(1 << 20, dtype=np.uint8)
+    res = z.decode_batch_into(blob, offs, lens, small)
+    assert 12 in res.statuses  # ZFLACB200_OUT_OF_MEMORY for the streams that no longer fitted
+    ok = [i for i in range(len(streams)) if res.statuses[i] == 0]
+    assert ok and all(np.array_equal(res.samples(i), oracle.decode(streams[i]).samples) for i in ok[:4])

@@ -114,7 +114,7 @@ def run(args, rank, world, local_rank, metric, ClockSampler, measured_peak):
     sptr = stream.cuda_stream
 
     b = z.open_batch(h_blob.numpy(), offs, lens, device_blob_ptr=d_blob.data_ptr(), device=local_rank, stream=sptr)
-    out_bytes = b.pcm_bytes()
+    out_bytes = max(b.pcm_bytes(), z.batch_pcm_bound(h_blob.numpy(), offs, lens))
     h_pcm = torch.empty(out_bytes, dtype=torch.uint8).pin_memory()
     # parity of what is timed: every file bit-exact vs the generator's PCM, MD5 verified on the device
     buf, po = b.read_all(h_pcm.numpy())
@@ -125,6 +125,10 @@ def run(args, rank, world, local_rank, metric, ClockSampler, measured_peak):
     b.close()
     if not ok:
         raise SystemExit("PARITY FAILURE: batch PCM differs from the generator's")
+    # ... and the same check through the one-call API the e2e figure is measured on
+    res = z.decode_batch_into(h_blob.numpy(), offs, lens, h_pcm.numpy(), device=local_rank, stream=sptr)
+    if res.statuses != [0] * len(files) or not all(np.array_equal(res.samples(i), f.pcm) for i, f in enumerate(files)):
+        raise SystemExit("PARITY FAILURE: zflacb200_batch_decode PCM differs from the generator's")
 
     def barrier():
         if world > 1:
@@ -137,11 +141,14 @@ def run(args, rank, world, local_rank, metric, ClockSampler, measured_peak):
         return info
 
     def step_e2e():
-        bb = z.open_batch(h_blob.numpy(), offs, lens, device=local_rank, stream=sptr)
-        bb.read_all(h_pcm.numpy())
-        info = bb.infos[0]
-        bb.close()
-        return info
+        if os.environ.get("ZFLACB200_BENCH_TWO_CALL"):  # the r01 shape of the call: open, then read everything back
+            bb = z.open_batch(h_blob.numpy(), offs, lens, device=local_rank, stream=sptr)
+            bb.read_all(h_pcm.numpy())
+            info = bb.infos[0]
+            bb.close()
+            return info
+        res = z.decode_batch_into(h_blob.numpy(), offs, lens, h_pcm.numpy(), device=local_rank, stream=sptr)
+        return res.infos[0]
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -184,7 +191,10 @@ def run(args, rank, world, local_rank, metric, ClockSampler, measured_peak):
     if not args.no_e2e:
         e2e = {"value": round(job_samples / (ms_e2e * 1e-3) / 1e6, 2), "unit": "Msamples/s", "h2d_bytes_per_step": int(job_flac),
                "d2h_bytes_per_step": int(job_pcm), "ms_per_step": round(ms_e2e, 3),
-               "api": "zflac_b200.open_batch(pinned host blob) + read_all(pinned host PCM) -> zflacb200_batch_open / _read_all (C ABI)",
+               "api": ("zflac_b200.open_batch(pinned host blob) + read_all(pinned host PCM) -> zflacb200_batch_open / _read_all (C ABI)"
+                       if os.environ.get("ZFLACB200_BENCH_TWO_CALL") else
+                       "zflac_b200.decode_batch_into(pinned host blob, pinned host PCM) -> zflacb200_batch_decode (C ABI), "
+                       "sub-batches overlapped over both PCIe directions"),
                "md5": "included"}
 
     cpu = None

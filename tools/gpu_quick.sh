@@ -15,3 +15,11 @@ for wl in ("c2","c3","c5","c2_single"):
         print(wl,"value",d["value"],"ms",d["ms_per_step"],d["kernel_ms"],"e2e",d.get("e2e") and d["e2e"]["ms_per_step"],"launches",d["gpu_launches"])
     except Exception as e: print(wl,"no bench line",e)
 PY
+ZFLACB200_BENCH_TWO_CALL=1 ZFLACB200_TRACE=1 python bench.py --workload c5 --steps 3 --warmup 2 --md5-steps 0 --no-cpu-baseline > gpurun_out/${tag}_bench_c5_twocall.json 2> gpurun_out/${tag}_bench_c5_twocall.err
+python - <<PY
+import json
+try:
+    d=json.loads(open("gpurun_out/${tag}_bench_c5_twocall.json").read().strip().splitlines()[-1]); print("c5 two-call e2e", d["e2e"]["ms_per_step"])
+except Exception as e: print("no two-call line", e)
+PY
+ZFLACB200_TRACE=1 python bench.py --workload c5 --steps 2 --warmup 1 --md5-steps 0 --no-cpu-baseline > /dev/null 2> gpurun_out/${tag}_c5_trace.err; grep -c . gpurun_out/${tag}_c5_trace.err

@@ -312,6 +312,61 @@ def open_batch(blob, offsets, lens, *, device_blob_ptr: int = 0, device: int = -
     return DeviceBatch(handle, infos, statuses, n)
 
 
+def batch_pcm_bound(blob, offsets, lens) -> int:
+    """Bytes zflacb200_batch_decode needs in its destination (from the STREAMINFO totals, host only)."""
+    blob = _as_u8(blob)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    lens = np.ascontiguousarray(lens, dtype=np.uint64)
+    v = C.c_uint64()
+    st = _native.load().zflacb200_batch_pcm_bound(blob.ctypes.data, offsets.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                  lens.ctypes.data_as(C.POINTER(C.c_uint64)), int(offsets.size), C.byref(v))
+    if st != 0:
+        _raise(st)
+    return int(v.value)
+
+
+class BatchResult:
+    """What zflacb200_batch_decode returned: statuses, infos, and where each stream's PCM sits in the caller's buffer."""
+
+    def __init__(self, infos, statuses, offs, dst, n):
+        self.n = n
+        self._raw_infos = infos
+        self.infos = _LazyInfos(infos, n)
+        self.statuses = np.frombuffer(statuses, dtype=np.int32, count=n).tolist() if n else []
+        self.pcm_offsets = offs
+        self.dst = dst
+
+    def samples(self, i: int):
+        """View of stream i's samples inside the destination buffer (None if it did not decode)."""
+        if self.statuses[i] != 0 or int(self.pcm_offsets[i]) == 2**64 - 1:
+            return None
+        inf = self._raw_infos[i]
+        o = int(self.pcm_offsets[i])
+        return self.dst[o:o + int(inf.pcm_bytes)].view(_DTYPES[inf.container_bytes])
+
+
+def decode_batch_into(blob, offsets, lens, dst: np.ndarray, *, device: int = -1, stream: int | None = None,
+                      verify_md5: bool = True, use_fast_path: bool = True) -> BatchResult:
+    """zflacb200_batch_decode: host blob in, host PCM out, upload / decode / read-back overlapped over sub-batches."""
+    lib = _native.load()
+    blob = _as_u8(blob)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    lens = np.ascontiguousarray(lens, dtype=np.uint64)
+    n = int(offsets.size)
+    flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_fast_path else NO_FAST_PATH)
+    opt = _options(flags, device, stream)
+    infos = (_native.Info * max(n, 1))()
+    statuses = (C.c_int * max(n, 1))()
+    offs = np.zeros(max(n, 1), dtype=np.uint64)
+    dst8 = dst.view(np.uint8).reshape(-1)
+    st = lib.zflacb200_batch_decode(blob.ctypes.data, offsets.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                    lens.ctypes.data_as(C.POINTER(C.c_uint64)), n, C.byref(opt), dst8.ctypes.data, dst8.nbytes,
+                                    offs.ctypes.data_as(C.POINTER(C.c_uint64)), infos, statuses)
+    if st != 0:
+        _raise(st)
+    return BatchResult(infos, statuses, offs, dst8, n)
+
+
 def decode_batch(streams, *, device: int = -1, verify_md5: bool = True, use_fast_path: bool = True):
     """Decodes a list of independent streams in one pipeline pass. Returns a list with, per stream, a DecodedFLAC
     or the ZflacError instance the reference's decode() would have raised."""

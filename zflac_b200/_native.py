@@ -20,7 +20,7 @@ EXPORTS = [
     "zflacb200_status_name", "zflacb200_last_error", "zflacb200_kernel_launches", "zflacb200_open", "zflacb200_read",
     "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_frames", "zflacb200_batch_open",
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
-    "zflacb200_batch_close",
+    "zflacb200_batch_close", "zflacb200_batch_pcm_bound", "zflacb200_batch_decode",
 ]
 
 
@@ -89,6 +89,11 @@ def load():
     lib.zflacb200_batch_device_pcm.restype = C.c_int
     lib.zflacb200_batch_close.argtypes = [C.c_void_p]
     lib.zflacb200_batch_close.restype = None
+    lib.zflacb200_batch_pcm_bound.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(C.c_uint64)]
+    lib.zflacb200_batch_pcm_bound.restype = C.c_int
+    lib.zflacb200_batch_decode.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(Options),
+                                           C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64), C.POINTER(Info), C.POINTER(C.c_int)]
+    lib.zflacb200_batch_decode.restype = C.c_int
     lib.zflacb200_frames.argtypes = [C.c_void_p, C.POINTER(Frame), C.c_size_t, C.POINTER(C.c_size_t)]
     lib.zflacb200_frames.restype = C.c_int
     _lib = lib

@@ -74,6 +74,8 @@ struct EpilogueParams {
     uint32_t *lossy_flag;      // set to 1 if a shifted value no longer shifts back (MD5 must then hash pre-shift data)
 };
 cudaError_t launch_epilogue(const EpilogueParams &p, cudaStream_t st);
+// xfer.cu: copies `bytes` between device memory and PINNED host memory (either direction) from the SMs.
+cudaError_t launch_copy_small(void *dst, const void *src, size_t bytes, cudaStream_t st);
 cudaError_t launch_shift_inplace(void *pcm, uint64_t n_samples, uint32_t container_bytes, uint32_t shift, cudaStream_t st);
 
 struct Md5Job {
