@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """bench.py — headline benchmark of the B200 FLAC decode path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c3|c5] [--seconds S]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c3|c5|c2r] [--seconds S]
 
 One "step" = one pass of the whole hot path (K1 sync scan + CRC-16 frame link, K2 subframe decode,
 K3 decorrelate/shift/interleave; K4 MD5 gate reported separately) over one synthetic stream.
@@ -40,7 +40,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5", "c2r"])
     ap.add_argument("--seconds", type=float, default=None, help="stream length (default: c2 3600 s, c3 600 s)")
     ap.add_argument("--md5-steps", type=int, default=1, help="timed steps of the MD5-gated variant (serial chain, slow)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -214,6 +214,10 @@ def main():
     if args.workload == "c5":
         from tools import bench_batch
         bench_batch.run(args, rank, world, local_rank, METRIC, ClockSampler, measured_peak)
+        return
+    if args.workload == "c2r":  # ONE c2 stream over the ranks by frame range (strong scaling)
+        from tools import bench_range
+        bench_range.run(args, rank, world, local_rank, METRIC, ClockSampler, measured_peak)
         return
     if args.impl == "reference":
         run_reference(args, rank, world)

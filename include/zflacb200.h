@@ -170,6 +170,37 @@ int zflacb200_batch_decode(const uint8_t *blob, const uint64_t *offsets, const u
                            const zflacb200_options *opt, void *dst, size_t dst_bytes, uint64_t *pcm_offsets,
                            zflacb200_info *infos, int *statuses);
 
+/* Frame-range decode of ONE stream (several GPUs on one long stream): decodes the frames whose
+ * header starts in [byte_lo, byte_hi) of `data` — the part of decode_frames()' loop
+ * (src/zflac.zig:340-581) that falls into that byte range — and writes their PCM (interleaved,
+ * post MSB-align shift) to `dst`. `data`/`len` is the whole stream in host memory; only the range
+ * plus one maximum frame on either side is uploaded. Nothing links the shards on the device:
+ * a frame's sample position comes from its coded number, the reference's chain rule (frame k+1
+ * starts at the byte and at the sample where frame k ended, :546-548, :580) is checked INSIDE the
+ * shard with the decoded frame ends, and zflacb200_stitch() checks it ACROSS shards from the
+ * zflacb200_range each call returns, plus "first frame at the audio offset" and "covers exactly
+ * the stated total" (:341). A caller splits [0, len) into contiguous ranges, runs one call per
+ * GPU, gathers the n small structs and stitches; if a shard says accepted == 0 or the stitch
+ * fails (no stated total, numbering the hints misjudge, damage, any error case), the stream is
+ * decoded whole with zflacb200_decode(), which reports the reference's error. The MD5 gate is one
+ * serial chain over the whole PCM and is not run here (info.md5_checked = 0).
+ * Returns a metadata error exactly as zflacb200_open() would (every shard sees the same header),
+ * ZFLACB200_OUT_OF_MEMORY if dst is too small (range.n_samples says what is needed). */
+typedef struct zflacb200_range {
+    uint32_t struct_size;        /* sizeof(zflacb200_range), set by the caller */
+    uint32_t accepted;           /* 1: the shard decoded and its inner chain holds; 0: decode the stream whole */
+    uint64_t first_frame_offset; /* byte offset of the first frame decoded */
+    uint64_t end_offset;         /* one past the last byte of the last frame decoded */
+    uint64_t first_sample;       /* per-channel index of the first sample decoded */
+    uint64_t n_samples;          /* samples per channel decoded (dst receives n_samples * channels elements) */
+    uint64_t n_frames;           /* 0: no frame starts in the range (the shard is skipped by the stitch) */
+    uint64_t total_samples;      /* STREAMINFO total per channel, for the stitch */
+} zflacb200_range;
+int zflacb200_decode_range(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_lo, uint64_t byte_hi,
+                           void *dst, size_t dst_capacity, zflacb200_range *range, zflacb200_info *info);
+/* 1 if the n ranges (in stream order) are all accepted and link up into the one chain the reference walks, else 0. */
+int zflacb200_stitch(const zflacb200_range *ranges, size_t n, uint64_t audio_offset);
+
 /* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
 typedef struct zflacb200_frame {
     uint64_t offset;        /* byte offset of the sync code */

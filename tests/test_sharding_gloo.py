@@ -78,3 +78,94 @@ def test_size_balanced_is_balanced():
         loads = [sum(sizes[i] for i in s) for s in plan]
         assert sorted(i for s in plan for i in s) == list(range(1000))
         assert max(loads) - min(loads) <= max(sizes)
+
+
+# ---------------------------------------------------------------- frame-range sharding of one stream (host logic)
+
+def _rows_from_oracle(data, world):
+    """What zflacb200_decode_range would report per rank, computed from the oracle's frame trace (the checker)."""
+    from oracle import oracle
+    from zflac_b200 import sharding
+    r = oracle.decode(data, trace_frames=True)
+    assert r.error == "OK"
+    C = r.channels
+    fr = r.frames
+    names = fr.dtype.names
+    off, end, s0, bs = (fr[names[0]].astype(np.int64), fr[names[1]].astype(np.int64), fr[names[2]].astype(np.int64),
+                        fr[names[3]].astype(np.int64))
+    total = int(r.samples.size) // C
+    rows = []
+    for lo, hi in sharding.byte_ranges(len(data), world):
+        m = (off >= max(lo, r.audio_offset)) & (off < hi)
+        if not m.any():
+            rows.append([1, max(lo, r.audio_offset), max(lo, r.audio_offset), 0, 0, 0, total])
+            continue
+        rows.append([1, int(off[m][0]), int(end[m][-1]), int(s0[m][0]) // C, int(bs[m].sum()), int(m.sum()), total])
+    return rows, r.audio_offset
+
+
+def test_byte_ranges_partition():
+    from zflac_b200 import sharding
+    for n, world in ((0, 3), (5, 8), (1000, 1), (284_294_528, 8), (12345, 7)):
+        rg = sharding.byte_ranges(n, world)
+        assert len(rg) == world and rg[0][0] == 0 and rg[-1][1] == n
+        assert all(a[1] == b[0] for a, b in zip(rg, rg[1:])) and all(lo <= hi for lo, hi in rg)
+
+
+def test_stitch_rule_against_oracle_frames():
+    import zflac_b200 as z
+    from tools import flacgen as fg
+    s = fg.generate(fg.c2(3.0), want_pcm=False)
+    for world in (1, 2, 3, 8, 64):
+        rows, audio = _rows_from_oracle(s.flac, world)
+        assert z.stitch_ranges(rows, audio)
+        if world > 1:
+            for k, delta in ((1, 1), (2, -1), (3, 4096), (4, 1)):   # a byte gap, an overlap, a sample gap, a lost frame count
+                bad = [list(r) for r in rows]
+                j = next(i for i in range(1, world) if bad[i][5])
+                bad[j][k] += delta
+                if k in (1, 3):
+                    assert not z.stitch_ranges(bad, audio)
+            bad = [list(r) for r in rows]
+            bad[0][0] = 0                                            # a shard that was not accepted
+            assert not z.stitch_ranges(bad, audio)
+        short = [list(r) for r in rows]
+        short[-1][6] += 1                                            # stated total not reached
+        short[0][6] += 1
+        assert not z.stitch_ranges(short, audio)
+        assert not z.stitch_ranges(rows, audio + 1)                  # first frame not at the audio offset
+
+
+def _range_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import zflac_b200 as z
+        from tools import flacgen as fg
+        from zflac_b200 import sharding
+        s = fg.generate(fg.c2(2.0), want_pcm=False)
+        rows, audio = _rows_from_oracle(s.flac, world)
+        mine = rows[rank]                        # each rank contributes only its own shard's seven scalars
+        gathered = sharding.gather_rows(mine)
+        q.put((rank, gathered, rows, z.stitch_ranges(gathered, audio)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_range_rows_gather_and_stitch():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_range_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, gathered, rows, ok in res:
+        assert gathered == rows and ok           # every rank sees all shards' rows in rank order and reaches the same verdict

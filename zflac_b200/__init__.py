@@ -133,6 +133,65 @@ def decode_into(data, dst: np.ndarray, *, device: int = -1, verify_md5: bool = T
     return _info_dict(info)
 
 
+@dataclass
+class RangeResult:
+    """One shard of a frame-range decode (zflacb200_decode_range): the frames whose header starts in the byte range."""
+    accepted: bool
+    first_frame_offset: int
+    end_offset: int
+    first_sample: int
+    n_samples: int          # per channel
+    n_frames: int
+    total_samples: int      # STREAMINFO total per channel
+    samples: np.ndarray | None = None   # interleaved, n_samples * channels elements (None if not accepted / empty)
+    info: dict = field(default_factory=dict)
+
+    def as_row(self):
+        """The seven scalars the stitch needs, as int64 (what ranks all-gather)."""
+        return [int(self.accepted), self.first_frame_offset, self.end_offset, self.first_sample, self.n_samples, self.n_frames,
+                self.total_samples]
+
+
+def decode_range(data, byte_lo: int, byte_hi: int, dst: np.ndarray | None = None, *, device: int = -1,
+                 stream: int | None = None) -> RangeResult:
+    """Decodes the frames of ONE stream whose header starts in [byte_lo, byte_hi) (zflacb200_decode_range). `dst`, if
+    given, receives the shard's PCM (bytes; pinned memory for full PCIe speed); else a buffer sized from the byte range's
+    share of the stream's PCM (+ two maximum blocks) is allocated."""
+    lib = _native.load()
+    arr = _as_u8(data)
+    opt = _options(SKIP_MD5, device, stream)
+    info, rng = _native.Info(), _native.Range()
+    rng.struct_size = C.sizeof(_native.Range)
+    own = dst is None
+    if own:
+        dst = np.empty(0, dtype=np.uint8)
+    for attempt in range(2):
+        d8 = dst.view(np.uint8).reshape(-1)
+        st = lib.zflacb200_decode_range(arr.ctypes.data, arr.size, C.byref(opt), int(byte_lo), int(byte_hi),
+                                        d8.ctypes.data if d8.size else None, d8.nbytes, C.byref(rng), C.byref(info))
+        if st == 12 and own and attempt == 0:  # ZFLACB200_OUT_OF_MEMORY: now the size is known
+            dst = np.empty(int(info.pcm_bytes), dtype=np.uint8)
+            continue
+        break
+    if st != 0:
+        _raise(st)
+    samples = None
+    if rng.accepted and rng.n_frames:
+        samples = dst.view(np.uint8).reshape(-1)[:int(info.pcm_bytes)].view(_DTYPES[info.container_bytes])
+    return RangeResult(bool(rng.accepted), int(rng.first_frame_offset), int(rng.end_offset), int(rng.first_sample),
+                       int(rng.n_samples), int(rng.n_frames), int(rng.total_samples), samples, _info_dict(info))
+
+
+def stitch_ranges(rows, audio_offset: int) -> bool:
+    """zflacb200_stitch over RangeResult objects or their as_row() lists, in stream order."""
+    rows = [r.as_row() if isinstance(r, RangeResult) else [int(x) for x in r] for r in rows]
+    buf = (_native.Range * max(len(rows), 1))()
+    for b, r in zip(buf, rows):
+        b.struct_size = C.sizeof(_native.Range)
+        b.accepted, b.first_frame_offset, b.end_offset, b.first_sample, b.n_samples, b.n_frames, b.total_samples = r
+    return bool(_native.load().zflacb200_stitch(buf, len(rows), int(audio_offset)))
+
+
 class DeviceStream:
     """A decoded stream whose PCM stays in HBM (zflacb200_open with ZFLACB200_INPUT_ON_DEVICE)."""
 

@@ -21,6 +21,7 @@ EXPORTS = [
     "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_frames", "zflacb200_batch_open",
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
     "zflacb200_batch_close", "zflacb200_batch_pcm_bound", "zflacb200_batch_decode",
+    "zflacb200_decode_range", "zflacb200_stitch",
 ]
 
 
@@ -36,6 +37,12 @@ class Info(C.Structure):
                 ("n_crc16_mismatch", C.c_uint64), ("fast_path", C.c_uint64), ("md5_computed", C.c_uint8 * 16),
                 ("md5_streaminfo", C.c_uint8 * 16), ("ms_scan", C.c_float), ("ms_link", C.c_float),
                 ("ms_decode", C.c_float), ("ms_epilogue", C.c_float), ("ms_md5", C.c_float), ("ms_total", C.c_float)]
+
+
+class Range(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("accepted", C.c_uint32), ("first_frame_offset", C.c_uint64),
+                ("end_offset", C.c_uint64), ("first_sample", C.c_uint64), ("n_samples", C.c_uint64),
+                ("n_frames", C.c_uint64), ("total_samples", C.c_uint64)]
 
 
 class Frame(C.Structure):
@@ -89,6 +96,11 @@ def load():
     lib.zflacb200_batch_device_pcm.restype = C.c_int
     lib.zflacb200_batch_close.argtypes = [C.c_void_p]
     lib.zflacb200_batch_close.restype = None
+    lib.zflacb200_decode_range.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.c_uint64, C.c_uint64, C.c_void_p,
+                                           C.c_size_t, C.POINTER(Range), C.POINTER(Info)]
+    lib.zflacb200_decode_range.restype = C.c_int
+    lib.zflacb200_stitch.argtypes = [C.POINTER(Range), C.c_size_t, C.c_uint64]
+    lib.zflacb200_stitch.restype = C.c_int
     lib.zflacb200_batch_pcm_bound.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(C.c_uint64)]
     lib.zflacb200_batch_pcm_bound.restype = C.c_int
     lib.zflacb200_batch_decode.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_size_t, C.POINTER(Options),

@@ -1564,6 +1564,218 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     info->audio_bytes = sum.end_offset - audio_offset;
     return ZFLACB200_OK;
 }
+
+// ---- frame-range decode of one stream: the shard's frames through the same K1 / K1h / K2a / K3p / K1v
+// kernels as the whole-stream fast path. What changes is bookkeeping only: slot 0 of the candidate list is the stream's
+// first frame (scanned from a 4 KiB head upload) so every shard judges its candidates against the same reference
+// header; the scan starts one maximum frame below the shard so the first frame of the shard finds its predecessor;
+// PCM and scratch positions are made relative to the shard's first sample by a first pass of the hint kernel.
+int decode_range_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_lo, uint64_t byte_hi, void *dst,
+                      size_t dst_capacity, zflacb200_range *out, zflacb200_info *info) {
+    if (!data || !out || !info || out->struct_size < sizeof(zflacb200_range) || (!dst && dst_capacity)) {
+        g_last_error = "null argument or zflacb200_range.struct_size not set";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    memset(info, 0, sizeof(*info));
+    memset((uint8_t *)out + 4, 0, sizeof(*out) - 4);
+    const uint32_t flags = (opt ? opt->flags : 0) | env_flags();
+    if (flags & ZFLACB200_INPUT_ON_DEVICE) {
+        g_last_error = "zflacb200_decode_range takes host input";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    int device = -1;
+    {
+        const int e = ensure_device(opt ? opt->device : -1, &device);
+        if (e != ZFLACB200_OK) return e;
+    }
+    DeviceCtx &ctx = g_ctx[device];
+    cudaStream_t st = (opt && opt->stream) ? (cudaStream_t)opt->stream : ctx.stream;
+    HostTrace tr("decode_range");
+
+    ByteSource src;
+    src.host = data;
+    src.len = len;
+    Streaminfo si;
+    uint64_t audio_offset = 0;
+    {
+        const int e = parse_metadata(src, si, audio_offset);
+        if (e != ZFLACB200_OK) return e;  // every shard reports what decode() reports (:220, :248, :309)
+    }
+    const uint32_t C = si.channels_m1 + 1;
+    const uint32_t depth = si.depth_m1 + 1, aligned = (depth + 7u) & ~7u;
+    const uint32_t cb = aligned == 8 ? 1 : aligned == 16 ? 2 : 4;
+    uint32_t msb_shift = 0;
+    if (depth >= 9 && depth <= 15) msb_shift = 16 - depth;
+    else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
+    info->audio_offset = audio_offset;
+    info->container_bytes = (uint8_t)cb;
+    memcpy(info->md5_streaminfo, si.md5, 16);
+    out->total_samples = si.total;
+    Hdr h0;
+    if (si.total == 0 || si.total * C >= (1ull << 40) || host_parse_header(src, audio_offset, h0) != ZFLACB200_OK)
+        return ZFLACB200_OK;  // accepted = 0: the whole-stream path decides what this stream is
+    const uint32_t bps0 = h0.bd_code == 0 ? depth : kBps[h0.bd_code];
+    const bool wide = bps0 == 32;
+    info->channels = (uint8_t)C;
+    info->bits_per_sample = (uint8_t)bps0;                                                 // :381-384
+    info->sample_rate = (h0.sr_code == 0 ? si.sample_rate : h0.sr_value) & 0xFFFFFFu;     // :376-379
+
+    // ---- what to scan and what to upload
+    const uint64_t lo = std::min<uint64_t>(std::max<uint64_t>(byte_lo, audio_offset), len);
+    const uint64_t hi = std::min<uint64_t>(std::max<uint64_t>(byte_hi, lo), len);
+    const uint32_t max_bs = si.max_block >= 16 ? si.max_block : 65535;
+    uint64_t max_frame = si.max_frame ? (uint64_t)si.max_frame + 16 : 32 + (uint64_t)max_bs * C * ((depth + 1 + 7) / 8 + 1);
+    max_frame = std::min<uint64_t>(std::max<uint64_t>(max_frame, 64u << 10), 4u << 20);
+    const uint64_t scan_lo = std::max<uint64_t>(audio_offset, lo > max_frame ? lo - max_frame : 0);
+    const uint64_t up_lo = scan_lo & ~4095ull;
+    const uint64_t up_hi = std::min<uint64_t>(len, hi + max_frame + 4096);
+    const uint64_t head_lo = audio_offset & ~4095ull;
+    const uint64_t head_hi = std::min<uint64_t>(len, audio_offset + 64);
+    if (hi <= lo) {  // nothing starts here
+        out->accepted = 1;
+        out->first_frame_offset = out->end_offset = lo;
+        return ZFLACB200_OK;
+    }
+    const uint64_t cap64 = (hi - scan_lo) / 256 + 4096;
+    if (cap64 > 0x3FFFFFFFull) return ZFLACB200_OK;
+    const uint32_t cap = (uint32_t)cap64;
+    const uint32_t n_tiles = scan_tile_count(scan_lo, hi) + 2;
+
+    DevBuf b_stream, b_head, b_cands, b_total, b_tiles, b_ticket, b_sd, b_recs, b_outs, b_ok, b_sum, b_flag, b_lohi, b_scratch, b_pcm;
+    SubframeStage stage;
+    if (b_stream.alloc(((up_hi - up_lo + 15) & ~15ull) + 64, st) || b_head.alloc(4096 + 64 + 64, st) ||
+        b_cands.alloc(sizeof(Cand) * (size_t)cap, st) || b_total.alloc(sizeof(uint32_t), st) ||
+        b_tiles.alloc(sizeof(unsigned long long) * n_tiles, st) || b_ticket.alloc(sizeof(uint32_t), st) ||
+        b_sd.alloc(sizeof(StreamDesc), st) || b_recs.alloc(sizeof(FrameRec) * (size_t)cap, st) ||
+        b_outs.alloc(sizeof(FrameOut) * (size_t)cap, st) || b_ok.alloc(cap, st) || b_sum.alloc(sizeof(StreamSummary), st) ||
+        b_flag.alloc(sizeof(uint32_t), st) || b_lohi.alloc(4 * sizeof(unsigned long long), st))
+        return ZFLACB200_CUDA_ERROR;
+    Events ev;
+    if (ev.init() != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(cudaEventRecord(ev.e[0], st));
+    CU_CHECK(cudaMemcpyAsync(b_head.p, data + head_lo, head_hi - head_lo, cudaMemcpyHostToDevice, st));
+    CU_CHECK(cudaMemcpyAsync(b_stream.p, data + up_lo, up_hi - up_lo, cudaMemcpyHostToDevice, st));
+    CU_CHECK(cudaEventRecord(ev.e[1], st));  // upload done
+    const uint8_t *d_head = (const uint8_t *)b_head.p - head_lo;    // absolute stream offsets index both buffers
+    const uint8_t *d_stream = (const uint8_t *)b_stream.p - up_lo;
+    Cand *d_cands = (Cand *)b_cands.p;
+    FrameRec *d_recs = (FrameRec *)b_recs.p;
+    FrameOut *d_outs = (FrameOut *)b_outs.p;
+    StreamSummary *d_sum = (StreamSummary *)b_sum.p;
+    unsigned long long *d_lohi = (unsigned long long *)b_lohi.p;
+
+    // ---- K1 twice: the stream's first header into slot 0, the shard's candidates behind it
+    CU_CHECK(launch_sync_scan_range(d_head, audio_offset, audio_offset + 1, head_hi, d_cands, 1, (uint32_t *)b_total.p,
+                                    (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
+    GET_SMALL(h_m0, ctx, b_total.p, sizeof(uint32_t), st);
+    CU_CHECK(launch_sync_scan_range(d_stream, scan_lo, hi, up_hi, d_cands + 1, cap - 1, (uint32_t *)b_total.p,
+                                    (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
+    GET_SMALL(h_m, ctx, b_total.p, sizeof(uint32_t), st);
+    CU_CHECK(cudaEventRecord(ev.e[2], st));
+    CU_CHECK(cudaStreamSynchronize(st));
+    const uint32_t m0 = *(const uint32_t *)h_m0, m = *(const uint32_t *)h_m;
+    tr.mark("upload+scan");
+    if (m0 != 1 || m > cap - 1) return ZFLACB200_OK;  // accepted = 0
+    const uint32_t n = 1 + m;
+    info->n_candidates = m;
+
+    // ---- K1h, first pass: which records stay, and where the shard starts (samples, bytes)
+    StreamDesc sd;
+    memset(&sd, 0, sizeof(sd));
+    sd.begin = 0;
+    sd.end = up_hi;  // nothing above the uploaded bytes is readable: a frame that runs past them fails the shard
+    sd.audio_begin = audio_offset;
+    sd.total = si.total;
+    sd.si_sample_rate = si.sample_rate;
+    sd.si_channels = (uint8_t)C;
+    sd.si_depth = (uint8_t)depth;
+    const uint32_t window = 16;
+    const unsigned long long lohi0[4] = {~0ull, ~0ull, 0ull, 0ull};  // min sample_base, min offset, kept, max sample end
+    CU_CHECK(put_small(ctx, b_sd.p, &sd, sizeof(sd), st));
+    CU_CHECK(put_small(ctx, d_lohi, lohi0, sizeof(lohi0), st));
+    CU_CHECK(cudaMemsetAsync(d_recs, 0, sizeof(FrameRec), st));  // slot 0 is never a record
+    RangeHint rh;
+    rh.decode_lo = lo;
+    rh.window_floor = 1;
+    rh.lo_out = d_lohi;
+    CU_CHECK(launch_hint_chain_shard(d_cands, 1, n, (const StreamDesc *)b_sd.p, 1, d_recs, window, d_lohi + 3, rh, st));
+    GET_SMALL(h_lohi, ctx, d_lohi, sizeof(lohi0), st);
+    CU_CHECK(cudaStreamSynchronize(st));
+    unsigned long long lohi[4];
+    memcpy(lohi, h_lohi, sizeof(lohi));
+    if (lohi[2] == 0) {  // no frame starts in [lo, hi): a shard thinner than one frame
+        out->accepted = 1;
+        out->first_frame_offset = out->end_offset = lo;
+        return ZFLACB200_OK;
+    }
+    if (lohi[0] % C != 0 || lohi[3] <= lohi[0]) return ZFLACB200_OK;
+    const uint64_t first_sample = lohi[0] / C, n_elems = lohi[3] - lohi[0];
+    out->first_sample = first_sample;
+    out->n_samples = n_elems / C;
+    out->first_frame_offset = lohi[1];
+    info->n_samples = n_elems;
+    info->pcm_bytes = n_elems * cb;
+    if (dst_capacity < n_elems * cb) {
+        g_last_error = "destination too small for the shard's PCM";
+        return ZFLACB200_OUT_OF_MEMORY;
+    }
+
+    // ---- second pass with positions relative to the shard (unsigned wrap-around: base + absolute = relative)
+    sd.pcm_base = 0ull - lohi[0];
+    sd.scratch_base = 0ull - (uint64_t)C * ((first_sample + 7) & ~7ull);
+    const uint64_t scratch_elems = (uint64_t)C * (((out->n_samples + 7) & ~7ull) + 16) + 64ull * n + 64;
+    if (b_scratch.alloc(scratch_elems * (wide ? 8 : 4), st) || b_pcm.alloc(((n_elems + 15) & ~15ull) * cb + 64, st) ||
+        stage.prepare(wide, flags, n, st) != ZFLACB200_OK)
+        return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(put_small(ctx, b_sd.p, &sd, sizeof(sd), st));
+    rh.lo_out = nullptr;
+    CU_CHECK(launch_hint_chain_shard(d_cands, 1, n, (const StreamDesc *)b_sd.p, 1, d_recs, window, nullptr, rh, st));
+    CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary), st));
+    CU_CHECK(cudaMemsetAsync(b_ok.p, 2, n, st));
+    CU_CHECK(cudaMemsetAsync(b_flag.p, 0, sizeof(uint32_t), st));
+    CU_CHECK(cudaMemsetAsync(d_outs, 0xFF, sizeof(FrameOut) * (size_t)n, st));
+    CU_CHECK(cudaEventRecord(ev.e[3], st));
+    if (stage.decode(d_stream, d_recs, n, b_scratch.p, wide, d_outs, true, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(cudaEventRecord(ev.e[4], st));
+    CU_CHECK(launch_crc16_frames(d_stream, d_recs, d_outs, n, d_sum, (uint8_t *)b_ok.p, st));
+    CU_CHECK(launch_verify_chain(d_cands, n, (const StreamDesc *)b_sd.p, 1, d_recs, d_outs, d_sum, window, st, true));
+    EpilogueParams ep;
+    ep.frames = d_recs;
+    ep.n_frames = n;
+    ep.max_block_size = max_bs;
+    ep.scratch = b_scratch.p;
+    ep.wide_scratch = wide;
+    ep.pcm = b_pcm.p;
+    ep.container_bytes = cb;
+    ep.msb_shift = msb_shift;
+    ep.lossy_flag = (uint32_t *)b_flag.p;
+    if (stage.epilogue(ep, d_outs, C, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(cudaEventRecord(ev.e[5], st));
+    GET_SMALL(h_sum, ctx, b_sum.p, sizeof(StreamSummary), st);
+    GET_SMALL(h_lossy, ctx, b_flag.p, sizeof(uint32_t), st);
+    CU_CHECK(cudaMemcpyAsync(dst, b_pcm.p, n_elems * cb, cudaMemcpyDeviceToHost, st));  // an unaccepted shard's bytes are garbage
+    CU_CHECK(cudaEventRecord(ev.e[7], st));
+    CU_CHECK(cudaStreamSynchronize(st));
+    tr.mark("decode+readback");
+    StreamSummary sum;
+    memcpy(&sum, h_sum, sizeof(sum));
+    const uint32_t lossy = *(const uint32_t *)h_lossy;
+    info->ms_scan = ev_ms(ev.e[1], ev.e[2]);      // the kernels only: upload (e0..e1) and read-back (e5..e7) are in ms_total
+    info->ms_link = ev_ms(ev.e[2], ev.e[3]);      // both hint passes, with the host round trip between them
+    info->ms_decode = ev_ms(ev.e[3], ev.e[4]);    // K2a
+    info->ms_epilogue = ev_ms(ev.e[4], ev.e[5]);  // CRC-16 + chain check + K3p
+    info->ms_total = ev_ms(ev.e[0], ev.e[7]);
+    info->n_frames = sum.n_frames;
+    info->n_crc16_mismatch = sum.n_crc16_mismatch;
+    info->audio_bytes = sum.end_offset > lohi[1] ? sum.end_offset - lohi[1] : 0;
+    out->n_frames = sum.n_frames;
+    out->end_offset = sum.end_offset;
+    const bool accepted = !sum.fail && sum.n_frames == lohi[2] && sum.n_samples == n_elems && !(msb_shift && lossy) &&
+                          sum.end_offset > lohi[1];
+    out->accepted = accepted ? 1u : 0u;
+    info->fast_path = accepted ? 1 : 0;
+    return ZFLACB200_OK;
+}
 }  // namespace
 
 extern "C" {
@@ -1680,6 +1892,32 @@ int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *o
     else r = zflacb200_read(h, dst, dst_capacity);
     zflacb200_close(h);
     return r;
+}
+
+int zflacb200_decode_range(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_lo, uint64_t byte_hi,
+                           void *dst, size_t dst_capacity, zflacb200_range *range, zflacb200_info *info) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    g_last_error.clear();
+    pin_rewind_all();
+    return decode_range_impl(data, len, opt, byte_lo, byte_hi, dst, dst_capacity, range, info);
+}
+
+// The reference's chain rule across shards: the first frame sits at the audio offset and holds sample 0 (:340), every
+// shard starts at the byte and at the sample where the one before ended (:546-548, :580), the chain covers exactly the
+// stated total (:341). Shards in which no frame starts are skipped.
+int zflacb200_stitch(const zflacb200_range *r, size_t n, uint64_t audio_offset) {
+    if (!r || n == 0) return 0;
+    uint64_t next_offset = audio_offset, next_sample = 0;
+    bool any = false;
+    for (size_t i = 0; i < n; ++i) {
+        if (!r[i].accepted) return 0;
+        if (r[i].n_frames == 0) continue;
+        if (r[i].first_frame_offset != next_offset || r[i].first_sample != next_sample) return 0;
+        next_offset = r[i].end_offset;
+        next_sample = r[i].first_sample + r[i].n_samples;
+        any = true;
+    }
+    return any && next_sample == r[0].total_samples ? 1 : 0;
 }
 
 int zflacb200_batch_open(const uint8_t *blob, const uint8_t *device_blob, const uint64_t *offsets, const uint64_t *lens,

@@ -54,7 +54,7 @@ __device__ __forceinline__ bool hint_of(const Cand &c, const Cand &ref, const St
 
 __global__ void __launch_bounds__(kChainThreads)
 k_hint_chain(const Cand *__restrict__ cands, uint32_t first, uint32_t n, const StreamDesc *__restrict__ streams, uint32_t n_streams,
-             FrameRec *__restrict__ recs, uint32_t window, unsigned long long *__restrict__ pcm_hi) {
+             FrameRec *__restrict__ recs, uint32_t window, unsigned long long *__restrict__ pcm_hi, RangeHint rh) {
     const uint32_t i = first + blockIdx.x * kChainThreads + threadIdx.x;
     if (i >= n) return;
     const Cand c = cands[i];
@@ -79,16 +79,19 @@ k_hint_chain(const Cand *__restrict__ cands, uint32_t first, uint32_t n, const S
         const uint32_t bps = ref.bd_code == 0 ? sd.si_depth : c_bps_of_code[ref.bd_code];
         if (ref.offset == sd.audio_begin && ref.bd_code != 3 && c_ch_count[ref.ch_code] == sd.si_channels &&  // :386
             hint_of(c, ref, sd, start)) {
-            if (i == r) {
+            if (c.offset == sd.audio_begin) {
                 keep = start == 0;
             } else {  // some earlier candidate must end, by its own hint, where this one starts
-                const uint32_t lo = i - r > window ? i - window : r;
+                const uint32_t floor_j = r > rh.window_floor ? r : rh.window_floor;  // range decode: slot 0 is a stand-in
+                const uint32_t lo = i - floor_j > window ? i - window : floor_j;
                 for (uint32_t j = i; j-- > lo && !keep;) {
                     const Cand p = cands[j];
                     uint64_t ps;
                     keep = hint_of(p, ref, sd, ps) && ps + p.block_size == start;
                 }
             }
+            // range decode: candidates below the shard are predecessors for the rule above only
+            if (c.offset < rh.decode_lo) keep = false;
             if (keep) {
                 const uint32_t C = sd.si_channels;
                 fr.stream_end = sd.end;
@@ -101,6 +104,11 @@ k_hint_chain(const Cand *__restrict__ cands, uint32_t first, uint32_t n, const S
                 fr.channels = (uint8_t)C;
                 fr.bps = (uint8_t)bps;
                 if (pcm_hi) atomicMax(pcm_hi, (unsigned long long)(fr.sample_base + (uint64_t)c.block_size * C));
+                if (rh.lo_out) {  // range decode, first pass: where the shard starts, in samples and in bytes
+                    atomicMin(rh.lo_out, (unsigned long long)fr.sample_base);
+                    atomicMin(rh.lo_out + 1, (unsigned long long)c.offset);
+                    atomicAdd(rh.lo_out + 2, 1ull);
+                }
             }
         }
     }
@@ -110,7 +118,7 @@ k_hint_chain(const Cand *__restrict__ cands, uint32_t first, uint32_t n, const S
 __global__ void __launch_bounds__(kChainThreads)
 k_verify_chain(const Cand *__restrict__ cands, uint32_t n, const StreamDesc *__restrict__ streams, uint32_t n_streams,
                const FrameRec *__restrict__ recs, const FrameOut *__restrict__ outs, StreamSummary *__restrict__ sums,
-               uint32_t window) {
+               uint32_t window, uint32_t open_end) {
     const uint32_t i = blockIdx.x * kChainThreads + threadIdx.x;
     if (i >= n) return;
     const FrameRec fr = recs[i];
@@ -135,8 +143,8 @@ k_verify_chain(const Cand *__restrict__ cands, uint32_t n, const StreamDesc *__r
     } else if (j < n && cands[j].offset < sd.end) {
         ok = false;  // more candidates than the window covers: cannot tell, let the host walk
     } else {
-        ok = ok && s_end == total_end;  // the chain must cover exactly the stated total (:341)
-        sums[sid].end_offset = o.end_offset;
+        if (!open_end) ok = ok && s_end == total_end;  // the chain must cover exactly the stated total (:341)
+        sums[sid].end_offset = o.end_offset;        // (range decode: the host checks the ends of adjacent shards instead)
     }
     if (fr.offset == sd.audio_begin) {  // head of the chain: latch what DecodedFLAC reports (:376-388)
         const Cand c = cands[i];
@@ -177,20 +185,25 @@ cudaError_t launch_hint_chain(const Cand *d_cands, uint32_t n, const StreamDesc 
 
 cudaError_t launch_hint_chain_range(const Cand *d_cands, uint32_t first, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
                                     FrameRec *d_recs, uint32_t window, unsigned long long *d_pcm_hi, cudaStream_t st) {
+    return launch_hint_chain_shard(d_cands, first, n, d_streams, n_streams, d_recs, window, d_pcm_hi, RangeHint{}, st);
+}
+
+cudaError_t launch_hint_chain_shard(const Cand *d_cands, uint32_t first, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
+                                    FrameRec *d_recs, uint32_t window, unsigned long long *d_pcm_hi, RangeHint rh, cudaStream_t st) {
     if (n <= first) return cudaSuccess;
     ZF_COUNT_LAUNCH();
     k_hint_chain<<<(n - first + kChainThreads - 1) / kChainThreads, kChainThreads, 0, st>>>(d_cands, first, n, d_streams, n_streams,
-                                                                                            d_recs, window, d_pcm_hi);
+                                                                                            d_recs, window, d_pcm_hi, rh);
     return cudaGetLastError();
 }
 
 cudaError_t launch_verify_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
                                 const FrameRec *d_recs, const FrameOut *d_outs, StreamSummary *d_sums, uint32_t window,
-                                cudaStream_t st) {
+                                cudaStream_t st, bool open_end) {
     if (n == 0) return cudaSuccess;
     ZF_COUNT_LAUNCH();
     k_verify_chain<<<(n + kChainThreads - 1) / kChainThreads, kChainThreads, 0, st>>>(d_cands, n, d_streams, n_streams, d_recs,
-                                                                                      d_outs, d_sums, window);
+                                                                                      d_outs, d_sums, window, open_end ? 1u : 0u);
     return cudaGetLastError();
 }
 

@@ -33,9 +33,20 @@ cudaError_t launch_hint_chain(const Cand *d_cands, uint32_t n, const StreamDesc 
 // largest PCM element end among the kept records (what may be copied out once these frames are decoded).
 cudaError_t launch_hint_chain_range(const Cand *d_cands, uint32_t first, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
                                     FrameRec *d_recs, uint32_t window, unsigned long long *d_pcm_hi, cudaStream_t st);
+// Range decode of ONE stream (a shard of its frames): slot 0 of the candidate list is a stand-in for the
+// stream's first frame (window_floor = 1 keeps it out of the predecessor search), candidates below decode_lo only serve
+// as predecessors, and lo_out (optional) receives {min sample_base, min offset, count} of the records kept.
+struct RangeHint {
+    uint64_t decode_lo = 0;
+    uint32_t window_floor = 0;
+    unsigned long long *lo_out = nullptr;
+};
+cudaError_t launch_hint_chain_shard(const Cand *d_cands, uint32_t first, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
+                                    FrameRec *d_recs, uint32_t window, unsigned long long *d_pcm_hi, RangeHint rh, cudaStream_t st);
+// open_end: the last record of the chain need not end at the stream's total (range decode: the host checks adjacent shards)
 cudaError_t launch_verify_chain(const Cand *d_cands, uint32_t n, const StreamDesc *d_streams, uint32_t n_streams,
                                 const FrameRec *d_recs, const FrameOut *d_outs, StreamSummary *d_sums, uint32_t window,
-                                cudaStream_t st);
+                                cudaStream_t st, bool open_end = false);
 
 // decode.cu
 cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, void *d_scratch,

@@ -48,3 +48,40 @@ def job_max(value: float, device=None) -> float:
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+# ---------------------------------------------------------------- frame-range sharding of ONE stream (SURVEY §8e)
+
+def byte_ranges(n_bytes: int, world: int) -> List[tuple]:
+    """[lo, hi) of each rank: equal contiguous pieces of the stream's bytes (a frame belongs to the rank its header
+    starts in; the library clamps the first range to the audio offset)."""
+    cut = [n_bytes * r // world for r in range(world + 1)]
+    return [(cut[r], cut[r + 1]) for r in range(world)]
+
+
+def gather_rows(row: Sequence[int], device=None) -> List[List[int]]:
+    """All ranks' rows (small int64 vectors), in rank order. No process group: just this rank's."""
+    import torch
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+        return [[int(x) for x in row]]
+    t = torch.tensor([int(x) for x in row], dtype=torch.int64, device=device)
+    out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return [[int(x) for x in o.tolist()] for o in out]
+
+
+def decode_sharded(data, *, rank: int, world: int, device: int = -1, dst=None, gather_device=None):
+    """One long stream over `world` GPUs, one process each: this rank decodes the frames that start in its byte range
+    (zflac_b200.decode_range), the ranks exchange seven scalars each and every rank checks that the shards link up into
+    the chain the reference walks (zflacb200_stitch). Returns (RangeResult of this rank, stitched: bool). When the
+    stitch fails every rank knows it (same rows everywhere) and the caller decodes the stream whole on one rank
+    (zflac_b200.decode), which also reports the reference's error for a bad stream. No bulk data crosses ranks."""
+    import zflac_b200 as z
+
+    n = len(data) if not hasattr(data, "nbytes") else int(data.nbytes)
+    lo, hi = byte_ranges(n, world)[rank]
+    res = z.decode_range(data, lo, hi, dst, device=device)
+    rows = gather_rows(res.as_row(), device=gather_device)
+    return res, z.stitch_ranges(rows, int(res.info["audio_offset"]))
