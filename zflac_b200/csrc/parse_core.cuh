@@ -53,77 +53,89 @@ ZF_HDI uint32_t parse_residual(BitReader<Src> &br, int32_t *__restrict__ out, ui
     if ((psize << po) != block_size || psize < order) return ST_UNDEFINED_IN_REFERENCE;  // Q16
     uint32_t err = ST_OK;
     uint32_t i = order;
+    // ONE loop over partitions and rows. With a partition loop around a row loop, the lanes of a warp meet again at
+    // the end of every partition: a lane with 16 partitions of 256 next to a lane with one partition of 4096 would
+    // idle through 4096 rows and then run its other 15 partitions alone (1.9x the work of either). Here a partition
+    // boundary is a short detour inside the row loop and the 8-row bodies of all lanes run together whatever their
+    // partition layout is.
+    const uint32_t nparts = 1u << po;
+    uint32_t part = 0, end = order;  // "partition -1" ends where the residual starts
+    uint32_t k = 0, kp1 = 1, pk = 1;
+    uint32_t force_single = 0;
+    uint32_t tick = 0;  // body count: warp-uniform, so the word source's every-other-body refill stays in step
 #pragma unroll 1
-    for (uint32_t part = 0; part < (1u << po); ++part) {
-        const uint32_t param = br.read(pbits);
-        const uint32_t end = (part + 1) * psize;
-        if (param == (1u << pbits) - 1u) {  // escape: raw signed residuals of esc bits (:646-654)
-            const uint32_t esc = br.read(5);
+    for (;;) {
+        if (i >= end) {  // partition boundary
+            if (part && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
+            if (part == nparts) break;
+            const uint32_t param = br.read(pbits);
+            end = (part + 1) * psize;
+            ++part;
+            if (param == (1u << pbits) - 1u) {  // escape: raw signed residuals of esc bits (:646-654)
+                const uint32_t esc = br.read(5);
 #pragma unroll 1
-            for (; i < end; ++i) {
-                const int32_t r = esc ? br.read_signed(esc) : 0;
-                if (wr) out[sub_idx(i, c8)] = r;
-                if ((i & 255u) == 255u && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
+                for (; i < end; ++i) {
+                    const int32_t r = esc ? br.read_signed(esc) : 0;
+                    if (wr) out[sub_idx(i, c8)] = r;
+                    if ((i & 255u) == 255u && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
+                }
+                continue;
             }
-        } else {
-            const uint32_t k = param, kp1 = param + 1;
-            uint32_t pk = 1u << param;
+            k = param;
+            kp1 = param + 1;
+            pk = 1u << param;
 #ifdef __CUDA_ARCH__
             asm("" : "+r"(pk));  // keep z * pk an IMAD (FMA pipe): the ALU pipe carries the bit chain
 #endif
-            uint32_t force_single = 0;
-#pragma unroll 1
-            while (i < end) {
-                if (force_single == 0 && (i & 7u) == 0 && i + 8 <= end) {
-                    // 8 codewords, speculative and branch-free; a codeword longer than the 32-bit window
-                    // (rare) only raises zmax: the body is rolled back and redone row by row
-                    br.prepare_fast(i >> 3);
-                    const uint32_t sA = br.A, sB = br.B, sN = br.N, so = br.o;
-                    uint32_t ws = br.enter_fast();
-                    uint32_t zmax = 0;
-                    int32_t r[8];
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) {
-                        const uint32_t win = br.peek();
-                        const uint32_t z = clz_sh(win);                                   // unary part (0xFFFFFFFF: no stop bit in sight)
-                        zmax = zmax > z ? zmax : z;
-                        const uint32_t low = funnel_hi(0u, shl_c(win, z + 1), k);        // the k bits after the stop bit
-                        const uint32_t cw = z * pk + low;                                 // (z << k) | low on the IMAD pipe
-                        br.skip_fast(z + kp1, ws);
-                        r[u] = zigzag(cw);
-                    }
-                    if (zmax <= 31u - k) {  // every codeword fitted the 32-bit window
-                        if (wr) {
-                            int32_t *dst = out + (size_t)(i >> 3) * c8;  // i is a multiple of 8
-                            *reinterpret_cast<int4 *>(dst) = make_int4(r[0], r[1], r[2], r[3]);
-                            *reinterpret_cast<int4 *>(dst + 4) = make_int4(r[4], r[5], r[6], r[7]);
-                        }
-                        br.leave_fast(ws);
-                        i += 8;
-                    } else {
-                        br.A = sA; br.B = sB; br.N = sN; br.o = so;
-                        br.src.note_rollback();
-                        force_single = 8;
-                    }
-                } else {
-                    const uint32_t win = br.peek();
-                    const uint32_t z = clz32(win);
-                    const uint32_t n = z + kp1;
-                    uint32_t cw;
-                    if (n <= 32) {
-                        cw = (z << k) | shr_c(shl_c(win, z + 1), 32 - k);
-                        br.template skip<true>(n);
-                    } else {
-                        cw = rice_slow(br, k, len_bits, err);
-                    }
-                    if (wr) out[sub_idx(i, c8)] = zigzag(cw);
-                    ++i;
-                    if (force_single) --force_single;
-                    if (err != ST_OK) return err;
-                }
-            }
+            if (i >= end) continue;  // a first partition that holds warm-up samples only
         }
-        if (br.pos_bits() > len_bits) return ST_END_OF_STREAM;
+        if (force_single == 0 && (i & 7u) == 0 && i + 8 <= end) {
+            // 8 codewords, speculative and branch-free; a codeword longer than the 32-bit window
+            // (rare) only raises zmax: the body is rolled back and redone row by row
+            br.prepare_fast(tick++);
+            const uint32_t sA = br.A, sB = br.B, sN = br.N, so = br.o;
+            uint32_t ws = br.enter_fast();
+            uint32_t zmax = 0;
+            int32_t r[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint32_t win = br.peek();
+                const uint32_t z = clz_sh(win);                                   // unary part (0xFFFFFFFF: no stop bit in sight)
+                zmax = zmax > z ? zmax : z;
+                const uint32_t low = funnel_hi(0u, shl_c(win, z + 1), k);        // the k bits after the stop bit
+                const uint32_t cw = z * pk + low;                                 // (z << k) | low on the IMAD pipe
+                br.skip_fast(z + kp1, ws);
+                r[u] = zigzag(cw);
+            }
+            if (zmax <= 31u - k) {  // every codeword fitted the 32-bit window
+                if (wr) {
+                    int32_t *dst = out + (size_t)(i >> 3) * c8;  // i is a multiple of 8
+                    *reinterpret_cast<int4 *>(dst) = make_int4(r[0], r[1], r[2], r[3]);
+                    *reinterpret_cast<int4 *>(dst + 4) = make_int4(r[4], r[5], r[6], r[7]);
+                }
+                br.leave_fast(ws);
+                i += 8;
+            } else {
+                br.A = sA; br.B = sB; br.N = sN; br.o = so;
+                br.src.note_rollback();
+                force_single = 8;
+            }
+        } else {
+            const uint32_t win = br.peek();
+            const uint32_t z = clz32(win);
+            const uint32_t n = z + kp1;
+            uint32_t cw;
+            if (n <= 32) {
+                cw = (z << k) | shr_c(shl_c(win, z + 1), 32 - k);
+                br.template skip<true>(n);
+            } else {
+                cw = rice_slow(br, k, len_bits, err);
+            }
+            if (wr) out[sub_idx(i, c8)] = zigzag(cw);
+            ++i;
+            if (force_single) --force_single;
+            if (err != ST_OK) return err;
+        }
     }
     return ST_OK;
 }
