@@ -1349,14 +1349,25 @@ struct EventList {
     }
 };
 
+// Two forms: host stream in / host PCM out (zflacb200_decode: `dst`), and device stream in / PCM left in HBM behind a
+// handle (zflacb200_open with ZFLACB200_INPUT_ON_DEVICE: `handle_out`). The second has no copies to overlap, but the
+// chunks still pay: chunk i's frame-serial kernels start as soon as ITS scan is done instead of after the scan of the
+// whole stream, and the HBM-bound K3p of early chunks runs under the latency-bound K2a of later ones. Measured (r02j,
+// C2): 2.04 ms with 3-4 chunks, 2.12 with 6, 2.67 with 12 against 1.96 ms unchunked — every chunk costs a host round trip
+// for its candidate count (~0.1 ms with the launches behind it), which only the PCIe-bound host form hides. So the
+// device form is opt-in (ZFLACB200_DEVICE_CHUNKS=n) until the count stays on the device.
 int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *opt, void *dst, size_t dst_capacity,
-                     zflacb200_info *info) {
+                     zflacb200_info *info, zflacb200_stream **handle_out = nullptr) {
     const uint32_t flags = (opt ? opt->flags : 0) | env_flags();
-    if (flags & (ZFLACB200_INPUT_ON_DEVICE | ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL | ZFLACB200_NO_PIPELINE)) return kNotPipelined;
+    if (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL | ZFLACB200_NO_PIPELINE)) return kNotPipelined;
+    const bool on_device = (flags & ZFLACB200_INPUT_ON_DEVICE) != 0;
+    if (on_device != (handle_out != nullptr)) return kNotPipelined;
     // test knobs: ZFLACB200_PIPELINE_MIN_BYTES (default 48 MiB), ZFLACB200_PIPELINE_CHUNK (default: len / 24, >= 8 MiB)
     static const uint64_t min_bytes = [] { const char *e = getenv("ZFLACB200_PIPELINE_MIN_BYTES"); return e ? strtoull(e, nullptr, 0) : (48ull << 20); }();
     static const uint64_t env_chunk = [] { const char *e = getenv("ZFLACB200_PIPELINE_CHUNK"); return e ? strtoull(e, nullptr, 0) : 0ull; }();
-    if (!data || !dst || !info || len < min_bytes || len < 4096) return kNotPipelined;  // short streams: nothing to overlap
+    static const uint64_t dev_chunks = [] { const char *e = getenv("ZFLACB200_DEVICE_CHUNKS"); return e ? strtoull(e, nullptr, 0) : 0ull; }();  // off by default, see below
+    if (!data || (!dst && !on_device) || !info || len < min_bytes || len < 4096) return kNotPipelined;  // short streams: nothing to overlap
+    if (on_device && dev_chunks < 2) return kNotPipelined;
     int device = -1;
     if (ensure_device(opt ? opt->device : -1, &device) != ZFLACB200_OK) return kNotPipelined;
     DeviceCtx &ctx = g_ctx[device];
@@ -1364,7 +1375,8 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     HostTrace tr("decode_pipelined");
 
     ByteSource src;
-    src.host = data;
+    if (on_device) src.dev = data;
+    else src.host = data;
     src.len = len;
     Streaminfo si;
     uint64_t audio_offset = 0;
@@ -1377,7 +1389,7 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
     if (si.total == 0 || si.total * C >= (1ull << 40)) return kNotPipelined;
     const uint64_t n_elems = si.total * C, pcm_bytes = n_elems * cb;
-    if (dst_capacity < pcm_bytes) return kNotPipelined;
+    if (!on_device && dst_capacity < pcm_bytes) return kNotPipelined;
     bool wide = false;
     {
         Hdr h0;
@@ -1387,7 +1399,7 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0;
 
     // ---- chunks: >= 8 MiB (a frame is < 2.1 MB: one that starts in chunk i ends inside chunk i + 1), about 24 of them
-    uint64_t chunk = std::max<uint64_t>(8ull << 20, (len / 24 + 0xFFFF) & ~0xFFFFull);
+    uint64_t chunk = std::max<uint64_t>(8ull << 20, (len / (on_device ? dev_chunks : 24) + 0xFFFF) & ~0xFFFFull);
     if (env_chunk >= 4096) chunk = (env_chunk + 15) & ~15ull;  // a frame longer than a chunk only costs the fallback
     if (audio_offset >= chunk) return kNotPipelined;
     const uint32_t K = (uint32_t)((len + chunk - 1) / chunk);
@@ -1405,7 +1417,7 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     const uint64_t scratch_elems = (uint64_t)C * (((si.total + 7) & ~7ull) + 8) + 64ull * cap + 64;
     DevBuf b_stream, b_cands, b_total, b_tiles, b_ticket, b_sd, b_recs, b_outs, b_ok, b_scratch, b_pcm, b_sum, b_flag, b_hi, b_jobs, b_digest;
     SubframeStage stage;
-    if (b_stream.alloc(((len + 15) & ~15ull) + 64, st) || b_cands.alloc(sizeof(Cand) * (size_t)cap, st) ||
+    if ((!on_device && b_stream.alloc(((len + 15) & ~15ull) + 64, st)) || b_cands.alloc(sizeof(Cand) * (size_t)cap, st) ||
         b_total.alloc(sizeof(uint32_t), st) || b_tiles.alloc(sizeof(unsigned long long) * chunk_tiles, st) ||
         b_ticket.alloc(sizeof(uint32_t), st) || b_sd.alloc(sizeof(StreamDesc), st) || b_recs.alloc(sizeof(FrameRec) * (size_t)cap, st) ||
         b_outs.alloc(sizeof(FrameOut) * (size_t)cap, st) || b_ok.alloc(cap, st) || b_scratch.alloc(scratch_elems * (wide ? 8 : 4), st) ||
@@ -1422,9 +1434,9 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     sd.si_sample_rate = si.sample_rate;
     sd.si_channels = (uint8_t)C;
     sd.si_depth = (uint8_t)depth;
-    EventList ev_in, ev_hint, ev_done;
+    EventList ev_in, ev_hint, ev_mid, ev_done;
     Events ev;
-    if (ev_in.make(K) || ev_hint.make(K) || ev_done.make(K) || ev.init()) return ZFLACB200_CUDA_ERROR;
+    if (ev_in.make(K) || ev_hint.make(K) || ev_mid.make(K) || ev_done.make(K) || ev.init()) return ZFLACB200_CUDA_ERROR;
     CU_CHECK(put_small(ctx, b_sd.p, &sd, sizeof(sd), st));
     CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary), st));
     CU_CHECK(cudaMemsetAsync(b_ok.p, 2, cap, st));
@@ -1435,14 +1447,14 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     CU_CHECK(cudaStreamWaitEvent(ctx.copy_in, ctx.ev_fork, 0));
     CU_CHECK(cudaStreamWaitEvent(ctx.copy_out, ctx.ev_fork, 0));
     for (auto &l : ctx.lane) CU_CHECK(cudaStreamWaitEvent(l, ctx.ev_fork, 0));
-    for (uint32_t i = 0; i < K; ++i) {  // the whole upload is queued at once: the wire never waits for the host
+    for (uint32_t i = 0; i < K && !on_device; ++i) {  // the whole upload is queued at once: the wire never waits for the host
         const uint64_t lo = i == 0 ? 0 : b[i];
         CU_CHECK(cudaMemcpyAsync((uint8_t *)b_stream.p + lo, data + lo, b[i + 1] - lo, cudaMemcpyHostToDevice, ctx.copy_in));
         CU_CHECK(cudaEventRecord(ev_in.v[i], ctx.copy_in));
     }
     tr.mark("setup");
 
-    const uint8_t *d_stream = (const uint8_t *)b_stream.p;
+    const uint8_t *d_stream = on_device ? data : (const uint8_t *)b_stream.p;
     Cand *d_cands = (Cand *)b_cands.p;
     FrameRec *d_recs = (FrameRec *)b_recs.p;
     FrameOut *d_outs = (FrameOut *)b_outs.p;
@@ -1454,6 +1466,7 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     bool bail = false;
     // PCM [copied, upto) leaves once chunk_i is decoded (it holds frames of chunk_i only: earlier chunks end below `copied`)
     auto copy_out = [&](uint32_t chunk_i, uint64_t upto) -> int {
+        if (on_device) return ZFLACB200_OK;  // the PCM stays in HBM
         if (upto > n_elems) upto = n_elems;
         if (upto <= copied) return ZFLACB200_OK;
         CU_CHECK(cudaStreamWaitEvent(ctx.copy_out, ev_done.v[chunk_i], 0));
@@ -1467,7 +1480,7 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
         // scan + hinted records on `st` (short, the host waits for the count); the frame-serial kernels of the
         // chunk on one of S lanes: they are latency-bound (one lane per frame), so several chunks run side by side
         cudaStream_t cs = ctx.lane[i % S];
-        CU_CHECK(cudaStreamWaitEvent(st, ev_in.v[std::min(i + 1, K - 1)], 0));
+        if (!on_device) CU_CHECK(cudaStreamWaitEvent(st, ev_in.v[std::min(i + 1, K - 1)], 0));
         const uint64_t readable = i + 2 >= K ? len : b[i + 2];
         CU_CHECK(launch_sync_scan_range(d_stream, b[i], b[i + 1], readable, d_cands + n, cap - n, (uint32_t *)b_total.p,
                                         (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
@@ -1485,8 +1498,10 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
         CU_CHECK(launch_copy_small(&ctx.mailbox[2 + i], d_hi + i, sizeof(unsigned long long), st));
         CU_CHECK(cudaEventRecord(ev_hint.v[i], st));
         CU_CHECK(cudaStreamWaitEvent(cs, ev_hint.v[i], 0));
+        if (i == 0) CU_CHECK(cudaEventRecord(ev.e[4], cs));  // the first K2a starts
         if (m) {
             if (stage.decode(d_stream, d_recs + n, m, b_scratch.p, wide, d_outs + n, true, cs, n) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+            CU_CHECK(cudaEventRecord(ev_mid.v[i], cs));
             EpilogueParams ep;
             ep.frames = d_recs + n;
             ep.n_frames = m;
@@ -1506,7 +1521,12 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
         if (i > 0 && copy_out(i - 1, ctx.mailbox[2 + i - 1]) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
     }
     tr.mark("chunks");
+    CU_CHECK(cudaEventRecord(ev.e[3], st));  // every scan and hint pass is done
+    // (an event that was never recorded counts as complete: chunks without candidates)
+    for (uint32_t i = launched > (uint32_t)S ? launched - S : 0; i < launched; ++i) CU_CHECK(cudaStreamWaitEvent(st, ev_mid.v[i], 0));
+    CU_CHECK(cudaEventRecord(ev.e[5], st));  // every K2a is done
     for (uint32_t i = launched > (uint32_t)S ? launched - S : 0; i < launched; ++i) CU_CHECK(cudaStreamWaitEvent(st, ev_done.v[i], 0));
+    CU_CHECK(cudaEventRecord(ev.e[6], st));  // every K3p is done
     uint32_t lossy = 0;
     StreamSummary sum;
     memset(&sum, 0, sizeof(sum));
@@ -1551,6 +1571,11 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     tr.mark("tail");
     if (!accepted) return kNotPipelined;
     info->ms_total = ev_ms(ev.e[0], ev.e[7]);
+    if (launched) {  // the chunks overlap: these are SPANS (first start to last end), they do not add up to ms_total
+        info->ms_scan = ev_ms(ev.e[0], ev.e[3]);      // K1 + K1h of all chunks, host round trips included
+        info->ms_decode = ev_ms(ev.e[4], ev.e[5]);    // first K2a start .. last K2a end (K3p of early chunks runs inside)
+        info->ms_epilogue = ev_ms(ev.e[5], ev.e[6]);  // what is left of K3p after the last K2a
+    }
     if (result != ZFLACB200_OK) return result;
     info->channels = sum.channels;
     info->bits_per_sample = sum.bps;
@@ -1562,6 +1587,19 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     info->fast_path = 1;
     info->n_crc16_mismatch = sum.n_crc16_mismatch;
     info->audio_bytes = sum.end_offset - audio_offset;
+    if (handle_out) {  // the PCM and the frame table stay on the device behind a handle, as zflacb200_open() leaves them
+        zflacb200_stream *h = new zflacb200_stream();
+        h->device = device;
+        h->pcm_bytes = info->pcm_bytes;
+        h->d_pcm = b_pcm.release();
+        h->d_recs = (FrameRec *)b_recs.release();
+        h->d_outs = (FrameOut *)b_outs.release();
+        h->d_frame_ok = (uint8_t *)b_ok.release();
+        h->n_recs = n;
+        h->frames_on_device = true;
+        h->info = *info;
+        *handle_out = h;
+    }
     return ZFLACB200_OK;
 }
 
@@ -1843,6 +1881,12 @@ int zflacb200_open(const uint8_t *data, size_t len, const zflacb200_options *opt
     std::lock_guard<std::mutex> lock(g_mutex);
     g_last_error.clear();
     pin_rewind_all();
+    if (out && info && (((opt ? opt->flags : 0) | env_flags()) & ZFLACB200_INPUT_ON_DEVICE)) {  // long device-resident stream: chunked
+        *out = nullptr;
+        const int p = decode_pipelined(data, len, opt, nullptr, 0, info, out);
+        if (p != kNotPipelined) return p;
+        if (*out) { zflacb200_stream *h = *out; *out = nullptr; dev_free(h->d_pcm, nullptr); delete h; }
+    }
     return open_impl(data, len, opt, out, info);
 }
 
