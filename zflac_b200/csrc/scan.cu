@@ -98,12 +98,17 @@ __device__ __noinline__ bool parse_header_at(const uint8_t *__restrict__ s, uint
 }
 
 // ------------------------------------------------------------------ K1
-// One CTA scans one 16 KB tile: 4 rows of 256 threads x 16 bytes, every global load a
-// coalesced 128-bit vector. Sync codes are found four bytes at a time with SIMD-in-register
-// byte compares; only the (rare) hits run the full header check.
+// One CTA scans one 64 KB tile as 4 groups of 4 rows of 256 threads x 16 bytes, every global load a
+// coalesced 128-bit vector, four of them in flight per thread. Sync codes are found four bytes at a
+// time with plain integer arithmetic; only the (rare) hits run the full header check. Candidates
+// leave in stream order: per group a warp scan of the four packed row counts, ONE block barrier for
+// the whole tile, one decoupled look-back across tiles. (With 16 KB tiles the two barriers and the
+// look-back per tile were the kernel: barrier stalls 10 per issued instruction, r02g.)
 constexpr int kScanThreads = 256;
-constexpr int kScanRows = 4;
-constexpr int kScanTileBytes = kScanThreads * 16 * kScanRows;
+constexpr int kScanRows = 4;     // rows per group
+constexpr int kScanGroups = 4;   // groups per tile
+constexpr int kScanGroupBytes = kScanThreads * 16 * kScanRows;
+constexpr int kScanTileBytes = kScanGroupBytes * kScanGroups;
 
 constexpr unsigned long long kFlagAgg = 1ull << 62;
 constexpr unsigned long long kFlagPrefix = 2ull << 62;
@@ -120,12 +125,12 @@ __device__ __forceinline__ uint32_t hits_to_mask4(uint32_t z) {  // 4-bit mask, 
     return (((z >> 7) & 0x01010101u) * 0x01020408u) >> 24;
 }
 
-__global__ void __launch_bounds__(kScanThreads, 6)
+__global__ void __launch_bounds__(kScanThreads, 4)
 k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_end, uint64_t len, uint64_t tile0, uint32_t n_tiles,
             Cand *__restrict__ out, uint32_t cap, uint32_t *__restrict__ total_out,
             unsigned long long *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
     __shared__ uint32_t s_tile;
-    __shared__ unsigned long long s_warp_sum[kScanThreads / 32];  // 4 x 16-bit row counts per warp
+    __shared__ unsigned long long s_warp_sum[kScanGroups][kScanThreads / 32];  // 4 x 16-bit row counts per warp and group
     __shared__ unsigned long long s_base;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // tiles start in order: look-back below cannot deadlock
@@ -134,70 +139,72 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     if (tile >= n_tiles) return;
     const uint64_t tile_base = tile0 + (uint64_t)tile * kScanTileBytes;
 
-    // ---- all loads of the tile first (4 independent 128-bit loads in flight per thread)
-    uint4 v[kScanRows];
+    uint32_t valid[kScanGroups][kScanRows / 2];   // per row a 16-bit mask of validated candidates in my 16 bytes, two rows per word
+    unsigned long long incl[kScanGroups];         // inclusive warp scan of the packed row counts (16 bits per row)
+    unsigned long long mine[kScanGroups];
 #pragma unroll
-    for (int r = 0; r < kScanRows; ++r) {
-        const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-        v[r] = make_uint4(0, 0, 0, 0);
-        if (pos + 16 <= len) {
-            v[r] = __ldg(reinterpret_cast<const uint4 *>(s + pos));
-        } else if (pos < len) {  // stream tail: bytes past len read as zero
-            uint32_t t[4] = {0, 0, 0, 0};
-            for (int i = 0; i < 16 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
-            v[r] = make_uint4(t[0], t[1], t[2], t[3]);
+    for (int g = 0; g < kScanGroups; ++g) {
+        const uint64_t group_base = tile_base + (uint64_t)g * kScanGroupBytes;
+        // ---- all loads of the group first (4 independent 128-bit loads in flight per thread)
+        uint4 v[kScanRows];
+#pragma unroll
+        for (int r = 0; r < kScanRows; ++r) {
+            const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+            v[r] = make_uint4(0, 0, 0, 0);
+            if (pos + 16 <= len) {
+                v[r] = __ldg(reinterpret_cast<const uint4 *>(s + pos));
+            } else if (pos < len) {  // stream tail: bytes past len read as zero
+                uint32_t t[4] = {0, 0, 0, 0};
+                for (int i = 0; i < 16 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+                v[r] = make_uint4(t[0], t[1], t[2], t[3]);
+            }
         }
-    }
-
-    uint32_t valid[kScanRows];       // per row: 16-bit mask of validated candidates in my 16 bytes
-    unsigned long long counts = 0;   // 16 bits per row
+        unsigned long long counts = 0;   // 16 bits per row
+        valid[g][0] = valid[g][1] = 0;
 #pragma unroll
-    for (int r = 0; r < kScanRows; ++r) {
-        const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-        // the byte after my 16: the next lane's first byte; lane 31 fetches it (L1/L2 hit: a neighbour loads that line)
-        uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1) & 0xFFu;
-        if (lane == 31) nb = (pos + 16 < len) ? s[pos + 16] : 0u;
-        const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
-        const uint32_t z0 = sync_hits4(w0, __funnelshift_r(w0, w1, 8)), z1 = sync_hits4(w1, __funnelshift_r(w1, w2, 8));
-        const uint32_t z2 = sync_hits4(w2, __funnelshift_r(w2, w3, 8)), z3 = sync_hits4(w3, __funnelshift_r(w3, nb, 8));
-        uint32_t raw = 0;
-        if (z0 | z1 | z2 | z3)  // a sync pattern in my 16 bytes: 2^-11; in the warp's 512 bytes: 1.6 %
-            raw = hits_to_mask4(z0) | (hits_to_mask4(z1) << 4) | (hits_to_mask4(z2) << 8) | (hits_to_mask4(z3) << 12);
-        uint32_t ok = 0;
-        while (raw) {  // rare: ~2^-15 per byte on compressed data
-            const int b = __ffs(raw) - 1;
-            raw &= raw - 1;
-            const uint64_t p = pos + b;
-            Cand c;
-            if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) ok |= 1u << b;
+        for (int r = 0; r < kScanRows; ++r) {
+            const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+            // the byte after my 16: the next lane's first byte; lane 31 fetches it (L1/L2 hit: a neighbour loads that line)
+            uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1) & 0xFFu;
+            if (lane == 31) nb = (pos + 16 < len) ? s[pos + 16] : 0u;
+            const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
+            const uint32_t z0 = sync_hits4(w0, __funnelshift_r(w0, w1, 8)), z1 = sync_hits4(w1, __funnelshift_r(w1, w2, 8));
+            const uint32_t z2 = sync_hits4(w2, __funnelshift_r(w2, w3, 8)), z3 = sync_hits4(w3, __funnelshift_r(w3, nb, 8));
+            uint32_t raw = 0;
+            if (z0 | z1 | z2 | z3)  // a sync pattern in my 16 bytes: 2^-11; in the warp's 512 bytes: 1.6 %
+                raw = hits_to_mask4(z0) | (hits_to_mask4(z1) << 4) | (hits_to_mask4(z2) << 8) | (hits_to_mask4(z3) << 12);
+            uint32_t ok = 0;
+            while (raw) {  // rare: ~2^-15 per byte on compressed data
+                const int b = __ffs(raw) - 1;
+                raw &= raw - 1;
+                const uint64_t p = pos + b;
+                Cand c;
+                if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) ok |= 1u << b;
+            }
+            valid[g][r >> 1] |= ok << (16 * (r & 1));
+            counts |= (unsigned long long)__popc(ok) << (16 * r);
         }
-        valid[r] = ok;
-        counts |= (unsigned long long)__popc(ok) << (16 * r);
-    }
-
-    // ---- one block-wide exclusive scan for all four rows at once (row counts <= 4096 fit 16 bits)
-    unsigned long long incl = counts;
+        // ---- warp-level inclusive scan of the four row counts at once (row counts <= 4096 fit 16 bits)
+        unsigned long long in = counts;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if (lane >= d) incl += t;
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, in, d);
+            if (lane >= d) in += t;
+        }
+        if (lane == 31) s_warp_sum[g][warp] = in;
+        incl[g] = in;
+        mine[g] = counts;
     }
-    if (lane == 31) s_warp_sum[warp] = incl;
     __syncthreads();
-    unsigned long long warp_off = 0, all = 0;
+
+    // ---- candidates in the whole tile (what the look-back publishes)
+    uint32_t running = 0;
 #pragma unroll
-    for (int w = 0; w < kScanThreads / 32; ++w) {
-        const unsigned long long t = s_warp_sum[w];
-        if (w < warp) warp_off += t;
-        all += t;
-    }
-    const unsigned long long excl = warp_off + incl - counts;
-    uint32_t rank[kScanRows];
-    uint32_t running = 0;  // candidates in earlier rows of this tile
+    for (int g = 0; g < kScanGroups; ++g) {
+        unsigned long long all = 0;
 #pragma unroll
-    for (int r = 0; r < kScanRows; ++r) {
-        rank[r] = running + (uint32_t)((excl >> (16 * r)) & 0xFFFFu);
-        running += (uint32_t)((all >> (16 * r)) & 0xFFFFu);
+        for (int w = 0; w < kScanThreads / 32; ++w) all += s_warp_sum[g][w];
+        running += (uint32_t)(all & 0xFFFFu) + (uint32_t)((all >> 16) & 0xFFFFu) + (uint32_t)((all >> 32) & 0xFFFFu) + (uint32_t)(all >> 48);
     }
 
     // ---- decoupled look-back by warp 0: tile t publishes its aggregate, then 32 predecessors at a
@@ -233,18 +240,32 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     __syncthreads();
     const unsigned long long base = s_base;
 
+    // ---- ranks inside the tile: groups in order, rows in order inside a group, threads in order inside a row
+    uint32_t before = 0;  // candidates in earlier groups / rows of this tile
 #pragma unroll
-    for (int r = 0; r < kScanRows; ++r) {
-        uint32_t ok = valid[r];
-        unsigned long long slot = base + rank[r];
-        const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-        while (ok) {
-            const int b = __ffs(ok) - 1;
-            ok &= ok - 1;
-            Cand c;
-            parse_header_at(s, pos + b, len, c);
-            if (slot < cap) out[slot] = c;
-            ++slot;
+    for (int g = 0; g < kScanGroups; ++g) {
+        unsigned long long warp_off = 0, all = 0;
+#pragma unroll
+        for (int w = 0; w < kScanThreads / 32; ++w) {
+            const unsigned long long t = s_warp_sum[g][w];
+            if (w < warp) warp_off += t;
+            all += t;
+        }
+        const unsigned long long excl = warp_off + incl[g] - mine[g];
+#pragma unroll
+        for (int r = 0; r < kScanRows; ++r) {
+            uint32_t ok = (valid[g][r >> 1] >> (16 * (r & 1))) & 0xFFFFu;
+            unsigned long long slot = base + before + (uint32_t)((excl >> (16 * r)) & 0xFFFFu);
+            before += (uint32_t)((all >> (16 * r)) & 0xFFFFu);
+            const uint64_t pos = tile_base + (uint64_t)g * kScanGroupBytes + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+            while (ok) {
+                const int b = __ffs(ok) - 1;
+                ok &= ok - 1;
+                Cand c;
+                parse_header_at(s, pos + b, len, c);
+                if (slot < cap) out[slot] = c;
+                ++slot;
+            }
         }
     }
 }
