@@ -10,15 +10,16 @@
 
 namespace zf {
 
-// SRC = StagedSrc (16-word warp-synchronous refills, 64-word ring, 116 registers: 4 CTAs per SM) or QuadSrc (4-word
-// refills, 32-word ring, 72 registers: 7 CTAs per SM). The kernel is latency-bound, so what counts is that ALL frames of
-// a launch are resident at once: the launcher picks QuadSrc when the frames do not fit one wave of the first.
+// SRC = StagedSrc (16-word warp-synchronous refills, 64-word ring, 116 registers: 512 lanes per SM, one-warp CTAs) or
+// QuadSrc (4-word refills, 32-word ring, 72 registers: 896 lanes per SM, 128-thread CTAs). The kernel is latency-bound,
+// so what counts is that ALL frames of a launch are resident at once and evenly spread: the launcher picks QuadSrc when
+// the frames do not fit one wave of the first.
 template <class SRC>
-__global__ void __launch_bounds__(kDecodeThreads, SRC::kMinBlocks)
+__global__ void __launch_bounds__(SRC::kThreads, SRC::kMinBlocks)
 k_parse_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frames, uint32_t n_frames,
                int32_t *__restrict__ scratch, SubRec *__restrict__ subs, FrameOut *__restrict__ outs,
                uint32_t *__restrict__ big_orders, int write_samples) {
-    const uint32_t f = blockIdx.x * kDecodeThreads + threadIdx.x;
+    const uint32_t f = blockIdx.x * SRC::kThreads + threadIdx.x;
     if (f >= n_frames) return;
     const FrameRec fr = frames[f];
     if (fr.block_size == 0) return;  // dropped candidate slot
@@ -50,12 +51,19 @@ cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frame
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (sms <= 0) sms = 148;
     }
-    if (blocks <= (uint32_t)sms * 4u)
-        k_parse_frames<StagedSrc<kDecodeThreads>><<<blocks, kDecodeThreads, kStagedRing * kDecodeThreads * sizeof(uint32_t), st>>>(
+    // One-warp CTAs for the StagedSrc kernel: with 128-thread CTAs a 1-hour stream is 303 CTAs on 148 SMs, seven SMs
+    // carry three CTAs (3 warps per scheduler instead of 2) and the whole launch waits 26 % longer for them
+    // (sm__cycles_active max 1.77 M vs avg 1.40 M, r02m); 1 212 one-warp CTAs spread the 28 extra warps over 28 SMs.
+    constexpr int kStagedThreads = 32;
+    if (blocks <= (uint32_t)sms * 4u) {
+        const uint32_t warps = (n_frames + kStagedThreads - 1) / kStagedThreads;
+        k_parse_frames<StagedSrc<kStagedThreads>><<<warps, kStagedThreads, kStagedRing * kStagedThreads * sizeof(uint32_t), st>>>(
             d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_big_orders, write_samples ? 1 : 0);
-    else
+    } else {
+        // (one-warp CTAs were slower here, r02p: C5 3.83 -> 4.30 ms; 860 CTAs of 128 already spread to within one CTA per SM)
         k_parse_frames<QuadSrc<kDecodeThreads>><<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(
             d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_big_orders, write_samples ? 1 : 0);
+    }
     return cudaGetLastError();
 }
 

@@ -128,7 +128,8 @@ constexpr uint32_t kStagedRing = 64;
 
 template <int NT>
 struct StagedSrc {
-    static constexpr int kMinBlocks = 4;  // CTAs per SM the kernel is compiled for
+    static constexpr int kThreads = NT;
+    static constexpr int kMinBlocks = 512 / NT;  // CTAs per SM the kernel is compiled for (512 lanes per SM: <= 128 registers)
     const uint8_t *g;    // global address of word 0 (16-byte aligned)
     uint32_t avail;      // bytes readable from g (stream end), clamped
     uint32_t col;        // shared-space byte address of zf_ring[lane column]
@@ -211,7 +212,8 @@ struct StagedSrc {
 // ---------------------------------------------------------------------------------------------
 template <int NT>
 struct QuadSrc {
-    static constexpr int kMinBlocks = 7;  // CTAs per SM the kernel is compiled for
+    static constexpr int kThreads = NT;
+    static constexpr int kMinBlocks = 896 / NT;  // CTAs per SM the kernel is compiled for (896 lanes per SM: <= 72 registers)
     const uint8_t *g;    // global address of word 0 (16-byte aligned)
     uint32_t avail;      // bytes readable from g (stream end), clamped
     uint32_t col;        // shared-space byte address of zf_ring[lane column]
