@@ -79,3 +79,44 @@ def test_pipelined_decode_matches_oracle():
     env = dict(os.environ, ZFLACB200_PIPELINE_MIN_BYTES="0", ZFLACB200_PIPELINE_CHUNK=str(256 << 10), ZFLACB200_DEVICE_CHUNKS="6")
     r = subprocess.run([sys.executable, "-c", SCRIPT % {"root": ROOT}], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "PIPELINE-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+ALLOC_SCRIPT = r'''
+import sys
+import numpy as np
+sys.path.insert(0, %(root)r)
+sys.path.insert(0, %(root)r + "/tests")
+import zflac_b200 as z
+from oracle import oracle
+from tools import flacgen as fg
+import synth_cases
+
+streams = [fg.generate(fg.c2(4.0 + i), want_pcm=False).flac for i in range(4)]
+streams += [synth_cases.make(n).flac for n in ("c3_8ch24_lpc32_po7", "c4_32bit_rice2_escapes", "unknown_total", "ch6_mixed")]
+refs = [oracle.decode(s) for s in streams]
+for rep in range(3):                      # sizes change from call to call: blocks are reused, split off the driver, trimmed
+    for s, ref in zip(streams, refs):
+        got = z.decode(s)
+        assert np.array_equal(got.samples, ref.samples)
+    res = z.decode_batch(streams)
+    assert all(np.array_equal(r.samples, ref.samples) for r, ref in zip(res, refs))
+    blob, offs, lens = z.pack_streams(streams)
+    dst = np.zeros(z.batch_pcm_bound(blob, offs, lens) + (8 << 20), dtype=np.uint8)
+    out = z.decode_batch_into(blob, offs, lens, dst)
+    assert all(np.array_equal(out.samples(i), ref.samples) for i, ref in enumerate(refs))
+    parts = [z.decode_range(streams[0], lo, hi) for lo, hi in ((0, len(streams[0]) // 2), (len(streams[0]) // 2, len(streams[0])))]
+    assert z.stitch_ranges(parts, parts[0].info["audio_offset"])
+    assert np.array_equal(np.concatenate([p.samples for p in parts]), refs[0].samples)
+z._native.load().zflacb200_shutdown()     # returns every cached block; the next call starts from nothing
+assert np.array_equal(z.decode(streams[1]).samples, refs[1].samples)
+print("ALLOC-OK")
+'''
+
+
+@pytest.mark.parametrize("env", [{"ZFLACB200_CACHE_MAX_MIB": "4"}, {"ZFLACB200_ALLOC": "pool"}, {}], ids=["tiny_cache", "driver_pool", "default"])
+def test_device_memory_paths(env):
+    """The library's block cache under pressure (a 4 MiB idle limit trims after almost every free), the driver's
+    stream-ordered pool (A/B switch) and the default: same results through every entry point, shutdown included."""
+    r = subprocess.run([sys.executable, "-c", ALLOC_SCRIPT % {"root": ROOT}], env=dict(os.environ, **env), capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0 and "ALLOC-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
