@@ -1967,7 +1967,7 @@ int zflacb200_stitch(const zflacb200_range *r, size_t n, uint64_t audio_offset) 
     uint64_t next_offset = audio_offset, next_sample = 0;
     bool any = false;
     for (size_t i = 0; i < n; ++i) {
-        if (!r[i].accepted) return 0;
+        if (!r[i].accepted || r[i].total_samples != r[0].total_samples) return 0;
         if (r[i].n_frames == 0) continue;
         if (r[i].first_frame_offset != next_offset || r[i].first_sample != next_sample) return 0;
         next_offset = r[i].end_offset;

@@ -15,6 +15,7 @@
 
 #include <cstdint>
 #include <cstdlib>
+#include <iterator>
 #include <map>
 #include <mutex>
 #include <unordered_map>
@@ -33,7 +34,8 @@ class DevCache {
         std::lock_guard<std::mutex> lock(m_);
         PerDevice &d = dev_[dev];
         auto it = d.idle.lower_bound(want);
-        if (it != d.idle.end() && it->first <= want + want / 4 + (1u << 20)) {  // at most 25 % + 1 MiB of slack
+        // at most 25 % of slack, plus 1 MiB for large requests (their sizes wobble from call to call) or 4 KiB for small ones
+        if (it != d.idle.end() && it->first <= want + want / 4 + (want >= (1u << 20) ? (1u << 20) : 4096u)) {
             Block b = it->second;
             d.idle.erase(it);
             d.idle_bytes -= b.bytes;

@@ -138,6 +138,7 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     const uint32_t tile = s_tile;
     if (tile >= n_tiles) return;
     const uint64_t tile_base = tile0 + (uint64_t)tile * kScanTileBytes;
+    const bool interior = tile_base + kScanTileBytes + 16 <= len;
 
     uint32_t valid[kScanGroups][kScanRows / 2];   // per row a 16-bit mask of validated candidates in my 16 bytes, two rows per word
     unsigned long long incl[kScanGroups];         // inclusive warp scan of the packed row counts (16 bits per row)
@@ -147,16 +148,22 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
         const uint64_t group_base = tile_base + (uint64_t)g * kScanGroupBytes;
         // ---- all loads of the group first (4 independent 128-bit loads in flight per thread)
         uint4 v[kScanRows];
+        if (interior) {  // the whole tile and the byte after it are inside the stream: no per-row length checks
+            const uint4 *src = reinterpret_cast<const uint4 *>(s + group_base) + tid;
 #pragma unroll
-        for (int r = 0; r < kScanRows; ++r) {
-            const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-            v[r] = make_uint4(0, 0, 0, 0);
-            if (pos + 16 <= len) {
-                v[r] = __ldg(reinterpret_cast<const uint4 *>(s + pos));
-            } else if (pos < len) {  // stream tail: bytes past len read as zero
-                uint32_t t[4] = {0, 0, 0, 0};
-                for (int i = 0; i < 16 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
-                v[r] = make_uint4(t[0], t[1], t[2], t[3]);
+            for (int r = 0; r < kScanRows; ++r) v[r] = __ldg(src + r * kScanThreads);
+        } else {
+#pragma unroll
+            for (int r = 0; r < kScanRows; ++r) {
+                const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+                v[r] = make_uint4(0, 0, 0, 0);
+                if (pos + 16 <= len) {
+                    v[r] = __ldg(reinterpret_cast<const uint4 *>(s + pos));
+                } else if (pos < len) {  // stream tail: bytes past len read as zero
+                    uint32_t t[4] = {0, 0, 0, 0};
+                    for (int i = 0; i < 16 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+                    v[r] = make_uint4(t[0], t[1], t[2], t[3]);
+                }
             }
         }
         unsigned long long counts = 0;   // 16 bits per row
@@ -166,7 +173,7 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
             const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
             // the byte after my 16: the next lane's first byte; lane 31 fetches it (L1/L2 hit: a neighbour loads that line)
             uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1) & 0xFFu;
-            if (lane == 31) nb = (pos + 16 < len) ? s[pos + 16] : 0u;
+            if (lane == 31) nb = (interior || pos + 16 < len) ? s[pos + 16] : 0u;
             const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
             const uint32_t z0 = sync_hits4(w0, __funnelshift_r(w0, w1, 8)), z1 = sync_hits4(w1, __funnelshift_r(w1, w2, 8));
             const uint32_t z2 = sync_hits4(w2, __funnelshift_r(w2, w3, 8)), z3 = sync_hits4(w3, __funnelshift_r(w3, nb, 8));
