@@ -132,6 +132,7 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     __shared__ uint32_t s_tile;
     __shared__ unsigned long long s_warp_sum[kScanGroups][kScanThreads / 32];  // 4 x 16-bit row counts per warp and group
     __shared__ unsigned long long s_base;
+    __shared__ Cand s_first[kScanThreads];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // tiles start in order: look-back below cannot deadlock
     __syncthreads();
@@ -140,6 +141,7 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     const uint64_t tile_base = tile0 + (uint64_t)tile * kScanTileBytes;
     const bool interior = tile_base + kScanTileBytes + 16 <= len;
 
+    uint64_t first_off = ~0ull;  // stream offset of the candidate kept in s_first[tid]
     uint32_t valid[kScanGroups][kScanRows / 2];   // per row a 16-bit mask of validated candidates in my 16 bytes, two rows per word
     unsigned long long incl[kScanGroups];         // inclusive warp scan of the packed row counts (16 bits per row)
     unsigned long long mine[kScanGroups];
@@ -186,7 +188,13 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
                 raw &= raw - 1;
                 const uint64_t p = pos + b;
                 Cand c;
-                if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) ok |= 1u << b;
+                if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) {
+                    ok |= 1u << b;
+                    if (first_off == ~0ull) {  // almost every thread that has a candidate has exactly one: keep it for the output pass
+                        first_off = p;
+                        s_first[tid] = c;
+                    }
+                }
             }
             valid[g][r >> 1] |= ok << (16 * (r & 1));
             counts |= (unsigned long long)__popc(ok) << (16 * r);
@@ -269,7 +277,8 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
                 const int b = __ffs(ok) - 1;
                 ok &= ok - 1;
                 Cand c;
-                parse_header_at(s, pos + b, len, c);
+                if (first_off == pos + b) c = s_first[tid];
+                else parse_header_at(s, pos + b, len, c);
                 if (slot < cap) out[slot] = c;
                 ++slot;
             }
