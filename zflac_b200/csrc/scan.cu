@@ -174,8 +174,13 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
         for (int r = 0; r < kScanRows; ++r) {
             const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
             // the byte after my 16: the next lane's first byte; lane 31 fetches it (L1/L2 hit: a neighbour loads that line)
-            uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1) & 0xFFu;
-            if (lane == 31) nb = (interior || pos + 16 < len) ? s[pos + 16] : 0u;
+            uint32_t nb;
+            if (interior) {  // every lane reads it (an L1 hit: the neighbour loaded that line): no shuffle, no one-lane branch
+                nb = __ldg(s + pos + 16);
+            } else {
+                nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1) & 0xFFu;
+                if (lane == 31) nb = (pos + 16 < len) ? s[pos + 16] : 0u;
+            }
             const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
             const uint32_t z0 = sync_hits4(w0, __funnelshift_r(w0, w1, 8)), z1 = sync_hits4(w1, __funnelshift_r(w1, w2, 8));
             const uint32_t z2 = sync_hits4(w2, __funnelshift_r(w2, w3, 8)), z3 = sync_hits4(w3, __funnelshift_r(w3, nb, 8));
