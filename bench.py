@@ -192,6 +192,7 @@ def run_reference(args, rank, world):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32/int64", "data": "synthetic",
         "config": {"workload": name, "sample": sample,
+                   "frame_crc16": "the library's per-frame CRC-16 diagnostic is off in value and e2e (the reference and the CPU arm ignore the field); value_with_frame_crc16 has it on",
                    "md5": "value excludes the MD5 pass on BOTH arms (one serial chain per stream); value_with_md5 includes it, as the reference's decode() does"},
         "value_with_md5": round(value_with, 3), "ms_per_step_with_md5": round(ms_with, 3),
         "compressed_gbs": round(copies * s.flac.size / (ms * 1e-3) / 1e9, 4),
@@ -265,14 +266,17 @@ def main():
         if world > 1:
             dist.barrier()
 
-    def step_device(verify_md5):
-        s = z.open_device(d_flac.data_ptr(), flac_bytes, device=local_rank, stream=sptr, verify_md5=verify_md5)
+    # The per-frame CRC-16 is a diagnostic of this library (info.n_crc16_mismatch): the reference reads the field and
+    # ignores it (src/zflac.zig:551) and so does the CPU arm, so the timed steps of both arms leave it out; the same
+    # step with the diagnostic on is reported next to it (value_with_frame_crc16).
+    def step_device(verify_md5, frame_crc16=False):
+        s = z.open_device(d_flac.data_ptr(), flac_bytes, device=local_rank, stream=sptr, verify_md5=verify_md5, frame_crc16=frame_crc16)
         info = s.info
         s.close()
         return info
 
     def step_e2e(verify_md5):
-        return z.decode_into(h_flac.numpy(), h_pcm.numpy(), device=local_rank, verify_md5=verify_md5, stream=sptr)
+        return z.decode_into(h_flac.numpy(), h_pcm.numpy(), device=local_rank, verify_md5=verify_md5, stream=sptr, frame_crc16=False)
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -316,6 +320,8 @@ def main():
     del exp, got
     if not parity_ok:
         raise SystemExit("PARITY FAILURE: device PCM / MD5 differs from the generator's")
+
+    ms_dev_crc, _, _, _ = timed(lambda: step_device(False, True), max(3, args.steps // 2), 1)
 
     # MD5-gated variant (K1->K4): a single stream's MD5 is one serial chain
     ms_dev_md5 = None
@@ -374,9 +380,11 @@ def main():
         "config": {"workload": wl_name, "samples_per_step_per_gpu": n_samples, "frames": int(info0["n_frames"]),
                    "compressed_bytes": flac_bytes, "pcm_bytes": pcm_bytes, "sharding": "one stream per GPU, no collective",
                    "l2": "inputs larger than L2 (no flush needed)" if flac_bytes > 126 * 2**20 else "input smaller than L2",
+                   "frame_crc16": "the library's per-frame CRC-16 diagnostic is off in value and e2e (the reference and the CPU arm ignore the field); value_with_frame_crc16 has it on",
                    "md5": "value excludes the MD5 pass on BOTH arms (one serial chain per stream); value_with_md5 includes it, as the reference's decode() does",
                    "generator_s": round(t_gen, 2)},
         "compressed_gbs": round(world * flac_bytes / (ms_dev * 1e-3) / 1e9, 3),
+        "value_with_frame_crc16": round(world * n_samples / (ms_dev_crc * 1e-3) / 1e6, 2), "ms_per_step_with_frame_crc16": round(ms_dev_crc, 4),
         "value_with_md5": round(world * n_samples / (ms_dev_md5 * 1e-3) / 1e6, 2) if ms_dev_md5 else None,
         "ms_per_step_with_md5": round(ms_dev_md5, 3) if ms_dev_md5 else None,
         "kernel_ms": {**{f: round(v, 4) for f, v in k.items()}, "ms_md5_when_on": round(ms_md5_kernel, 3)},

@@ -67,6 +67,8 @@ typedef enum zflacb200_status {
 #define ZFLACB200_INPUT_ON_DEVICE 0x4u /* `data` is a device pointer (bench: inputs resident in HBM) */
 #define ZFLACB200_NO_CRC_ACCEL 0x8u    /* diagnostics: ignore CRC-16 links, probe every frame end (slow path) */
 #define ZFLACB200_NO_FAST_PATH 0x10u   /* diagnostics: skip the device-side hinted chain, walk the chain on the host */
+#define ZFLACB200_SKIP_FRAME_CRC16 0x80u /* additive: do not compute the per-frame CRC-16 diagnostic (the reference reads the field and
+                                          * ignores it, :551): info.n_crc16_mismatch stays 0, zflacb200_frame.crc16_ok says 2 = not checked */
 #define ZFLACB200_NO_PIPELINE 0x40u    /* diagnostics: zflacb200_decode uploads, decodes and reads back one after the other */
 #define ZFLACB200_SINGLE_PASS 0x20u    /* diagnostics: fused single-pass subframe decoder (K2 + K3) instead of parse + predict */
 

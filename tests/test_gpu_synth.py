@@ -50,6 +50,13 @@ def test_crc_damage_is_ignored_like_the_reference(z):
     got = z.decode(bad_crc, use_fast_path=False)
     assert np.array_equal(got.samples, s.pcm)
     assert got.info["n_crc16_mismatch"] == 1 and got.info["n_probed_frames"] >= 1
+    # ZFLACB200_SKIP_FRAME_CRC16: the diagnostic is not computed, nothing else changes
+    h = z.open_device(0, 0, host_data=bad_crc, frame_crc16=False)
+    assert np.array_equal(h.to_host(), s.pcm) and h.info["n_crc16_mismatch"] == 0 and h.info["fast_path"] == 1
+    assert set(h.frames()["crc16_ok"].tolist()) == {2}
+    h.close()
+    dst = np.zeros(s.pcm.size, dtype=s.pcm.dtype)
+    assert z.decode_into(bad_crc, dst, frame_crc16=False)["n_crc16_mismatch"] == 0 and np.array_equal(dst, s.pcm)
     hdr = int(r0.frames["offset"][5]) + int(r0.frames["header_len"][5]) - 1  # CRC-8 byte of frame 5
     bad_crc8 = s.flac.copy()
     bad_crc8[hdr] ^= 0x33

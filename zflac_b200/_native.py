@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "_lib", "libzflacb200.so")
 # zflacb200_options.flags
 VERIFY_MD5 = 0x1
 SKIP_MD5 = 0x2
+SKIP_FRAME_CRC16 = 0x80
 INPUT_ON_DEVICE = 0x4
 NO_CRC_ACCEL = 0x8
 NO_FAST_PATH = 0x10

@@ -688,11 +688,15 @@ int run_fast_group(FastGroup &g, Events &ev) {
     if (stage.decode(g.d_blob, d_recs, n, b_scratch.p, g.wide, d_outs, true, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
     CU_CHECK(cudaEventRecord(ev.e[5], st));
 
-    // side stream: CRC-16 of every decoded frame, overlapping K3 (+K4)
-    CU_CHECK(cudaEventRecord(ctx.ev_fork, st));
-    CU_CHECK(cudaStreamWaitEvent(ctx.side, ctx.ev_fork, 0));
-    CU_CHECK(launch_crc16_frames(g.d_blob, d_recs, d_outs, n, d_sum, (uint8_t *)g.b_ok.p, ctx.side));
-    CU_CHECK(cudaEventRecord(ctx.ev_join, ctx.side));
+    // side stream: CRC-16 of every decoded frame, overlapping K3 (+K4). A diagnostic only — the reference reads the
+    // field and ignores it (:551) — but it re-reads the whole stream while K3p wants the HBM: ZFLACB200_SKIP_FRAME_CRC16
+    const bool frame_crc = (g.flags & ZFLACB200_SKIP_FRAME_CRC16) == 0;
+    if (frame_crc) {
+        CU_CHECK(cudaEventRecord(ctx.ev_fork, st));
+        CU_CHECK(cudaStreamWaitEvent(ctx.side, ctx.ev_fork, 0));
+        CU_CHECK(launch_crc16_frames(g.d_blob, d_recs, d_outs, n, d_sum, (uint8_t *)g.b_ok.p, ctx.side));
+        CU_CHECK(cudaEventRecord(ctx.ev_join, ctx.side));
+    }
 
     CU_CHECK(launch_verify_chain(g.d_cands, n, d_sd, ns, d_recs, d_outs, d_sum, window, st));
     EpilogueParams ep;
@@ -742,7 +746,7 @@ int run_fast_group(FastGroup &g, Events &ev) {
         }
     }
     CU_CHECK(cudaEventRecord(ev.e[7], st));
-    CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));
+    if (frame_crc) CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));
     g.sums.resize(ns);
     GET_SMALL(h_sums, ctx, b_sum.p, sizeof(StreamSummary) * ns, st);
     tr.mark("md5_setup");
@@ -1544,7 +1548,8 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     StreamSummary sum;
     memset(&sum, 0, sizeof(sum));
     if (!bail && n > 0) {
-        CU_CHECK(launch_crc16_frames(d_stream, d_recs, d_outs, n, d_sum, (uint8_t *)b_ok.p, st));
+        if ((flags & ZFLACB200_SKIP_FRAME_CRC16) == 0)
+            CU_CHECK(launch_crc16_frames(d_stream, d_recs, d_outs, n, d_sum, (uint8_t *)b_ok.p, st));
         CU_CHECK(launch_verify_chain(d_cands, n, (const StreamDesc *)b_sd.p, 1, d_recs, d_outs, d_sum, window, st));
         GET_SMALL(h_sum, ctx, b_sum.p, sizeof(sum), st);
         GET_SMALL(h_lossy, ctx, b_flag.p, sizeof(lossy), st);
@@ -1788,7 +1793,8 @@ int decode_range_impl(const uint8_t *data, size_t len, const zflacb200_options *
     CU_CHECK(cudaEventRecord(ev.e[3], st));
     if (stage.decode(d_stream, d_recs, n, b_scratch.p, wide, d_outs, true, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
     CU_CHECK(cudaEventRecord(ev.e[4], st));
-    CU_CHECK(launch_crc16_frames(d_stream, d_recs, d_outs, n, d_sum, (uint8_t *)b_ok.p, st));
+    if ((flags & ZFLACB200_SKIP_FRAME_CRC16) == 0)
+        CU_CHECK(launch_crc16_frames(d_stream, d_recs, d_outs, n, d_sum, (uint8_t *)b_ok.p, st));
     CU_CHECK(launch_verify_chain(d_cands, n, (const StreamDesc *)b_sd.p, 1, d_recs, d_outs, d_sum, window, st, true));
     EpilogueParams ep;
     ep.frames = d_recs;
