@@ -203,6 +203,20 @@ int zflacb200_decode_range(const uint8_t *data, size_t len, const zflacb200_opti
 /* 1 if the n ranges (in stream order) are all accepted and link up into the one chain the reference walks, else 0. */
 int zflacb200_stitch(const zflacb200_range *ranges, size_t n, uint64_t audio_offset);
 
+/* ---- Raw frame streams / "sync to next frame" (additive; the reference's Readme.md:54 TODO) -------------
+ * `data` needs no "fLaC" signature and no metadata (flac-test-files uncommon/10-11, which zflac.decode rejects with
+ * InvalidSignature, tests/std_uncommon.zig:53-59), and `byte_offset` may point anywhere, into the middle of a frame too.
+ * The sync scan runs from byte_offset; decoding starts at the first frame header (grammar of src/zflac.zig:343-374 and a
+ * valid CRC-8) whose CRC-16 reaches another such header or the end of the data, else at the first header found. That
+ * frame's fields stand in for STREAMINFO exactly as the reference latches them from its first frame (:376-388): channel
+ * count, bits per sample (code 0 = "from STREAMINFO" -> MissingStreaminfo) and sample rate (code 0 -> 0). No total is known,
+ * so the frame loop follows the reference's rules for a stream that states none (:341, :394-402): it runs until fewer than 4
+ * bytes remain, and anything after the last frame that is not a frame is an InvalidFrameHeader. There is no MD5 to check
+ * (info.md5_checked = 0). info.audio_offset says where decoding began; no frame found at all = EndOfStream.
+ * Everything else (read, device_pcm, frames, close) is the same handle API as zflacb200_open(). */
+int zflacb200_open_frames(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_offset,
+                          zflacb200_stream **out, zflacb200_info *info);
+
 /* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
 typedef struct zflacb200_frame {
     uint64_t offset;        /* byte offset of the sync code */

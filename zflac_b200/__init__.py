@@ -24,7 +24,7 @@ from . import _native
 from ._native import INPUT_ON_DEVICE, NO_CRC_ACCEL, NO_FAST_PATH, SKIP_FRAME_CRC16, SKIP_MD5, VERIFY_MD5  # noqa: F401
 
 __all__ = ["decode", "decode_into", "decode_batch", "open_batch", "DeviceBatch", "pack_streams", "DecodedFLAC", "ZflacError",
-           "CudaError", "open_device", "DeviceStream"]
+           "CudaError", "open_device", "DeviceStream", "decode_frames"]
 
 
 class ZflacError(Exception):
@@ -75,7 +75,7 @@ class DecodedFLAC:
 
 
 def _info_dict(info: _native.Info) -> dict:
-    d = {k: getattr(info, k) for k, _ in _native.Info._fields_ if not k.startswith("md5_")}
+    d = {k: getattr(info, k) for k, _ in _native.Info._fields_ if k not in ("md5_computed", "md5_streaminfo")}
     d["md5_computed"] = bytes(info.md5_computed)
     d["md5_streaminfo"] = bytes(info.md5_streaminfo)
     return d
@@ -111,6 +111,29 @@ def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bo
         _raise(st)
     try:
         # the caller-side allocation of the reference (allocator.allocWithOptions(u8, n, 32), zflac.zig:331)
+        out = np.empty(int(info.n_samples), dtype=_DTYPES[info.container_bytes])
+        st = lib.zflacb200_read(handle, out.ctypes.data, out.nbytes)
+        if st != 0:
+            _raise(st)
+    finally:
+        lib.zflacb200_close(handle)
+    return DecodedFLAC(info.channels, info.sample_rate, info.bits_per_sample, out, _info_dict(info))
+
+
+def decode_frames(data, byte_offset: int = 0, *, device: int = -1, use_crc_links: bool = True) -> DecodedFLAC:
+    """Additive (not in the reference, whose Readme.md:54 lists "sync to next frame" as a TODO): decode a raw frame
+    stream, or resync inside any stream from `byte_offset` on (zflacb200_open_frames). No signature, no metadata, no MD5
+    gate; the first frame's header supplies channels / bits per sample / sample rate. `info["audio_offset"]` is the byte
+    offset of the frame decoding began at."""
+    lib = _native.load()
+    arr = _as_u8(data)
+    opt = _options(0 if use_crc_links else NO_CRC_ACCEL, device)
+    handle = C.c_void_p()
+    info = _native.Info()
+    st = lib.zflacb200_open_frames(arr.ctypes.data, arr.size, C.byref(opt), int(byte_offset), C.byref(handle), C.byref(info))
+    if st != 0:
+        _raise(st)
+    try:
         out = np.empty(int(info.n_samples), dtype=_DTYPES[info.container_bytes])
         st = lib.zflacb200_read(handle, out.ctypes.data, out.nbytes)
         if st != 0:

@@ -22,7 +22,7 @@ EXPORTS = [
     "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_frames", "zflacb200_batch_open",
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
     "zflacb200_batch_close", "zflacb200_batch_pcm_bound", "zflacb200_batch_decode",
-    "zflacb200_decode_range", "zflacb200_stitch",
+    "zflacb200_decode_range", "zflacb200_stitch", "zflacb200_open_frames",
 ]
 
 
@@ -76,6 +76,9 @@ def load():
     lib.zflacb200_kernel_launches.restype = C.c_uint64
     lib.zflacb200_open.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.POINTER(C.c_void_p), C.POINTER(Info)]
     lib.zflacb200_open.restype = C.c_int
+    lib.zflacb200_open_frames.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.c_uint64, C.POINTER(C.c_void_p),
+                                          C.POINTER(Info)]
+    lib.zflacb200_open_frames.restype = C.c_int
     lib.zflacb200_read.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
     lib.zflacb200_read.restype = C.c_int
     lib.zflacb200_device_pcm.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]

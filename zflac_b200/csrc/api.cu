@@ -761,8 +761,14 @@ int run_fast_group(FastGroup &g, Events &ev) {
     return ZFLACB200_OK;
 }
 
-int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info) {
-    if (!data || !out || !info) {
+// raw_from != kNotRaw: zflacb200_open_frames() — no signature, no metadata; the stream parameters come from the first
+// frame the sync scan and the CRC-16 links agree on at or after `raw_from` (the robust path only: no stated total).
+constexpr uint64_t kNotRaw = ~0ull;
+
+int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info,
+              uint64_t raw_from = kNotRaw) {
+    const bool raw = raw_from != kNotRaw;
+    if (!data || !out || !info || (raw && raw_from > len)) {
         g_last_error = "null argument";
         return ZFLACB200_INVALID_ARGUMENT;
     }
@@ -786,13 +792,15 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     pl.use_links = (flags & ZFLACB200_NO_CRC_ACCEL) == 0;
 
     // ---- signature + metadata (host, a few dozen bytes)
-    {
+    if (raw) {
+        pl.audio_offset = raw_from;  // moved to the first frame once the scan has found it
+    } else {
         const int e = parse_metadata(pl.src, pl.si, pl.audio_offset);
         if (e != ZFLACB200_OK) return e;
     }
-    const uint32_t depth = pl.si.depth_m1 + 1;            // :256
-    const uint32_t aligned = (depth + 7u) & ~7u;          // :257
-    const uint32_t container_bytes = aligned == 8 ? 1 : aligned == 16 ? 2 : 4;  // :259-264
+    uint32_t depth = pl.si.depth_m1 + 1;            // :256
+    uint32_t aligned = (depth + 7u) & ~7u;          // :257
+    uint32_t container_bytes = aligned == 8 ? 1 : aligned == 16 ? 2 : 4;  // :259-264
     memcpy(info->md5_streaminfo, pl.si.md5, 16);
     info->audio_offset = pl.audio_offset;
     info->container_bytes = (uint8_t)container_bytes;
@@ -848,7 +856,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     uint32_t msb_shift = 0;  // :287-306, keyed on the STREAMINFO depth
     if (depth >= 9 && depth <= 15) msb_shift = 16 - depth;
     else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
-    const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0;
+    const bool do_md5 = (flags & ZFLACB200_SKIP_MD5) == 0 && !raw;  // a raw frame stream states no MD5
 
     // ---- fast path: device-side hinted chain, verified after decoding (no host walk, no CRC-16 pre-pass)
     if (n_cand > 0 && pl.si.total > 0 && (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0 &&
@@ -933,6 +941,31 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     CU_CHECK(cudaEventRecord(ev.e[3], st));
     CU_CHECK(cudaStreamSynchronize(st));
     info->n_candidates = n_cand;
+
+    if (raw) {  // "sync to next frame": the first header whose CRC-16 reaches another header (or the end of the data),
+                // else the first header; its fields stand in for STREAMINFO the way the reference latches them (:376-388)
+        if (n_cand == 0) return ZFLACB200_END_OF_STREAM;  // no frame header before the data ran out
+        uint32_t c0 = 0;
+        for (uint32_t i = 0; i < n_cand; ++i)
+            if (pl.link[i] != kNoLink) { c0 = i; break; }
+        const Cand &c = pl.cands[c0];
+        if (c.bd_code == 0 || kBps[c.bd_code] == 0) return ZFLACB200_MISSING_STREAMINFO;  // "take the depth from STREAMINFO"
+        if (kChCount[c.ch_code] == 0) return ZFLACB200_INVALID_FRAME_HEADER;
+        pl.audio_offset = c.offset;
+        pl.si.channels_m1 = kChCount[c.ch_code] - 1u;
+        pl.si.depth_m1 = kBps[c.bd_code] - 1u;
+        pl.si.sample_rate = c.sr_code == 0 ? 0 : c.sr_value;
+        pl.si.total = 0;  // unknown: the reference's rules for a stream that states no total (:341, :394-402)
+        depth = pl.si.depth_m1 + 1;
+        aligned = (depth + 7u) & ~7u;
+        container_bytes = aligned == 8 ? 1 : aligned == 16 ? 2 : 4;
+        pl.wide = depth == 32;
+        msb_shift = 0;
+        if (depth >= 9 && depth <= 15) msb_shift = 16 - depth;
+        else if (depth >= 17 && depth <= 31) msb_shift = 32 - depth;
+        info->audio_offset = pl.audio_offset;
+        info->container_bytes = (uint8_t)container_bytes;
+    }
 
     // ---- chain + K2, repeated only if a decoded frame end contradicts a CRC-16 link
     Chain chain;
@@ -1907,6 +1940,18 @@ int zflacb200_open(const uint8_t *data, size_t len, const zflacb200_options *opt
         if (*out) { zflacb200_stream *h = *out; *out = nullptr; dev_free(h->d_pcm, nullptr); delete h; }
     }
     return open_impl(data, len, opt, out, info);
+}
+
+int zflacb200_open_frames(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_offset,
+                          zflacb200_stream **out, zflacb200_info *info) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    g_last_error.clear();
+    pin_rewind_all();
+    if (byte_offset == kNotRaw || byte_offset > len) {
+        g_last_error = "byte_offset past the end of the data";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    return open_impl(data, len, opt, out, info, byte_offset);
 }
 
 int zflacb200_read(zflacb200_stream *s, void *dst, size_t dst_bytes) {
