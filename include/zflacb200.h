@@ -217,6 +217,25 @@ int zflacb200_stitch(const zflacb200_range *ranges, size_t n, uint64_t audio_off
 int zflacb200_open_frames(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_offset,
                           zflacb200_stream **out, zflacb200_info *info);
 
+/* ---- Output conventions (additive) ------------------------------------------------------------------
+ * The reference leaves the output convention open (Readme.md:53 "auto convert to u8"; src/zflac.zig:282-292: "output
+ * conventions differ quite a bit ... let the caller deal with it") and returns s8 / s16 / s32, MSB-aligned for 9-15 and
+ * 17-31 bit streams. zflacb200_read() returns exactly that. zflacb200_read_as() re-expresses the same decoded PCM with one
+ * streaming pass on the device before the read-back:
+ *   F32         float, v * 2^-7 / 2^-15 / 2^-31 for the s8 / s16 / s32 container (int -> float rounds to nearest even)
+ *   S24_PACKED  s32 container only: the top 24 bits of every sample (v >> 8), 3 bytes little-endian — for a 24-bit stream
+ *               that is the sample as coded; a 32-bit stream loses its low 8 bits
+ *   U8          s8 container only: v +% 128, the commented-out loop at :288-292
+ * A format the stream's container does not define is ZFLACB200_INVALID_ARGUMENT. */
+typedef enum zflacb200_format {
+    ZFLACB200_FMT_NATIVE = 0, /* what zflacb200_read() writes */
+    ZFLACB200_FMT_F32 = 1,
+    ZFLACB200_FMT_S24_PACKED = 2,
+    ZFLACB200_FMT_U8 = 3
+} zflacb200_format;
+int zflacb200_format_bytes(zflacb200_stream *s, int format, uint64_t *bytes); /* what zflacb200_read_as() writes */
+int zflacb200_read_as(zflacb200_stream *s, int format, void *dst, size_t dst_bytes);
+
 /* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
 typedef struct zflacb200_frame {
     uint64_t offset;        /* byte offset of the sync code */

@@ -94,6 +94,7 @@ def _as_u8(data) -> np.ndarray:
 
 
 _DTYPES = {1: np.int8, 2: np.int16, 4: np.int32}
+FORMATS = {"native": 0, "f32": 1, "s24": 2, "u8": 3}  # zflacb200_format
 
 
 def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bool = True,
@@ -233,6 +234,22 @@ class DeviceStream:
     def to_host(self) -> np.ndarray:
         out = np.empty(self.n_samples, dtype=_DTYPES[self.container_bytes])
         st = _native.load().zflacb200_read(self._h, out.ctypes.data, out.nbytes)
+        if st != 0:
+            _raise(st)
+        return out
+
+    def to_host_as(self, fmt: str) -> np.ndarray:
+        """Read the PCM back in another output convention (zflacb200_read_as): "native", "f32" (normalised float),
+        "s24" (packed 3-byte little-endian, s32 streams; returned as a uint8 array of 3 * n bytes), "u8" (s8 streams)."""
+        lib = _native.load()
+        code = FORMATS[fmt]
+        need = C.c_uint64()
+        st = lib.zflacb200_format_bytes(self._h, code, C.byref(need))
+        if st != 0:
+            _raise(st)
+        dt = {0: _DTYPES[self.container_bytes], 1: np.float32, 2: np.uint8, 3: np.uint8}[code]
+        out = np.empty(need.value // np.dtype(dt).itemsize, dtype=dt)
+        st = lib.zflacb200_read_as(self._h, code, out.ctypes.data, out.nbytes)
         if st != 0:
             _raise(st)
         return out

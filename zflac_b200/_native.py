@@ -23,6 +23,7 @@ EXPORTS = [
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
     "zflacb200_batch_close", "zflacb200_batch_pcm_bound", "zflacb200_batch_decode",
     "zflacb200_decode_range", "zflacb200_stitch", "zflacb200_open_frames",
+    "zflacb200_format_bytes", "zflacb200_read_as",
 ]
 
 
@@ -81,6 +82,10 @@ def load():
     lib.zflacb200_open_frames.restype = C.c_int
     lib.zflacb200_read.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
     lib.zflacb200_read.restype = C.c_int
+    lib.zflacb200_format_bytes.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+    lib.zflacb200_format_bytes.restype = C.c_int
+    lib.zflacb200_read_as.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+    lib.zflacb200_read_as.restype = C.c_int
     lib.zflacb200_device_pcm.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
     lib.zflacb200_device_pcm.restype = C.c_int
     lib.zflacb200_close.argtypes = [C.c_void_p]

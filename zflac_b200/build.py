@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "_lib")
 LIB_PATH = os.path.join(LIB_DIR, "libzflacb200.so")
-SOURCES = ["scan.cu", "chain.cu", "decode.cu", "parse.cu", "predict.cu", "epilogue.cu", "xfer.cu", "api.cu"]
+SOURCES = ["scan.cu", "chain.cu", "decode.cu", "parse.cu", "predict.cu", "epilogue.cu", "xfer.cu", "convert.cu", "api.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "-Xcompiler", "-Wno-unknown-pragmas", "--expt-relaxed-constexpr"]
 

@@ -1966,6 +1966,55 @@ int zflacb200_read(zflacb200_stream *s, void *dst, size_t dst_bytes) {
     return ZFLACB200_OK;
 }
 
+static int format_bytes(const zflacb200_stream *s, int format, uint64_t *bytes) {
+    const uint64_t n = s->info.n_samples;
+    const uint32_t cb = s->info.container_bytes;
+    switch (format) {
+        case ZFLACB200_FMT_NATIVE: *bytes = s->pcm_bytes; return ZFLACB200_OK;
+        case ZFLACB200_FMT_F32: *bytes = n * 4; return ZFLACB200_OK;
+        case ZFLACB200_FMT_S24_PACKED:
+            if (cb != 4) break;
+            *bytes = n * 3;
+            return ZFLACB200_OK;
+        case ZFLACB200_FMT_U8:
+            if (cb != 1) break;
+            *bytes = n;
+            return ZFLACB200_OK;
+        default: break;
+    }
+    g_last_error = "format not defined for this stream's container";
+    return ZFLACB200_INVALID_ARGUMENT;
+}
+
+int zflacb200_format_bytes(zflacb200_stream *s, int format, uint64_t *bytes) {
+    if (!s || !bytes) return ZFLACB200_INVALID_ARGUMENT;
+    return format_bytes(s, format, bytes);
+}
+
+int zflacb200_read_as(zflacb200_stream *s, int format, void *dst, size_t dst_bytes) {
+    if (!s) return ZFLACB200_INVALID_ARGUMENT;
+    if (format == ZFLACB200_FMT_NATIVE) return zflacb200_read(s, dst, dst_bytes);
+    uint64_t need = 0;
+    {
+        const int e = format_bytes(s, format, &need);
+        if (e != ZFLACB200_OK) return e;
+    }
+    if ((!dst && need) || dst_bytes < need) {
+        g_last_error = "destination smaller than zflacb200_format_bytes()";
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    if (need == 0) return ZFLACB200_OK;
+    std::lock_guard<std::mutex> lock(g_mutex);
+    CU_CHECK(cudaSetDevice(s->device));
+    cudaStream_t st = g_ctx[s->device].stream;
+    DevBuf b_out;
+    if (b_out.alloc(need + 64, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    CU_CHECK(launch_convert_pcm(s->d_pcm, s->info.n_samples, s->info.container_bytes, format, b_out.p, st));
+    CU_CHECK(cudaMemcpyAsync(dst, b_out.p, need, cudaMemcpyDeviceToHost, st));
+    CU_CHECK(cudaStreamSynchronize(st));
+    return ZFLACB200_OK;
+}
+
 int zflacb200_device_pcm(zflacb200_stream *s, void **dev_ptr, size_t *bytes) {
     if (!s || !dev_ptr || !bytes) return ZFLACB200_INVALID_ARGUMENT;
     *dev_ptr = s->d_pcm;

@@ -99,4 +99,8 @@ struct Md5Job {
 };
 cudaError_t launch_md5(const Md5Job *d_jobs, uint32_t n_jobs, uint8_t *d_digests, cudaStream_t st);
 
+// convert.cu: output conventions (zflacb200_read_as). Values match zflacb200_format in include/zflacb200.h.
+constexpr int kFmtNative = 0, kFmtF32 = 1, kFmtS24 = 2, kFmtU8 = 3;
+cudaError_t launch_convert_pcm(const void *pcm, uint64_t n_samples, uint32_t container_bytes, int fmt, void *out, cudaStream_t st);
+
 }  // namespace zf
