@@ -236,6 +236,39 @@ typedef enum zflacb200_format {
 int zflacb200_format_bytes(zflacb200_stream *s, int format, uint64_t *bytes); /* what zflacb200_read_as() writes */
 int zflacb200_read_as(zflacb200_stream *s, int format, void *dst, size_t dst_bytes);
 
+/* ---- Metadata surface (additive, host only, no device needed) ----------------------------------------
+ * The reference walks the metadata blocks and skips everything but STREAMINFO (src/zflac.zig:243-247). These calls run the
+ * same walk — same errors in the same order (InvalidSignature :220, EndOfStream, InvalidMetadataHeader :248,
+ * MissingStreaminfo :309) — and report what it stepped over. `data` is a HOST pointer. Each call fills at most `capacity`
+ * entries of `dst` (NULL allowed) and always sets the count, so a caller can size the array with a first call. */
+typedef struct zflacb200_metadata_block {
+    uint64_t offset;       /* of the block's data, just past its 4-byte header */
+    uint32_t length;       /* the 24-bit length field as stored */
+    uint32_t stored_bytes; /* what the walk advances by: `length`, except STREAMINFO = 34 whatever the field says (:224-240) */
+    uint8_t type;          /* 0 STREAMINFO, 1 PADDING, 2 APPLICATION, 3 SEEKTABLE, 4 VORBIS_COMMENT, 5 CUESHEET, 6 PICTURE */
+    uint8_t is_last;
+    uint8_t pad[6];
+} zflacb200_metadata_block;
+int zflacb200_metadata(const uint8_t *data, size_t len, zflacb200_metadata_block *dst, size_t capacity, size_t *n_blocks,
+                       uint64_t *audio_offset);
+
+/* SEEKTABLE (RFC 9639 8.5): stream_offset counts from the first frame (add audio_offset). */
+typedef struct zflacb200_seekpoint {
+    uint64_t sample_number; /* first sample (per channel) of the target frame; 0xFFFFFFFFFFFFFFFF = placeholder */
+    uint64_t stream_offset;
+    uint32_t frame_samples;
+    uint32_t is_placeholder;
+} zflacb200_seekpoint;
+int zflacb200_seektable(const uint8_t *data, size_t len, zflacb200_seekpoint *dst, size_t capacity, size_t *n_points);
+
+/* VORBIS_COMMENT (RFC 9639 8.6): byte spans inside `data` of the vendor string and of each "NAME=value" field (UTF-8, not
+ * NUL-terminated). A block whose internal lengths overrun it is InvalidMetadataHeader. */
+typedef struct zflacb200_span {
+    uint64_t offset, length;
+} zflacb200_span;
+int zflacb200_vorbis_comments(const uint8_t *data, size_t len, zflacb200_span *vendor, zflacb200_span *dst, size_t capacity,
+                              size_t *n_comments);
+
 /* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
 typedef struct zflacb200_frame {
     uint64_t offset;        /* byte offset of the sync code */

@@ -1,0 +1,100 @@
+"""CPU (host-only entry points, no device): zflacb200_metadata / _seektable / _vorbis_comments against
+an independent walk in Python and against the oracle — same errors as the reference's metadata walk
+(src/zflac.zig:217-253, :309), same audio offset, and every seek point lands on a frame of the oracle's chain."""
+import struct
+
+import numpy as np
+import pytest
+
+from conftest import corpus_bytes, corpus_entries, corpus_ids
+
+HEAD_ERRORS = ("InvalidSignature", "InvalidMetadataHeader", "MissingStreaminfo")
+
+
+def py_walk(data: bytes):
+    assert data[:4] == b"fLaC"
+    pos, blocks = 4, []
+    while True:
+        t, last = data[pos] & 0x7F, data[pos] >> 7
+        length = int.from_bytes(data[pos + 1: pos + 4], "big")
+        stored = 34 if t == 0 else length
+        blocks.append((t, pos + 4, length, stored, last))
+        pos += 4 + stored
+        if last:
+            return blocks, pos
+
+
+@pytest.fixture(scope="module")
+def z():
+    import zflac_b200
+    return zflac_b200
+
+
+@pytest.mark.parametrize("entry", corpus_entries(), ids=corpus_ids())
+def test_corpus_metadata(z, entry):
+    from oracle import oracle
+    data = corpus_bytes(entry)
+    ref = oracle.decode(data, trace_frames=True, keep_on_md5_mismatch=True, copy_samples=False)
+    if ref.error in HEAD_ERRORS:
+        with pytest.raises(z.ZflacError) as ei:
+            z.metadata(data)
+        assert type(ei.value).__name__ == ref.error
+        return
+    m = z.metadata(data)
+    blocks, audio = py_walk(data)
+    assert m["audio_offset"] == audio == ref.audio_offset
+    assert [(z.BLOCK_TYPES.index(b["type"]), b["offset"], b["length"], b["stored_bytes"], int(b["is_last"])) for b in m["blocks"]] == blocks
+    # SEEKTABLE: every real point is a frame of the oracle's chain, at that sample number
+    st = [b for b in blocks if b[0] == 3]
+    assert len(m["seektable"]) == (st[0][3] // 18 if st else 0)
+    if st and ref.frames is not None and len(ref.frames):
+        ch = max(ref.channels, 1)
+        starts = {int(o): int(s) // ch for o, s in zip(ref.frames["offset"], ref.frames["sample_offset"])}
+        for k, p in enumerate(m["seektable"]):
+            sn, so, fs = struct.unpack(">QQH", data[st[0][1] + 18 * k: st[0][1] + 18 * k + 18])
+            assert (p["sample_number"], p["stream_offset"], p["frame_samples"]) == (sn, so, fs)
+            if p["is_placeholder"]:
+                continue
+            at = audio + p["stream_offset"]
+            if at in starts:  # (a truncated or faulty file may list points past what decodes)
+                assert starts[at] == p["sample_number"]
+            else:
+                assert entry["expect_error"] or at >= int(ref.frames["end_offset"][-1])
+    # VORBIS_COMMENT
+    vc = [b for b in blocks if b[0] == 4]
+    if (entry["group"], entry["id"]) == ("faulty", "10"):  # "invalid vorbis comment metadata block": decodes, comments do not parse
+        assert m["comments_error"] == "InvalidMetadataHeader" and m["comments"] == [] and not entry["expect_error"]
+    elif vc:
+        o = vc[0][1]
+        vl = int.from_bytes(data[o: o + 4], "little")
+        assert m["vendor"] == data[o + 4: o + 4 + vl].decode("utf-8", "replace")
+        n = int.from_bytes(data[o + 4 + vl: o + 8 + vl], "little")
+        assert len(m["comments"]) == n
+        q = o + 8 + vl
+        for c in m["comments"][:50]:
+            cl = int.from_bytes(data[q: q + 4], "little")
+            assert c == data[q + 4: q + 4 + cl].decode("utf-8", "replace")
+            q += 4 + cl
+    else:
+        assert m["vendor"] == "" and m["comments"] == []
+
+
+def test_head_errors_in_the_reference_order(z):
+    si = bytes([0x80, 0, 0, 34]) + bytes(34)
+    with pytest.raises(z.InvalidSignature):
+        z.metadata(b"fLaX" + si)
+    with pytest.raises(z.EndOfStream):
+        z.metadata(b"fL")
+    with pytest.raises(z.EndOfStream):
+        z.metadata(b"fLaC" + si[:20])
+    with pytest.raises(z.InvalidMetadataHeader):
+        z.metadata(b"fLaC" + bytes([0x07, 0, 0, 0]) + si)
+    with pytest.raises(z.MissingStreaminfo):
+        z.metadata(b"fLaC" + bytes([0x81, 0, 0, 4]) + bytes(4))
+    with pytest.raises(z.EndOfStream):  # a block longer than the data
+        z.metadata(b"fLaC" + bytes([0x00, 0, 0, 34]) + bytes(34) + bytes([0x81, 0, 1, 0]) + bytes(10))
+    # comment lengths overrun the block: the walk is fine (the reference skips the block), the comments are not
+    m = z.metadata(b"fLaC" + bytes([0x00, 0, 0, 34]) + bytes(34) + bytes([0x84, 0, 0, 8]) + (100).to_bytes(4, "little") + bytes(4))
+    assert m["comments_error"] == "InvalidMetadataHeader" and m["audio_offset"] == 54
+    m = z.metadata(b"fLaC" + bytes([0x80, 0, 0, 99]) + bytes(34))  # Q13: STREAMINFO is 34 bytes whatever its length field says
+    assert m["audio_offset"] == 42 and m["blocks"][0]["length"] == 99 and m["blocks"][0]["stored_bytes"] == 34

@@ -24,7 +24,7 @@ from . import _native
 from ._native import INPUT_ON_DEVICE, NO_CRC_ACCEL, NO_FAST_PATH, SKIP_FRAME_CRC16, SKIP_MD5, VERIFY_MD5  # noqa: F401
 
 __all__ = ["decode", "decode_into", "decode_batch", "open_batch", "DeviceBatch", "pack_streams", "DecodedFLAC", "ZflacError",
-           "CudaError", "open_device", "DeviceStream", "decode_frames"]
+           "CudaError", "open_device", "DeviceStream", "decode_frames", "metadata"]
 
 
 class ZflacError(Exception):
@@ -215,6 +215,43 @@ def stitch_ranges(rows, audio_offset: int) -> bool:
         b.struct_size = C.sizeof(_native.Range)
         b.accepted, b.first_frame_offset, b.end_offset, b.first_sample, b.n_samples, b.n_frames, b.total_samples = r
     return bool(_native.load().zflacb200_stitch(buf, len(rows), int(audio_offset)))
+
+
+BLOCK_TYPES = ("STREAMINFO", "PADDING", "APPLICATION", "SEEKTABLE", "VORBIS_COMMENT", "CUESHEET", "PICTURE")
+
+
+def metadata(data) -> dict:
+    """Additive, host only: what the reference's metadata walk steps over (src/zflac.zig:243-247) — the block list, the
+    SEEKTABLE and the VORBIS_COMMENT fields. Raises the same errors decode() raises for a broken head."""
+    lib = _native.load()
+    arr = _as_u8(data)
+    n, ao = C.c_size_t(), C.c_uint64()
+    st = lib.zflacb200_metadata(arr.ctypes.data, arr.size, None, 0, C.byref(n), C.byref(ao))
+    if st != 0:
+        _raise(st)
+    blocks = (_native.MetadataBlock * max(n.value, 1))()
+    lib.zflacb200_metadata(arr.ctypes.data, arr.size, blocks, n.value, C.byref(n), C.byref(ao))
+    out = {"audio_offset": ao.value,
+           "blocks": [dict(type=BLOCK_TYPES[b.type], offset=b.offset, length=b.length, stored_bytes=b.stored_bytes,
+                           is_last=bool(b.is_last)) for b in blocks[: n.value]]}
+    st = lib.zflacb200_seektable(arr.ctypes.data, arr.size, None, 0, C.byref(n))
+    if st != 0:
+        _raise(st)
+    pts = (_native.SeekPoint * max(n.value, 1))()
+    lib.zflacb200_seektable(arr.ctypes.data, arr.size, pts, n.value, C.byref(n))
+    out["seektable"] = [dict(sample_number=p.sample_number, stream_offset=p.stream_offset, frame_samples=p.frame_samples,
+                             is_placeholder=bool(p.is_placeholder)) for p in pts[: n.value]]
+    vendor = _native.Span()
+    st = lib.zflacb200_vorbis_comments(arr.ctypes.data, arr.size, C.byref(vendor), None, 0, C.byref(n))
+    if st != 0:  # a malformed comment block (flac-test-files faulty/10) does not stop the reference, which skips the block
+        out.update(vendor="", comments=[], comments_error=lib.zflacb200_status_name(st).decode())
+        return out
+    spans = (_native.Span * max(n.value, 1))()
+    lib.zflacb200_vorbis_comments(arr.ctypes.data, arr.size, C.byref(vendor), spans, n.value, C.byref(n))
+    raw = arr.tobytes() if n.value or vendor.length else b""
+    out["vendor"] = raw[vendor.offset: vendor.offset + vendor.length].decode("utf-8", "replace")
+    out["comments"] = [raw[s.offset: s.offset + s.length].decode("utf-8", "replace") for s in spans[: n.value]]
+    return out
 
 
 class DeviceStream:

@@ -23,7 +23,7 @@ EXPORTS = [
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
     "zflacb200_batch_close", "zflacb200_batch_pcm_bound", "zflacb200_batch_decode",
     "zflacb200_decode_range", "zflacb200_stitch", "zflacb200_open_frames",
-    "zflacb200_format_bytes", "zflacb200_read_as",
+    "zflacb200_format_bytes", "zflacb200_read_as", "zflacb200_metadata", "zflacb200_seektable", "zflacb200_vorbis_comments",
 ]
 
 
@@ -45,6 +45,20 @@ class Range(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("accepted", C.c_uint32), ("first_frame_offset", C.c_uint64),
                 ("end_offset", C.c_uint64), ("first_sample", C.c_uint64), ("n_samples", C.c_uint64),
                 ("n_frames", C.c_uint64), ("total_samples", C.c_uint64)]
+
+
+class MetadataBlock(C.Structure):
+    _fields_ = [("offset", C.c_uint64), ("length", C.c_uint32), ("stored_bytes", C.c_uint32), ("type", C.c_uint8),
+                ("is_last", C.c_uint8), ("pad", C.c_uint8 * 6)]
+
+
+class SeekPoint(C.Structure):
+    _fields_ = [("sample_number", C.c_uint64), ("stream_offset", C.c_uint64), ("frame_samples", C.c_uint32),
+                ("is_placeholder", C.c_uint32)]
+
+
+class Span(C.Structure):
+    _fields_ = [("offset", C.c_uint64), ("length", C.c_uint64)]
 
 
 class Frame(C.Structure):
@@ -86,6 +100,14 @@ def load():
     lib.zflacb200_format_bytes.restype = C.c_int
     lib.zflacb200_read_as.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
     lib.zflacb200_read_as.restype = C.c_int
+    lib.zflacb200_metadata.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(MetadataBlock), C.c_size_t, C.POINTER(C.c_size_t),
+                                       C.POINTER(C.c_uint64)]
+    lib.zflacb200_metadata.restype = C.c_int
+    lib.zflacb200_seektable.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(SeekPoint), C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.zflacb200_seektable.restype = C.c_int
+    lib.zflacb200_vorbis_comments.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Span), C.POINTER(Span), C.c_size_t,
+                                              C.POINTER(C.c_size_t)]
+    lib.zflacb200_vorbis_comments.restype = C.c_int
     lib.zflacb200_device_pcm.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
     lib.zflacb200_device_pcm.restype = C.c_int
     lib.zflacb200_close.argtypes = [C.c_void_p]

@@ -2306,6 +2306,123 @@ void zflacb200_batch_close(zflacb200_batch *b) {
     delete b;
 }
 
+// ---- metadata surface (host only): the blocks the reference's walk skips over (src/zflac.zig:243-247)
+static int walk_metadata(const uint8_t *data, size_t len, std::vector<zflacb200_metadata_block> &blocks, uint64_t &audio_offset) {
+    // same walk, same errors, same order as parse_metadata() / :217-253 + :309
+    if (len < 4) return ZFLACB200_END_OF_STREAM;
+    if (!(data[0] == 0x66 && data[1] == 0x4C && data[2] == 0x61 && data[3] == 0x43)) return ZFLACB200_INVALID_SIGNATURE;
+    uint64_t pos = 4;
+    bool have = false;
+    for (;;) {
+        if (len - pos < 4) return ZFLACB200_END_OF_STREAM;
+        const uint8_t *b = data + pos;
+        pos += 4;
+        zflacb200_metadata_block mb;
+        memset(&mb, 0, sizeof(mb));
+        mb.type = b[0] & 0x7F;
+        mb.is_last = (b[0] & 0x80) ? 1 : 0;
+        mb.length = ((uint32_t)b[1] << 16) | ((uint32_t)b[2] << 8) | b[3];
+        mb.offset = pos;
+        if (mb.type == 0) {  // STREAMINFO is read as 34 bytes whatever its length field says (Q13)
+            if (len - pos < 34) return ZFLACB200_END_OF_STREAM;
+            mb.stored_bytes = 34;
+            have = true;
+        } else if (mb.type >= 1 && mb.type <= 6) {
+            if (len - pos < mb.length) return ZFLACB200_END_OF_STREAM;
+            mb.stored_bytes = mb.length;
+        } else {
+            return ZFLACB200_INVALID_METADATA_HEADER;
+        }
+        pos += mb.stored_bytes;
+        blocks.push_back(mb);
+        if (mb.is_last) break;
+    }
+    if (!have) return ZFLACB200_MISSING_STREAMINFO;
+    audio_offset = pos;
+    return ZFLACB200_OK;
+}
+
+static uint64_t be_uint(const uint8_t *p, int n) {
+    uint64_t v = 0;
+    for (int i = 0; i < n; ++i) v = (v << 8) | p[i];
+    return v;
+}
+
+int zflacb200_metadata(const uint8_t *data, size_t len, zflacb200_metadata_block *dst, size_t capacity, size_t *n_blocks,
+                       uint64_t *audio_offset) {
+    if (!data || !n_blocks) return ZFLACB200_INVALID_ARGUMENT;
+    std::vector<zflacb200_metadata_block> blocks;
+    uint64_t ao = 0;
+    const int e = walk_metadata(data, len, blocks, ao);
+    *n_blocks = blocks.size();
+    for (size_t i = 0; dst && i < blocks.size() && i < capacity; ++i) dst[i] = blocks[i];
+    if (e != ZFLACB200_OK) return e;
+    if (audio_offset) *audio_offset = ao;
+    return ZFLACB200_OK;
+}
+
+int zflacb200_seektable(const uint8_t *data, size_t len, zflacb200_seekpoint *dst, size_t capacity, size_t *n_points) {
+    if (!data || !n_points) return ZFLACB200_INVALID_ARGUMENT;
+    *n_points = 0;
+    std::vector<zflacb200_metadata_block> blocks;
+    uint64_t ao = 0;
+    const int e = walk_metadata(data, len, blocks, ao);
+    if (e != ZFLACB200_OK) return e;
+    for (const zflacb200_metadata_block &mb : blocks) {
+        if (mb.type != 3) continue;
+        const size_t n = mb.stored_bytes / 18;  // 64-bit sample number, 64-bit offset from the first frame, 16-bit frame samples
+        *n_points = n;
+        for (size_t i = 0; dst && i < n && i < capacity; ++i) {
+            const uint8_t *p = data + mb.offset + 18 * i;
+            dst[i].sample_number = be_uint(p, 8);
+            dst[i].stream_offset = be_uint(p + 8, 8);
+            dst[i].frame_samples = (uint32_t)be_uint(p + 16, 2);
+            dst[i].is_placeholder = dst[i].sample_number == ~0ull ? 1u : 0u;
+        }
+        break;  // a stream has at most one SEEKTABLE; the first one counts
+    }
+    return ZFLACB200_OK;
+}
+
+int zflacb200_vorbis_comments(const uint8_t *data, size_t len, zflacb200_span *vendor, zflacb200_span *dst, size_t capacity,
+                              size_t *n_comments) {
+    if (!data || !n_comments) return ZFLACB200_INVALID_ARGUMENT;
+    *n_comments = 0;
+    if (vendor) vendor->offset = vendor->length = 0;
+    std::vector<zflacb200_metadata_block> blocks;
+    uint64_t ao = 0;
+    const int e = walk_metadata(data, len, blocks, ao);
+    if (e != ZFLACB200_OK) return e;
+    for (const zflacb200_metadata_block &mb : blocks) {
+        if (mb.type != 4) continue;
+        // little-endian (Vorbis convention): vendor length + vendor, count, then count x (length + "NAME=value")
+        const uint64_t end = mb.offset + mb.stored_bytes;
+        uint64_t pos = mb.offset;
+        auto le32 = [&](uint64_t at, uint32_t &v) {
+            if (end - at < 4) return false;
+            v = (uint32_t)data[at] | ((uint32_t)data[at + 1] << 8) | ((uint32_t)data[at + 2] << 16) | ((uint32_t)data[at + 3] << 24);
+            return true;
+        };
+        uint32_t vlen = 0, count = 0;
+        if (!le32(pos, vlen) || end - (pos + 4) < vlen) return ZFLACB200_INVALID_METADATA_HEADER;
+        if (vendor) { vendor->offset = pos + 4; vendor->length = vlen; }
+        pos += 4 + (uint64_t)vlen;
+        if (!le32(pos, count)) return ZFLACB200_INVALID_METADATA_HEADER;
+        pos += 4;
+        size_t got = 0;
+        for (uint32_t i = 0; i < count; ++i) {
+            uint32_t clen = 0;
+            if (!le32(pos, clen) || end - (pos + 4) < clen) return ZFLACB200_INVALID_METADATA_HEADER;
+            if (dst && got < capacity) { dst[got].offset = pos + 4; dst[got].length = clen; }
+            ++got;
+            pos += 4 + (uint64_t)clen;
+        }
+        *n_comments = got;
+        break;
+    }
+    return ZFLACB200_OK;
+}
+
 int zflacb200_frames(zflacb200_stream *s, zflacb200_frame *dst, size_t capacity, size_t *n_frames) {
     if (!s || !n_frames) return ZFLACB200_INVALID_ARGUMENT;
     if (s->frames_on_device) {  // fast path: build the table from the device records on first use
