@@ -81,3 +81,4 @@ def test_truncated_streams_match_oracle_errors(z):
             with pytest.raises(z.ZflacError) as ei:
                 z.decode(data)
             assert type(ei.value).__name__ == want, cut
+

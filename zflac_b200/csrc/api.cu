@@ -768,7 +768,7 @@ constexpr uint64_t kNotRaw = ~0ull;
 int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info,
               uint64_t raw_from = kNotRaw) {
     const bool raw = raw_from != kNotRaw;
-    if (!data || !out || !info || (raw && raw_from > len)) {
+    if ((!data && len) || !out || !info || (raw && raw_from > len)) {  // an empty slice may carry a null pointer: EndOfStream below
         g_last_error = "null argument";
         return ZFLACB200_INVALID_ARGUMENT;
     }
