@@ -34,6 +34,13 @@ sys.path.insert(0, ROOT)
 METRIC = "decoded Msamples/s (interleaved PCM samples out; compressed GB/s alongside)"
 
 
+def shared_config(name: str) -> dict:
+    """config of BOTH arms, byte-identical (the driver compares them): what is measured, not how long it took."""
+    return {"workload": name,
+            "frame_crc16": "the library's per-frame CRC-16 diagnostic is off in value and e2e (the reference and the CPU arm ignore the field); value_with_frame_crc16 has it on",
+            "md5": "value excludes the MD5 pass on BOTH arms (one serial chain per stream); `gated` / value_with_md5 include it, as the reference's decode() does"}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -42,7 +49,8 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5", "c2r"])
     ap.add_argument("--seconds", type=float, default=None, help="stream length (default: c2 3600 s, c3 600 s)")
-    ap.add_argument("--md5-steps", type=int, default=1, help="timed steps of the MD5-gated variant (serial chain, slow)")
+    ap.add_argument("--md5-steps", type=int, default=2, help="timed steps of the MD5-gated variant (one serial chain on a host thread, ~1 s per step on c2)")
+    ap.add_argument("--md5-device-steps", type=int, default=0, help="timed steps with the chain on the GPU (k_md5: ~5 s per step on c2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--files", type=int, default=10000, help="c5: number of files in the batch (whole job)")
@@ -191,9 +199,7 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": "Msamples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32/int64", "data": "synthetic",
-        "config": {"workload": name, "sample": sample,
-                   "frame_crc16": "the library's per-frame CRC-16 diagnostic is off in value and e2e (the reference and the CPU arm ignore the field); value_with_frame_crc16 has it on",
-                   "md5": "value excludes the MD5 pass on BOTH arms (one serial chain per stream); value_with_md5 includes it, as the reference's decode() does"},
+        "config": shared_config(name), "sample": sample,
         "value_with_md5": round(value_with, 3), "ms_per_step_with_md5": round(ms_with, 3),
         "compressed_gbs": round(copies * s.flac.size / (ms * 1e-3) / 1e9, 4),
         "cpu_baseline": {"value": round(value, 3), "unit": "Msamples/s", "cores": copies, "kind": "port", "sample": sample,
@@ -269,8 +275,9 @@ def main():
     # The per-frame CRC-16 is a diagnostic of this library (info.n_crc16_mismatch): the reference reads the field and
     # ignores it (src/zflac.zig:551) and so does the CPU arm, so the timed steps of both arms leave it out; the same
     # step with the diagnostic on is reported next to it (value_with_frame_crc16).
-    def step_device(verify_md5, frame_crc16=False):
-        s = z.open_device(d_flac.data_ptr(), flac_bytes, device=local_rank, stream=sptr, verify_md5=verify_md5, frame_crc16=frame_crc16)
+    def step_device(verify_md5, frame_crc16=False, md5_on_device=False):
+        s = z.open_device(d_flac.data_ptr(), flac_bytes, device=local_rank, stream=sptr, verify_md5=verify_md5, frame_crc16=frame_crc16,
+                          md5_on_device=md5_on_device)
         info = s.info
         s.close()
         return info
@@ -324,9 +331,11 @@ def main():
     ms_dev_crc, _, _, _ = timed(lambda: step_device(False, True), max(3, args.steps // 2), 1)
 
     # MD5-gated variant (K1->K4): a single stream's MD5 is one serial chain
-    ms_dev_md5 = None
+    ms_dev_md5 = ms_dev_md5_gpu = None
     if args.md5_steps > 0:
         ms_dev_md5, _, _, _ = timed(lambda: step_device(True), args.md5_steps, 1)
+        if args.md5_device_steps > 0:  # the device-side chain (k_md5), for the record: ~5 s per step on C2
+            ms_dev_md5_gpu, _, _, _ = timed(lambda: step_device(True, md5_on_device=True), args.md5_device_steps, 0)
 
     # ---------------------------------------------------------------- end to end through the public API
     e2e = None
@@ -367,6 +376,17 @@ def main():
             dist.destroy_process_group()
         return
 
+    # the drop-in decode() contract: MD5 gate ON (the library's default and the only mode the reference has)
+    gated = None
+    if ms_dev_md5:
+        gated = {"value": round(world * n_samples / (ms_dev_md5 * 1e-3) / 1e6, 2), "ms_per_step": round(ms_dev_md5, 3),
+                 "e2e": e2e.get("value_with_md5") if e2e else None,
+                 "e2e_ms_per_step": e2e.get("ms_per_step_with_md5") if e2e else None,
+                 "vs_cpu": round(e2e["value_with_md5"] / cpu["value"], 2) if e2e and cpu and e2e.get("value_with_md5") else None,
+                 "unit": "Msamples/s",
+                 "md5": "one stream's MD5 is a serial chain: it runs on ONE host thread over the PCM as it lands in host memory "
+                        "(verification only, no sample is produced on the CPU); the device chain (ZFLACB200_MD5_ON_DEVICE) is in md5_on_device",
+                 "md5_on_device_ms_per_step": round(ms_dev_md5_gpu, 3) if ms_dev_md5_gpu else None}
     peak, peak_src = measured_peak()
     algo_bytes = audio_bytes + pcm_bytes  # compressed read once + PCM written once
     dom = max(("ms_decode", "ms_epilogue", "ms_scan", "ms_link"), key=lambda f: k[f])
@@ -377,12 +397,12 @@ def main():
         "metric": METRIC, "value": round(value, 2), "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_dev, 4), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32/int64", "data": "synthetic",
-        "config": {"workload": wl_name, "samples_per_step_per_gpu": n_samples, "frames": int(info0["n_frames"]),
-                   "compressed_bytes": flac_bytes, "pcm_bytes": pcm_bytes, "sharding": "one stream per GPU, no collective",
-                   "l2": "inputs larger than L2 (no flush needed)" if flac_bytes > 126 * 2**20 else "input smaller than L2",
-                   "frame_crc16": "the library's per-frame CRC-16 diagnostic is off in value and e2e (the reference and the CPU arm ignore the field); value_with_frame_crc16 has it on",
-                   "md5": "value excludes the MD5 pass on BOTH arms (one serial chain per stream); value_with_md5 includes it, as the reference's decode() does",
-                   "generator_s": round(t_gen, 2)},
+        "config": shared_config(wl_name),
+        "workload_detail": {"samples_per_step_per_gpu": n_samples, "frames": int(info0["n_frames"]),
+                            "compressed_bytes": flac_bytes, "pcm_bytes": pcm_bytes, "sharding": "one stream per GPU, no collective",
+                            "l2": "inputs larger than L2 (no flush needed)" if flac_bytes > 126 * 2**20 else "input smaller than L2",
+                            "generator_s": round(t_gen, 2)},
+        "gated": gated,
         "compressed_gbs": round(world * flac_bytes / (ms_dev * 1e-3) / 1e9, 3),
         "value_with_frame_crc16": round(world * n_samples / (ms_dev_crc * 1e-3) / 1e6, 2), "ms_per_step_with_frame_crc16": round(ms_dev_crc, 4),
         "value_with_md5": round(world * n_samples / (ms_dev_md5 * 1e-3) / 1e6, 2) if ms_dev_md5 else None,

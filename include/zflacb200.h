@@ -71,6 +71,9 @@ typedef enum zflacb200_status {
                                           * ignores it, :551): info.n_crc16_mismatch stays 0, zflacb200_frame.crc16_ok says 2 = not checked */
 #define ZFLACB200_NO_PIPELINE 0x40u    /* diagnostics: zflacb200_decode uploads, decodes and reads back one after the other */
 #define ZFLACB200_SINGLE_PASS 0x20u    /* diagnostics: fused single-pass subframe decoder (K2 + K3) instead of parse + predict */
+#define ZFLACB200_MD5_ON_DEVICE 0x100u /* diagnostics: run a single stream's MD5 chain on the GPU (k_md5, 119 MB/s) instead of on a host
+                                        * thread over the PCM as it lands in host memory (the default for streams >= 256 KiB of PCM;
+                                        * batches always hash on the device, one chain per lane) */
 
 typedef struct zflacb200_options {
     uint32_t struct_size; /* sizeof(zflacb200_options) */

@@ -62,8 +62,14 @@ assert check(s.flac) == "fast"
 assert check_device(s.flac) == "fast"
 assert check_device(s.flac, verify_md5=False) == "fast"
 assert check(s.flac, verify_md5=False) == "fast"
+assert check(s.flac, md5_on_device=True) == "fast"     # the device chain instead of the host hash worker
+assert check_device(s.flac, md5_on_device=True) == "fast"
+wrong = s.flac.copy(); wrong[8 + 18 + 7] ^= 0x02      # STREAMINFO MD5 off by one bit: every home of the gate must refuse
+assert check(wrong) == "error:InvalidChecksum" and check(wrong, md5_on_device=True) == "error:InvalidChecksum"
+assert check_device(wrong) == "error:InvalidChecksum" and check_device(wrong, md5_on_device=True) == "error:InvalidChecksum"
 s3 = fg.generate(fg.c3(2.0), want_pcm=False)          # 8 channels, order 32, 24-bit (MSB-align shift 8)
-assert check(s3.flac) == "fast"
+assert check(s3.flac) == "fast"                        # 3 bytes of every s32 enter the hash, shift undone (Q4)
+assert check(s3.flac, md5_on_device=True) == "fast"
 bad = s.flac.copy(); bad[bad.size // 2] ^= 0x10       # payload damage: chain or MD5 refuses -> plain path decides
 print("damaged:", check(bad), check_device(bad))
 cut = s.flac[: s.flac.size * 2 // 3].copy()           # truncated

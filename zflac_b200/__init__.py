@@ -21,7 +21,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _native
-from ._native import INPUT_ON_DEVICE, NO_CRC_ACCEL, NO_FAST_PATH, SKIP_FRAME_CRC16, SKIP_MD5, VERIFY_MD5  # noqa: F401
+from ._native import INPUT_ON_DEVICE, MD5_ON_DEVICE, NO_CRC_ACCEL, NO_FAST_PATH, SKIP_FRAME_CRC16, SKIP_MD5, VERIFY_MD5  # noqa: F401
 
 __all__ = ["decode", "decode_into", "decode_batch", "open_batch", "DeviceBatch", "pack_streams", "DecodedFLAC", "ZflacError",
            "CudaError", "open_device", "DeviceStream", "decode_frames", "metadata"]
@@ -98,12 +98,13 @@ FORMATS = {"native": 0, "f32": 1, "s24": 2, "u8": 3}  # zflacb200_format
 
 
 def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bool = True,
-           use_fast_path: bool = True) -> DecodedFLAC:
+           use_fast_path: bool = True, md5_on_device: bool = False) -> DecodedFLAC:
     """Drop-in for `zflac.decode(allocator, reader)`: `data` is bytes / ndarray / a readable object
     holding the whole stream. Raises the ZflacError subclass named like the Zig error."""
     lib = _native.load()
     arr = _as_u8(data)
     flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL) | (0 if use_fast_path else NO_FAST_PATH)
+    flags |= MD5_ON_DEVICE if md5_on_device else 0
     opt = _options(flags, device)
     handle = C.c_void_p()
     info = _native.Info()
@@ -145,12 +146,13 @@ def decode_frames(data, byte_offset: int = 0, *, device: int = -1, use_crc_links
 
 
 def decode_into(data, dst: np.ndarray, *, device: int = -1, verify_md5: bool = True, stream: int | None = None,
-                frame_crc16: bool = True) -> dict:
+                frame_crc16: bool = True, md5_on_device: bool = False) -> dict:
     """One-call variant (zflacb200_decode): decodes into a caller-owned buffer (pinned host memory
     makes both copies run at full PCIe speed). frame_crc16=False skips the per-frame CRC-16 diagnostic."""
     lib = _native.load()
     arr = _as_u8(data)
-    opt = _options((0 if verify_md5 else SKIP_MD5) | (0 if frame_crc16 else SKIP_FRAME_CRC16), device, stream)
+    opt = _options((0 if verify_md5 else SKIP_MD5) | (0 if frame_crc16 else SKIP_FRAME_CRC16) |
+                   (MD5_ON_DEVICE if md5_on_device else 0), device, stream)
     info = _native.Info()
     st = lib.zflacb200_decode(arr.ctypes.data, arr.size, C.byref(opt), dst.ctypes.data, dst.nbytes, C.byref(info))
     if st != 0:
@@ -311,12 +313,14 @@ class DeviceStream:
 
 
 def open_device(dev_ptr: int, nbytes: int, *, device: int = -1, stream: int | None = None, verify_md5: bool = True,
-                use_crc_links: bool = True, use_fast_path: bool = True, host_data=None, frame_crc16: bool = True) -> DeviceStream:
+                use_crc_links: bool = True, use_fast_path: bool = True, host_data=None, frame_crc16: bool = True,
+                md5_on_device: bool = False) -> DeviceStream:
     """Decode a stream that already sits in device memory (or, with host_data, upload it first)
     and keep the PCM on the device."""
     lib = _native.load()
     flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL) | (0 if use_fast_path else NO_FAST_PATH)
     flags |= 0 if frame_crc16 else SKIP_FRAME_CRC16
+    flags |= MD5_ON_DEVICE if md5_on_device else 0
     if host_data is not None:
         arr = _as_u8(host_data)
         ptr, n = arr.ctypes.data, arr.size

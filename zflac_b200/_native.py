@@ -15,6 +15,7 @@ SKIP_FRAME_CRC16 = 0x80
 INPUT_ON_DEVICE = 0x4
 NO_CRC_ACCEL = 0x8
 NO_FAST_PATH = 0x10
+MD5_ON_DEVICE = 0x100
 
 EXPORTS = [
     "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown",

@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -21,6 +22,7 @@
 
 #include "common.cuh"
 #include "devcache.cuh"
+#include "hostmd5.h"
 #include "kernels.cuh"
 
 using namespace zf;
@@ -47,6 +49,10 @@ struct DeviceCtx {
     // pinned staging for the small transfers of one call (xfer.cu): bump-allocated, rewound by the public entry points
     std::vector<std::pair<uint8_t *, size_t>> pin_blocks;
     size_t pin_used = 0;
+    // host-side MD5 gate of a device-resident stream (hostmd5.h): two pinned staging buffers the PCM passes through
+    static constexpr size_t kMd5Stage = 8u << 20;
+    uint8_t *md5_stage[2] = {nullptr, nullptr};
+    cudaEvent_t ev_md5[2] = {nullptr, nullptr};
 };
 DeviceCtx g_ctx[64];
 
@@ -124,12 +130,59 @@ const void *get_small(DeviceCtx &c, const void *d_src, size_t bytes, cudaStream_
     if (zf::launch_copy_small(slot, d_src, bytes, st) != cudaSuccess) return nullptr;
     return slot;
 }
+// ---- where one stream's MD5 chain runs (hostmd5.h): on a host thread unless the stream is short or the caller insists
+bool md5_on_host(uint32_t flags, uint64_t pcm_bytes) {
+    const char *e = getenv("ZFLACB200_HOST_MD5_MIN_BYTES");  // test knob, read on every call
+    const uint64_t min_bytes = e ? strtoull(e, nullptr, 0) : (256ull << 10);
+    return (flags & ZFLACB200_MD5_ON_DEVICE) == 0 && pcm_bytes >= min_bytes;
+}
+
 #define GET_SMALL(var, ctx, d_src, bytes, st)                                  \
     const void *var = get_small(ctx, d_src, bytes, st);                        \
     if (!var) {                                                                \
         g_last_error = "small device->host transfer failed (" #d_src ")";      \
         return ZFLACB200_CUDA_ERROR;                                           \
     }
+
+// MD5 of PCM that stays in HBM, on the calling host thread (hostmd5.h): the bytes pass through two pinned staging
+// buffers, the copy of piece i + 1 running under the hash of piece i. Everything queued on `st` so far is waited for.
+int host_md5_of_device_pcm(DeviceCtx &ctx, const void *d_pcm, uint64_t n_samples, uint32_t cb, uint32_t hb, uint32_t unshift,
+                           cudaStream_t st, uint8_t out[16], float *ms_host) {
+    for (int k = 0; k < 2; ++k) {
+        if (!ctx.md5_stage[k]) CU_CHECK(cudaHostAlloc((void **)&ctx.md5_stage[k], DeviceCtx::kMd5Stage, cudaHostAllocDefault));
+        if (!ctx.ev_md5[k]) CU_CHECK(cudaEventCreateWithFlags(&ctx.ev_md5[k], cudaEventDisableTiming));
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    CU_CHECK(cudaEventRecord(ctx.ev_fork, st));
+    CU_CHECK(cudaStreamWaitEvent(ctx.copy_out, ctx.ev_fork, 0));
+    zf::PcmHasher h;
+    h.container_bytes = cb;
+    h.hash_bytes = hb;
+    h.unshift = unshift;
+    const uint64_t per = DeviceCtx::kMd5Stage / cb;
+    uint64_t queued = 0, done = 0, cnt[2] = {0, 0};
+    auto queue = [&](int slot) -> int {
+        const uint64_t m = std::min<uint64_t>(per, n_samples - queued);
+        CU_CHECK(cudaMemcpyAsync(ctx.md5_stage[slot], (const uint8_t *)d_pcm + queued * cb, m * cb, cudaMemcpyDeviceToHost, ctx.copy_out));
+        CU_CHECK(cudaEventRecord(ctx.ev_md5[slot], ctx.copy_out));
+        cnt[slot] = m;
+        queued += m;
+        return ZFLACB200_OK;
+    };
+    int cur = 0;
+    if (n_samples && queue(0) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    while (done < n_samples) {
+        if (queued < n_samples && queue(cur ^ 1) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+        CU_CHECK(cudaEventSynchronize(ctx.ev_md5[cur]));
+        h.update(ctx.md5_stage[cur], cnt[cur]);
+        done += cnt[cur];
+        cur ^= 1;
+    }
+    if (n_samples == 0) CU_CHECK(cudaStreamSynchronize(st));
+    h.finish(out);
+    if (ms_host) *ms_host = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return ZFLACB200_OK;
+}
 
 // Host-side phase timer: ZFLACB200_TRACE=1 prints where the HOST spends its time inside a call (stderr).
 struct HostTrace {
@@ -627,6 +680,7 @@ struct FastGroup {
     std::vector<uint8_t> digests;         // 16 bytes per stream
     DevBuf b_pcm, b_recs, b_outs, b_ok;
     float ms_hint = 0, ms_decode = 0, ms_epilogue = 0, ms_md5 = 0;
+    bool md5_host = false;  // ms_md5 is host time (hostmd5.h), not part of the event span e[0]..e[7]
 
     void plan() {  // output and scratch slots from the STREAMINFO totals (host-known)
         pcm_elems = scratch_elems = 0;
@@ -725,6 +779,35 @@ int run_fast_group(FastGroup &g, Events &ev) {
                 ep.msb_shift = 0;
                 if (stage.epilogue(ep, d_outs, max_channels, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
             }
+        }
+        if (ns == 1 && md5_on_host(g.flags, g.streams[0].total * g.streams[0].si_channels * g.container_bytes)) {
+            // one long stream: the chain runs on the host (hostmd5.h); the verdict of the device-side chain check is
+            // read first so that a refused stream does not pay for a hash nobody will look at
+            const StreamDesc &sd = g.streams[0];
+            CU_CHECK(cudaEventRecord(ev.e[7], st));
+            if (frame_crc) CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));  // its counters land in the same summary
+            GET_SMALL(h_sums0, ctx, b_sum.p, sizeof(StreamSummary), st);
+            CU_CHECK(cudaStreamSynchronize(st));
+            g.sums.resize(1);
+            memcpy(g.sums.data(), h_sums0, sizeof(StreamSummary));
+            float ms_host = 0;
+            if (g.accepted(0)) {
+                const int r = host_md5_of_device_pcm(ctx, (const uint8_t *)g.b_pcm.p + sd.pcm_base * g.container_bytes,
+                                                     sd.total * sd.si_channels, g.container_bytes, g.hash_bytes[0],
+                                                     lossy ? 0 : g.msb_shift, st, g.digests.data(), &ms_host);
+                if (r != ZFLACB200_OK) return r;
+                if (lossy) {
+                    CU_CHECK(launch_shift_inplace(g.b_pcm.p, g.pcm_elems, g.container_bytes, g.msb_shift, st));
+                    CU_CHECK(cudaStreamSynchronize(st));
+                }
+            }
+            tr.mark("host_md5");
+            g.ms_hint = ev_ms(ev.e[2], ev.e[3]);
+            g.ms_decode = ev_ms(ev.e[4], ev.e[5]);
+            g.ms_epilogue = ev_ms(ev.e[5], ev.e[6]);
+            g.ms_md5 = ms_host;
+            g.md5_host = true;
+            return ZFLACB200_OK;
         }
         std::vector<Md5Job> jobs(ns);
         for (uint32_t i = 0; i < ns; ++i) {
@@ -896,7 +979,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
             info->ms_decode = g.ms_decode;
             info->ms_epilogue = g.ms_epilogue;
             info->ms_md5 = g.ms_md5;
-            info->ms_total = ev_ms(ev.e[0], ev.e[7]);
+            info->ms_total = ev_ms(ev.e[0], ev.e[7]) + (g.md5_host ? g.ms_md5 : 0.f);
             info->md5_checked = do_md5 ? 1 : 0;
             memcpy(info->md5_computed, g.digests.data(), 16);
             if (do_md5 && memcmp(info->md5_computed, pl.si.md5, 16) != 0) return ZFLACB200_INVALID_CHECKSUM;  // :279-280
@@ -1048,6 +1131,8 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
 
     // ---- K4: MD5 gate
     uint32_t lossy = 0;
+    bool md5_host = false;
+    float ms_md5_host = 0;
     if (do_md5) {
         if (msb_shift) {
             CU_CHECK(cudaMemcpyAsync(&lossy, b_flag.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -1057,27 +1142,37 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
                 if (stage.epilogue(ep, (const FrameOut *)b_outs.p, chain.channels, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
             }
         }
-        Md5Job job;
-        job.pcm = b_pcm.p;
-        job.n_samples = chain.n_samples;
-        job.container_bytes = container_bytes;
-        job.hash_bytes = aligned == 24 ? 3 : container_bytes;  // :268-277
-        job.unshift = lossy ? 0 : msb_shift;
-        job.pad = 0;
-        CU_CHECK(cudaMemcpyAsync(b_jobs.p, &job, sizeof(job), cudaMemcpyHostToDevice, st));
-        CU_CHECK(launch_md5((const Md5Job *)b_jobs.p, 1, (uint8_t *)b_digest.p, st));
-        if (lossy) CU_CHECK(launch_shift_inplace(b_pcm.p, chain.n_samples, container_bytes, msb_shift, st));
-        CU_CHECK(cudaMemcpyAsync(info->md5_computed, b_digest.p, 16, cudaMemcpyDeviceToHost, st));
+        if (md5_on_host(flags, pcm_bytes)) {  // one long stream: the chain runs on the host (hostmd5.h)
+            CU_CHECK(cudaEventRecord(ev.e[7], st));
+            const int r = host_md5_of_device_pcm(g_ctx[device], b_pcm.p, chain.n_samples, container_bytes,
+                                                 aligned == 24 ? 3 : container_bytes, lossy ? 0 : msb_shift, st, info->md5_computed,
+                                                 &ms_md5_host);
+            if (r != ZFLACB200_OK) return r;
+            md5_host = true;
+            if (lossy) CU_CHECK(launch_shift_inplace(b_pcm.p, chain.n_samples, container_bytes, msb_shift, st));
+        } else {
+            Md5Job job;
+            job.pcm = b_pcm.p;
+            job.n_samples = chain.n_samples;
+            job.container_bytes = container_bytes;
+            job.hash_bytes = aligned == 24 ? 3 : container_bytes;  // :268-277
+            job.unshift = lossy ? 0 : msb_shift;
+            job.pad = 0;
+            CU_CHECK(cudaMemcpyAsync(b_jobs.p, &job, sizeof(job), cudaMemcpyHostToDevice, st));
+            CU_CHECK(launch_md5((const Md5Job *)b_jobs.p, 1, (uint8_t *)b_digest.p, st));
+            if (lossy) CU_CHECK(launch_shift_inplace(b_pcm.p, chain.n_samples, container_bytes, msb_shift, st));
+            CU_CHECK(cudaMemcpyAsync(info->md5_computed, b_digest.p, 16, cudaMemcpyDeviceToHost, st));
+        }
     }
-    CU_CHECK(cudaEventRecord(ev.e[7], st));
+    if (!md5_host) CU_CHECK(cudaEventRecord(ev.e[7], st));
     CU_CHECK(cudaStreamSynchronize(st));
 
     info->ms_scan = ev_ms(ev.e[1], ev.e[2]);
     info->ms_link = ev_ms(ev.e[2], ev.e[3]);
     info->ms_decode = ev_ms(ev.e[4], ev.e[5]);
     info->ms_epilogue = ev_ms(ev.e[5], ev.e[6]);
-    info->ms_md5 = ev_ms(ev.e[6], ev.e[7]);
-    info->ms_total = ev_ms(ev.e[0], ev.e[7]);
+    info->ms_md5 = md5_host ? ms_md5_host : ev_ms(ev.e[6], ev.e[7]);
+    info->ms_total = ev_ms(ev.e[0], ev.e[7]) + (md5_host ? ms_md5_host : 0.f);
     info->md5_checked = do_md5 ? 1 : 0;
     if (do_md5 && memcmp(info->md5_computed, pl.si.md5, 16) != 0) return ZFLACB200_INVALID_CHECKSUM;  // :279-280
 
@@ -1484,9 +1579,14 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     sd.si_sample_rate = si.sample_rate;
     sd.si_channels = (uint8_t)C;
     sd.si_depth = (uint8_t)depth;
-    EventList ev_in, ev_hint, ev_mid, ev_done;
+    EventList ev_in, ev_hint, ev_mid, ev_done, ev_out;
     Events ev;
-    if (ev_in.make(K) || ev_hint.make(K) || ev_mid.make(K) || ev_done.make(K) || ev.init()) return ZFLACB200_CUDA_ERROR;
+    if (ev_in.make(K) || ev_hint.make(K) || ev_mid.make(K) || ev_done.make(K) || ev_out.make(K + 1) || ev.init()) return ZFLACB200_CUDA_ERROR;
+    // the MD5 gate of a host-output decode runs on a host thread over the PCM pieces as they land in `dst` (hostmd5.h)
+    std::unique_ptr<zf::HashWorker> hasher;
+    if (do_md5 && !on_device && md5_on_host(flags, pcm_bytes))
+        hasher.reset(new zf::HashWorker(device, cb, aligned == 24 ? 3 : cb, msb_shift));
+    uint32_t n_out = 0;
     CU_CHECK(put_small(ctx, b_sd.p, &sd, sizeof(sd), st));
     CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary), st));
     CU_CHECK(cudaMemsetAsync(b_ok.p, 2, cap, st));
@@ -1522,6 +1622,11 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
         CU_CHECK(cudaStreamWaitEvent(ctx.copy_out, ev_done.v[chunk_i], 0));
         CU_CHECK(cudaMemcpyAsync((uint8_t *)dst + copied * cb, (const uint8_t *)b_pcm.p + copied * cb, (upto - copied) * cb,
                                  cudaMemcpyDeviceToHost, ctx.copy_out));
+        if (hasher && n_out < ev_out.v.size()) {
+            CU_CHECK(cudaEventRecord(ev_out.v[n_out], ctx.copy_out));
+            hasher->push(ev_out.v[n_out], (const uint8_t *)dst + copied * cb, upto - copied);
+            ++n_out;
+        }
         copied = upto;
         return ZFLACB200_OK;
     };
@@ -1601,7 +1706,22 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     info->audio_offset = audio_offset;
     info->container_bytes = (uint8_t)cb;
     int result = ZFLACB200_OK;
-    if (accepted && do_md5) {  // K4 over the device copy while the last PCM chunk is still on its way out
+    if (accepted && do_md5 && hasher) {
+        const auto t0 = std::chrono::steady_clock::now();
+        const bool ok = hasher->finish(info->md5_computed) && copied == n_elems;
+        info->ms_md5 = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();  // the tail the copies did not hide
+        if (!ok) {
+            g_last_error = "host MD5 worker failed";
+            return ZFLACB200_CUDA_ERROR;
+        }
+        info->md5_checked = 1;
+        if (memcmp(info->md5_computed, si.md5, 16) != 0) result = ZFLACB200_INVALID_CHECKSUM;  // :279-280
+    } else if (accepted && do_md5 && md5_on_host(flags, pcm_bytes)) {  // device form: PCM stays in HBM, staged through pinned buffers
+        const int r = host_md5_of_device_pcm(ctx, b_pcm.p, n_elems, cb, aligned == 24 ? 3 : cb, msb_shift, st, info->md5_computed, &info->ms_md5);
+        if (r != ZFLACB200_OK) return r;
+        info->md5_checked = 1;
+        if (memcmp(info->md5_computed, si.md5, 16) != 0) result = ZFLACB200_INVALID_CHECKSUM;  // :279-280
+    } else if (accepted && do_md5) {  // K4 over the device copy while the last PCM chunk is still on its way out
         Md5Job job;
         job.pcm = b_pcm.p;
         job.n_samples = n_elems;
