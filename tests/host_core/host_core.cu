@@ -7,6 +7,7 @@
 
 #include "../../zflac_b200/csrc/decode_core.cuh"
 #include "../../zflac_b200/csrc/parse_core.cuh"
+#include "../../zflac_b200/csrc/parse_narrow.cuh"
 
 namespace {
 
@@ -45,6 +46,43 @@ struct HostSrc {
     // raw order here = byte-reversed, like the little-endian shared-memory word of the device ring
     __host__ __device__ void note_rollback() { ++rollbacks; }
     static __host__ __device__ uint32_t fix(uint32_t raw) { return __builtin_bswap32(raw); }
+};
+
+// Host stand-in for PairSrc (ring_src.cuh): entry j = {word j - 1, word j}, MSB-first, over plain memory, with the
+// device ring's residency rules mimicked so that an unchecked entry read outside the guarantee is caught here.
+struct HostPairSrc {
+    const uint8_t *g;
+    uint64_t avail;
+    uint32_t guaranteed_lo, guaranteed_hi;  // entries [lo, hi) may be read unchecked (set by top_up)
+    uint32_t ensured;                       // the one entry ensure() made resident
+    int violations;
+    uint32_t word_be(uint32_t w) const {
+        uint32_t v = 0;
+        for (int i = 0; i < 4; ++i) {
+            const uint64_t off = (uint64_t)w * 4 + i;
+            v = (v << 8) | (off < avail ? g[off] : 0u);
+        }
+        return v;
+    }
+    uint2 make(uint32_t j) const { return make_uint2(j ? word_be(j - 1) : 0u, word_be(j)); }
+    uint2 entry(uint32_t j) {
+        if (j != ensured && !(j >= guaranteed_lo && j < guaranteed_hi)) ++violations;
+        return make(j);
+    }
+    int speculative = 0;  // unchecked reads outside the guarantee inside the current body: they count if it is accepted
+    uint2 entry_at(uint32_t Q) {
+        const uint32_t j = (31u - Q) >> 5;
+        if (!(j >= guaranteed_lo && j < guaranteed_hi)) ++speculative;
+        return make(j);
+    }
+    void body_done(bool ok) {
+        if (ok) violations += speculative;
+        speculative = 0;
+    }
+    void ensure(uint32_t j) { ensured = j; guaranteed_lo = guaranteed_hi = 0; }
+    void top_up(uint32_t j0, uint32_t) { guaranteed_lo = j0; guaranteed_hi = j0 + zf::kFastEntries; ensured = 0xFFFFFFFFu; }
+    // cursor of one body ago: the device keeps [j_old, j_old + 8 + kFastEntries) resident
+    void top_up_stale(uint32_t j_old) { guaranteed_lo = j_old; guaranteed_hi = j_old + 8 + zf::kFastEntries; ensured = 0xFFFFFFFFu; }
 };
 
 }  // namespace
@@ -94,6 +132,29 @@ int zf_host_parse_frame(const uint8_t *stream, const zf::FrameRec *fr, int32_t *
     if (g_rollbacks) *g_rollbacks += br.src.rollbacks;
     return br.src.violations;
 }
+
+// Narrow pass A (parse_narrow.cuh) on the host: folded 16-bit residuals into `scratch` (uint16, sub_idx() layout).
+// Returns the unchecked-read violations (must be 0); *overflow != 0 when a value did not fit 16 bits.
+int zf_host_parse_frame_narrow(const uint8_t *stream, const zf::FrameRec *fr, uint16_t *scratch, zf::SubRec *subs, int write_samples,
+                               zf::FrameOut *out, uint32_t *overflow) {
+    const uint64_t start = fr->offset + fr->header_len;
+    const uint64_t origin = start & ~15ull;  // the device source starts at a 16-byte aligned address
+    const uint64_t bytes = fr->stream_end > origin ? fr->stream_end - origin : 0;
+    zf::PosReader<HostPairSrc> br;
+    br.src.g = stream + origin;
+    br.src.avail = bytes;
+    br.src.guaranteed_lo = br.src.guaranteed_hi = 0;
+    br.src.ensured = 0xFFFFFFFFu;
+    br.src.violations = 0;
+    br.init_at((uint32_t)(start - origin));
+    uint32_t max_order = 0;
+    *overflow = 0;
+    zf::parse_frame_narrow(br, *fr, scratch, subs, bytes * 8, write_samples != 0, origin, *out, max_order, *overflow);
+    return br.src.violations;
+}
+
+// the unfold pass B applies to a narrow scratch value
+int32_t zf_host_unfold(uint32_t cw) { return zf::zigzag(cw); }
 
 // Scalar restatement of what pass B (predict.cu) does to one scratch plane: predictor recurrence in
 // place, then the wasted-bits shift. Test-side stand-in for the CUDA kernel (the -m gpu tests pin the kernel).

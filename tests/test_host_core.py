@@ -21,8 +21,8 @@ import synth_cases
 HERE = os.path.join(ROOT, "tests", "host_core")
 LIB = os.path.join(HERE, "_build", "libzf_host_core.so")
 SRC = os.path.join(HERE, "host_core.cu")
-DEPS = [SRC, os.path.join(ROOT, "zflac_b200", "csrc", "decode_core.cuh"), os.path.join(ROOT, "zflac_b200", "csrc", "parse_core.cuh"),
-        os.path.join(ROOT, "zflac_b200", "csrc", "common.cuh")]
+DEPS = [SRC] + [os.path.join(ROOT, "zflac_b200", "csrc", f) for f in
+                ("decode_core.cuh", "parse_core.cuh", "common.cuh", "pos_reader.cuh", "parse_narrow.cuh")]
 
 FRAME_REC = np.dtype([("offset", "<u8"), ("stream_end", "<u8"), ("sample_base", "<u8"), ("scratch_base", "<u8"),
                       ("block_size", "<u4"), ("scratch_pitch", "<u4"), ("header_len", "u1"), ("ch_code", "u1"),
@@ -47,12 +47,16 @@ def core():
     lib.zf_host_predict_plane.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
     lib.zf_host_predict_plane.restype = None
     assert lib.zf_host_subrec_size() == 80
+    lib.zf_host_parse_frame_narrow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    lib.zf_host_parse_frame_narrow.restype = C.c_int
     return lib
 
 
-def host_decode(lib, data: bytes, ref, two_pass: bool = False):
+def host_decode(lib, data: bytes, ref, two_pass: bool = False, narrow: bool = False, stats=None):
     """Decode all frames of the oracle's frame trace with the host core; return interleaved PCM like the reference's.
-    two_pass: pass A (parse_core.cuh) + a scalar restatement of pass B instead of the single-pass decoder."""
+    two_pass: pass A (parse_core.cuh) + a scalar restatement of pass B instead of the single-pass decoder.
+    narrow: pass A is parse_narrow.cuh (PosReader, folded 16-bit scratch); a frame that reports overflow is redone with
+    parse_core.cuh, the way the host library falls back (stats["overflow_frames"] counts them)."""
     arr = np.frombuffer(data, dtype=np.uint8)
     ch, bps = ref.channels, ref.bits_per_sample
     wide = bps == 32
@@ -72,7 +76,22 @@ def host_decode(lib, data: bytes, ref, two_pass: bool = False):
         if two_pass:
             assert not wide
             subs = np.zeros(8 * 80, dtype=np.uint8)
-            viol = lib.zf_host_parse_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, subs.ctypes.data, 1, out.ctypes.data)
+            done = False
+            if narrow:
+                s16 = np.zeros((bs + 15) // 16 * 16 * ch, dtype=np.uint16)  # sub_idx16() layout: groups of 16 steps x channels x 16
+                ovf = np.zeros(1, dtype=np.uint32)
+                viol = lib.zf_host_parse_frame_narrow(arr.ctypes.data, rec.ctypes.data, s16.ctypes.data, subs.ctypes.data, 1,
+                                                      out.ctypes.data, ovf.ctypes.data)
+                assert viol == 0, "unchecked ring entry read outside the top_up guarantee"
+                if int(ovf[0]) == 0:
+                    val = s16.view(np.int16).astype(np.int32).reshape(-1, ch, 16)
+                    planes16 = val.transpose(1, 0, 2).reshape(ch, -1)[:, :pitch]   # [channel][time step]
+                    scratch = planes16.reshape(ch, pitch // 8, 8).transpose(1, 0, 2).reshape(-1).copy()  # the int32 sub_idx() layout
+                    done = True
+                elif stats is not None:
+                    stats["overflow_frames"] = stats.get("overflow_frames", 0) + 1
+            if not done:
+                viol = lib.zf_host_parse_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, subs.ctypes.data, 1, out.ctypes.data)
             if int(out["status"][0]) == 0:
                 planar = np.zeros(pitch * ch, dtype=np.int32)
                 for c in range(ch):
@@ -149,4 +168,34 @@ def test_host_core_synth(core, name):
     ref = oracle.decode(data, trace_frames=True)
     assert ref.error == "OK"
     got = host_decode(core, data, ref)
+    assert np.array_equal(got, ref.samples)
+
+
+@pytest.mark.parametrize("entry", [e for e in corpus_entries() if not e["expect_error"]],
+                         ids=[i for i, e in zip(corpus_ids(), corpus_entries()) if not e["expect_error"]])
+def test_host_parse_narrow_corpus(core, entry):
+    """Narrow pass A (parse_narrow.cuh: PosReader, float-exponent unary count, folded 16-bit scratch) + the recurrence ==
+    the oracle, frame ends included. Streams deeper than 16 bits run too: frames whose values do not fit report overflow."""
+    data = corpus_bytes(entry)
+    ref = oracle.decode(data, trace_frames=True)
+    if ref.error != "OK":
+        pytest.skip(f"oracle: {ref.error}")
+    if ref.bits_per_sample == 32:
+        pytest.skip("32 bps streams stay on the single-pass int64 decoder")
+    stats = {}
+    got = host_decode(core, data, ref, two_pass=True, narrow=True, stats=stats)
+    assert np.array_equal(got, ref.samples)
+    if ref.bits_per_sample <= 16 and entry["id"] not in ("61",):  # 61: "predictor overflow check", full-scale residuals
+        assert stats.get("overflow_frames", 0) == 0
+
+
+@pytest.mark.parametrize("name", sorted(synth_cases.CASES))
+def test_host_parse_narrow_synth(core, name):
+    s = synth_cases.make(name)
+    data = s.flac.tobytes()
+    ref = oracle.decode(data, trace_frames=True)
+    assert ref.error == "OK"
+    if ref.bits_per_sample == 32:
+        pytest.skip("32 bps streams stay on the single-pass int64 decoder")
+    got = host_decode(core, data, ref, two_pass=True, narrow=True)
     assert np.array_equal(got, ref.samples)

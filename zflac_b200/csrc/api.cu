@@ -594,6 +594,10 @@ struct DevBuf {  // stream-ordered allocation released on scope exit
     void *p = nullptr;
     cudaStream_t st = nullptr;
     int alloc(size_t bytes, cudaStream_t s) {
+        if (p) {
+            dev_free(p, st ? st : s);
+            p = nullptr;
+        }
         st = s;
         CU_CHECK(dev_alloc(&p, bytes ? bytes : 16, s));
         return ZFLACB200_OK;
@@ -614,21 +618,29 @@ struct DevBuf {  // stream-ordered allocation released on scope exit
 // scratch) and ZFLACB200_SINGLE_PASS run the fused single-pass K2 + K3.
 struct SubframeStage {
     bool two_pass = false;
-    DevBuf b_subs, b_big;
-    int prepare(bool wide, uint32_t flags, uint32_t n_recs, cudaStream_t st) {
+    bool narrow = false;  // uint16 scratch of folded residuals (parse_narrow.cuh): streams of <= 16 bits per sample
+    DevBuf b_subs, b_big;  // b_big: {some order above 12, a value did not fit the narrow scratch}
+    // depth: bits per sample by STREAMINFO (largest of a batch group); 0 or allow_narrow = false keeps the int32 scratch
+    int prepare(bool wide, uint32_t flags, uint32_t n_recs, cudaStream_t st, uint32_t depth = 0, bool allow_narrow = true) {
         two_pass = !wide && (flags & ZFLACB200_SINGLE_PASS) == 0;
+        narrow = false;
         if (!two_pass) return ZFLACB200_OK;
-        if (b_subs.p) { dev_free(b_subs.p, st); b_subs.p = nullptr; }
-        if (b_big.p) { dev_free(b_big.p, st); b_big.p = nullptr; }
-        if (b_subs.alloc(kSubRecBytes * 8 * (size_t)std::max<uint32_t>(n_recs, 1), st) || b_big.alloc(sizeof(uint32_t), st))
+        static const bool env_no_narrow = getenv("ZFLACB200_NO_NARROW") != nullptr;  // diagnostics: A/B runs
+        narrow = allow_narrow && !env_no_narrow && depth >= 1 && depth <= 16;
+        if (b_subs.alloc(kSubRecBytes * 8 * (size_t)std::max<uint32_t>(n_recs, 1), st) || b_big.alloc(2 * sizeof(uint32_t), st))
             return ZFLACB200_CUDA_ERROR;
-        CU_CHECK(cudaMemsetAsync(b_big.p, 0, sizeof(uint32_t), st));
+        CU_CHECK(cudaMemsetAsync(b_big.p, 0, 2 * sizeof(uint32_t), st));
         return ZFLACB200_OK;
     }
+    const uint32_t *overflow_flag() const { return (const uint32_t *)b_big.p + 1; }
     // d_recs / d_outs point at record `first` of the prepared range (chunked decode), n records from there
     int decode(const uint8_t *d_stream, const FrameRec *d_recs, uint32_t n, void *d_scratch, bool wide, FrameOut *d_outs, bool write,
                cudaStream_t st, uint32_t first = 0) {
-        if (two_pass)
+        if (two_pass && narrow)
+            CU_CHECK(launch_parse_frames_narrow(d_stream, d_recs, n, (uint16_t *)d_scratch,
+                                                (SubRec *)((uint8_t *)b_subs.p + kSubRecBytes * 8 * (size_t)first), d_outs,
+                                                (uint32_t *)b_big.p, write, st));
+        else if (two_pass)
             CU_CHECK(launch_parse_frames(d_stream, d_recs, n, (int32_t *)d_scratch,
                                          (SubRec *)((uint8_t *)b_subs.p + kSubRecBytes * 8 * (size_t)first), d_outs, (uint32_t *)b_big.p,
                                          write, st));
@@ -653,6 +665,7 @@ struct SubframeStage {
         pp.msb_shift = ep.msb_shift;
         pp.lossy_flag = ep.lossy_flag;
         pp.big_orders = (const uint32_t *)b_big.p;
+        pp.narrow = narrow;
         CU_CHECK(launch_predict_epilogue(pp, st));
         return ZFLACB200_OK;
     }
@@ -681,6 +694,7 @@ struct FastGroup {
     DevBuf b_pcm, b_recs, b_outs, b_ok;
     float ms_hint = 0, ms_decode = 0, ms_epilogue = 0, ms_md5 = 0;
     bool md5_host = false;  // ms_md5 is host time (hostmd5.h), not part of the event span e[0]..e[7]
+    bool allow_narrow = true, narrow_overflow = false;  // uint16 scratch (parse_narrow.cuh) and its escape hatch
 
     void plan() {  // output and scratch slots from the STREAMINFO totals (host-known)
         pcm_elems = scratch_elems = 0;
@@ -704,7 +718,17 @@ struct FastGroup {
 // the chain rules verified on the device from the decoded frame ends, the per-frame CRC-16 on a side
 // stream, K4 per stream. One host synchronisation at the very end (two when an MSB-aligned stream
 // is hashed). Returns a CUDA-level status; per-stream acceptance is g.accepted(i).
+int run_fast_group_once(FastGroup &g, Events &ev);
 int run_fast_group(FastGroup &g, Events &ev) {
+    int r = run_fast_group_once(g, ev);
+    if (r == ZFLACB200_OK && g.narrow_overflow) {  // a residual beyond 16 bits: once more on the int32 scratch
+        g.allow_narrow = false;
+        g.narrow_overflow = false;
+        r = run_fast_group_once(g, ev);
+    }
+    return r;
+}
+int run_fast_group_once(FastGroup &g, Events &ev) {
     cudaStream_t st = g.st;
     DeviceCtx &ctx = g_ctx[g.device];
     const uint32_t n = g.n_cand;
@@ -716,9 +740,12 @@ int run_fast_group(FastGroup &g, Events &ev) {
 
     DevBuf b_sd, b_scratch, b_sum, b_flag, b_jobs, b_digest;
     SubframeStage stage;
-    if (stage.prepare(g.wide, g.flags, n, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
-    uint32_t max_channels = 1;
-    for (const auto &sd : g.streams) max_channels = std::max<uint32_t>(max_channels, sd.si_channels);
+    uint32_t max_channels = 1, max_depth = 0;
+    for (const auto &sd : g.streams) {
+        max_channels = std::max<uint32_t>(max_channels, sd.si_channels);
+        max_depth = std::max<uint32_t>(max_depth, sd.si_depth);
+    }
+    if (stage.prepare(g.wide, g.flags, n, st, max_depth, g.allow_narrow) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
     if (b_sd.alloc(sizeof(StreamDesc) * ns, st) || g.b_recs.alloc(sizeof(FrameRec) * (size_t)n, st) ||
         g.b_outs.alloc(sizeof(FrameOut) * (size_t)n, st) || b_scratch.alloc(g.scratch_elems * (g.wide ? 8 : 4), st) ||
         g.b_pcm.alloc(g.pcm_elems * g.container_bytes + 64, st) || b_sum.alloc(sizeof(StreamSummary) * ns, st) ||
@@ -787,9 +814,14 @@ int run_fast_group(FastGroup &g, Events &ev) {
             CU_CHECK(cudaEventRecord(ev.e[7], st));
             if (frame_crc) CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));  // its counters land in the same summary
             GET_SMALL(h_sums0, ctx, b_sum.p, sizeof(StreamSummary), st);
+            GET_SMALL(h_ovf0, ctx, stage.two_pass ? (const void *)stage.overflow_flag() : b_flag.p, sizeof(uint32_t), st);
             CU_CHECK(cudaStreamSynchronize(st));
             g.sums.resize(1);
             memcpy(g.sums.data(), h_sums0, sizeof(StreamSummary));
+            if (stage.narrow && *(const uint32_t *)h_ovf0) {
+                g.narrow_overflow = true;
+                return ZFLACB200_OK;
+            }
             float ms_host = 0;
             if (g.accepted(0)) {
                 const int r = host_md5_of_device_pcm(ctx, (const uint8_t *)g.b_pcm.p + sd.pcm_base * g.container_bytes,
@@ -832,8 +864,10 @@ int run_fast_group(FastGroup &g, Events &ev) {
     if (frame_crc) CU_CHECK(cudaStreamWaitEvent(st, ctx.ev_join, 0));
     g.sums.resize(ns);
     GET_SMALL(h_sums, ctx, b_sum.p, sizeof(StreamSummary) * ns, st);
+    GET_SMALL(h_ovf, ctx, stage.two_pass ? (const void *)stage.overflow_flag() : b_flag.p, sizeof(uint32_t), st);
     tr.mark("md5_setup");
     CU_CHECK(cudaStreamSynchronize(st));
+    if (stage.narrow && *(const uint32_t *)h_ovf) g.narrow_overflow = true;
     if (h_digests) memcpy(g.digests.data(), h_digests, 16 * (size_t)ns);
     memcpy(g.sums.data(), h_sums, sizeof(StreamSummary) * ns);
     tr.mark("final_sync");
@@ -1057,6 +1091,7 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     std::vector<FrameOut> outs;
     int final_status = ZFLACB200_OK;
     bool decoded_ok = false;
+    bool allow_narrow = true;
     for (int round = 0; round < 64 && !decoded_ok; ++round) {
         if (round == 63) pl.use_links = false;  // give up on links: probe everything (always consistent)
         {
@@ -1073,7 +1108,9 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
         if (b_frames.alloc(sizeof(FrameRec) * std::max<uint32_t>(nf, 1), st) || b_outs.alloc(sizeof(FrameOut) * std::max<uint32_t>(nf, 1), st))
             return ZFLACB200_CUDA_ERROR;
         if (write && b_scratch.alloc(chain.scratch_elems * (pl.wide ? 8 : 4), st)) return ZFLACB200_CUDA_ERROR;
-        if (stage.prepare(pl.wide, write ? flags : (flags | ZFLACB200_SINGLE_PASS), nf, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+        if (stage.prepare(pl.wide, write ? flags : (flags | ZFLACB200_SINGLE_PASS), nf, st, depth, allow_narrow) != ZFLACB200_OK)
+            return ZFLACB200_CUDA_ERROR;
+        uint32_t narrow_overflow = 0;
         outs.resize(nf);
         if (nf) {
             CU_CHECK(cudaMemcpyAsync(b_frames.p, recs.data(), sizeof(FrameRec) * nf, cudaMemcpyHostToDevice, st));
@@ -1083,10 +1120,15 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
                 return ZFLACB200_CUDA_ERROR;
             CU_CHECK(cudaEventRecord(ev.e[5], st));
             CU_CHECK(cudaMemcpyAsync(outs.data(), b_outs.p, sizeof(FrameOut) * nf, cudaMemcpyDeviceToHost, st));
+            if (stage.narrow) CU_CHECK(cudaMemcpyAsync(&narrow_overflow, stage.overflow_flag(), sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
             CU_CHECK(cudaStreamSynchronize(st));
         } else {
             CU_CHECK(cudaEventRecord(ev.e[4], st));
             CU_CHECK(cudaEventRecord(ev.e[5], st));
+        }
+        if (narrow_overflow) {  // a residual beyond 16 bits: once more on the int32 scratch
+            allow_narrow = false;
+            continue;
         }
         decoded_ok = true;
         for (uint32_t i = 0; i < nf; ++i) {
@@ -1182,7 +1224,8 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
     info->n_samples = chain.n_samples;
     info->pcm_bytes = pcm_bytes;
     info->n_frames = nf;
-    info->n_probed_frames = chain.n_probed;
+    info->n_probed_frames = 0;  // frames whose end came from decoding them, in whichever round of the loop above
+    for (const auto &cf : chain.frames) info->n_probed_frames += cf.probed ? 1 : 0;
     info->audio_bytes = nf ? chain.frames.back().expect_end - pl.audio_offset : 0;
 
     zflacb200_stream *h = new zflacb200_stream();
@@ -1568,7 +1611,7 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
         b_outs.alloc(sizeof(FrameOut) * (size_t)cap, st) || b_ok.alloc(cap, st) || b_scratch.alloc(scratch_elems * (wide ? 8 : 4), st) ||
         b_pcm.alloc(((n_elems + 15) & ~15ull) * cb + 64, st) || b_sum.alloc(sizeof(StreamSummary), st) ||
         b_flag.alloc(sizeof(uint32_t), st) || b_hi.alloc(sizeof(unsigned long long) * K, st) || b_jobs.alloc(sizeof(Md5Job), st) ||
-        b_digest.alloc(16, st) || stage.prepare(wide, flags, cap, st) != ZFLACB200_OK)
+        b_digest.alloc(16, st) || stage.prepare(wide, flags, cap, st, depth) != ZFLACB200_OK)
         return ZFLACB200_CUDA_ERROR;
     StreamDesc sd;
     memset(&sd, 0, sizeof(sd));
@@ -1691,11 +1734,13 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
         CU_CHECK(launch_verify_chain(d_cands, n, (const StreamDesc *)b_sd.p, 1, d_recs, d_outs, d_sum, window, st));
         GET_SMALL(h_sum, ctx, b_sum.p, sizeof(sum), st);
         GET_SMALL(h_lossy, ctx, b_flag.p, sizeof(lossy), st);
+        GET_SMALL(h_ovf, ctx, stage.two_pass ? (const void *)stage.overflow_flag() : b_flag.p, sizeof(uint32_t), st);
         CU_CHECK(cudaEventRecord(ev.e[7], st));
         if (copy_out(K - 1, n_elems) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
         CU_CHECK(cudaStreamSynchronize(st));
         memcpy(&sum, h_sum, sizeof(sum));
         lossy = *(const uint32_t *)h_lossy;
+        if (stage.narrow && *(const uint32_t *)h_ovf) bail = true;  // a residual beyond 16 bits: the plain path redoes it on the int32 scratch
     } else {
         CU_CHECK(cudaStreamSynchronize(st));
     }
@@ -1934,7 +1979,7 @@ int decode_range_impl(const uint8_t *data, size_t len, const zflacb200_options *
     sd.scratch_base = 0ull - (uint64_t)C * ((first_sample + 7) & ~7ull);
     const uint64_t scratch_elems = (uint64_t)C * (((out->n_samples + 7) & ~7ull) + 16) + 64ull * n + 64;
     if (b_scratch.alloc(scratch_elems * (wide ? 8 : 4), st) || b_pcm.alloc(((n_elems + 15) & ~15ull) * cb + 64, st) ||
-        stage.prepare(wide, flags, n, st) != ZFLACB200_OK)
+        stage.prepare(wide, flags, n, st, sd.si_depth) != ZFLACB200_OK)
         return ZFLACB200_CUDA_ERROR;
     CU_CHECK(put_small(ctx, b_sd.p, &sd, sizeof(sd), st));
     rh.lo_out = nullptr;
@@ -1963,6 +2008,7 @@ int decode_range_impl(const uint8_t *data, size_t len, const zflacb200_options *
     CU_CHECK(cudaEventRecord(ev.e[5], st));
     GET_SMALL(h_sum, ctx, b_sum.p, sizeof(StreamSummary), st);
     GET_SMALL(h_lossy, ctx, b_flag.p, sizeof(uint32_t), st);
+    GET_SMALL(h_ovf, ctx, stage.two_pass ? (const void *)stage.overflow_flag() : b_flag.p, sizeof(uint32_t), st);
     CU_CHECK(cudaMemcpyAsync(dst, b_pcm.p, n_elems * cb, cudaMemcpyDeviceToHost, st));  // an unaccepted shard's bytes are garbage
     CU_CHECK(cudaEventRecord(ev.e[7], st));
     CU_CHECK(cudaStreamSynchronize(st));
@@ -1980,8 +2026,9 @@ int decode_range_impl(const uint8_t *data, size_t len, const zflacb200_options *
     info->audio_bytes = sum.end_offset > lohi[1] ? sum.end_offset - lohi[1] : 0;
     out->n_frames = sum.n_frames;
     out->end_offset = sum.end_offset;
+    const bool narrow_overflow = stage.narrow && *(const uint32_t *)h_ovf != 0;  // the whole-stream path redoes it on the int32 scratch
     const bool accepted = !sum.fail && sum.n_frames == lohi[2] && sum.n_samples == n_elems && !(msb_shift && lossy) &&
-                          sum.end_offset > lohi[1];
+                          sum.end_offset > lohi[1] && !narrow_overflow;
     out->accepted = accepted ? 1u : 0u;
     info->fast_path = accepted ? 1 : 0;
     return ZFLACB200_OK;
@@ -2016,6 +2063,10 @@ void zflacb200_shutdown(void) {
             cudaStreamDestroy(g_ctx[d].copy_out);
             for (auto &l : g_ctx[d].lane) cudaStreamDestroy(l);
             cudaFreeHost(g_ctx[d].mailbox);
+            for (int k = 0; k < 2; ++k) {
+                if (g_ctx[d].md5_stage[k]) cudaFreeHost(g_ctx[d].md5_stage[k]);
+                if (g_ctx[d].ev_md5[k]) cudaEventDestroy(g_ctx[d].ev_md5[k]);
+            }
             for (auto &pb : g_ctx[d].pin_blocks) cudaFreeHost(pb.first);
             cudaEventDestroy(g_ctx[d].ev_fork);
             cudaEventDestroy(g_ctx[d].ev_join);

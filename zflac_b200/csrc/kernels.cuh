@@ -57,6 +57,9 @@ struct SubRec;  // parse_core.cuh
 constexpr size_t kSubRecBytes = 80;  // sizeof(SubRec); 8 slots per frame record
 cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, int32_t *d_scratch,
                                 SubRec *d_subs, FrameOut *d_outs, uint32_t *d_big_orders, bool write_samples, cudaStream_t st);
+// narrow K2a (streams of <= 16 bits per sample): uint16 scratch of folded residuals; d_flags = {big orders, 16-bit overflow}
+cudaError_t launch_parse_frames_narrow(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, uint16_t *d_scratch,
+                                       SubRec *d_subs, FrameOut *d_outs, uint32_t *d_flags, bool write_samples, cudaStream_t st);
 struct PredictParams {
     const FrameRec *frames;
     const FrameOut *outs;      // frames whose status is not ST_OK are skipped
@@ -69,6 +72,7 @@ struct PredictParams {
     uint32_t msb_shift;
     uint32_t *lossy_flag;
     const uint32_t *big_orders;  // written by launch_parse_frames: != 0 iff some subframe has an order above 12
+    bool narrow = false;         // scratch is uint16 folded residuals (launch_parse_frames_narrow)
 };
 cudaError_t launch_predict_epilogue(const PredictParams &p, cudaStream_t st);
 

@@ -6,6 +6,7 @@
 // one lane per subframe. The logic is parse_core.cuh; the word source is StagedSrc of ring_src.cuh.
 #include "kernels.cuh"
 #include "parse_core.cuh"
+#include "parse_narrow.cuh"
 #include "ring_src.cuh"
 
 namespace zf {
@@ -37,6 +38,55 @@ k_parse_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frame
     parse_frame(br, fr, scratch, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order);
     if (max_order > 12 && write_samples) *big_orders = 1u;  // pass B then also runs its 32-tap kernel
     outs[f] = o;
+}
+
+// Narrow K2a (parse_narrow.cuh): streams of <= 16 bits per sample. One-warp CTAs, one lane per frame, PosReader over a
+// PairSrc ring in static shared memory; the scratch is uint16 (folded residuals as coded). flags[0]: some subframe has an
+// order above 12 (pass B then also runs its 32-tap kernel); flags[1]: a value did not fit 16 bits (the host redoes the
+// launch group on the int32 path).
+template <int RING>
+__global__ void __launch_bounds__(32, RING >= 64 ? 14 : 20)
+k_parse_frames_narrow(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frames, uint32_t n_frames,
+                      uint16_t *__restrict__ scratch, SubRec *__restrict__ subs, FrameOut *__restrict__ outs,
+                      uint32_t *__restrict__ flags, int write_samples) {
+    const uint32_t f = blockIdx.x * 32u + threadIdx.x;
+    if (f >= n_frames) return;
+    const FrameRec fr = frames[f];
+    if (fr.block_size == 0) return;  // dropped candidate slot
+    const uint64_t start = fr.offset + fr.header_len;  // first subframe header
+    const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(s + start) & 15u);
+    const uint64_t origin = start - lead;
+    const uint64_t span = fr.stream_end > start ? fr.stream_end - start + lead : 0;
+    PosReader<PairSrc<RING>> br;
+    br.src.init(s + start - lead, span, threadIdx.x);
+    br.init_at(lead);
+    const uint64_t len_bits = span * 8;
+    FrameOut o;
+    uint32_t max_order = 0, overflow = 0;
+    parse_frame_narrow(br, fr, scratch, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order, overflow);
+    if (max_order > 12 && write_samples) flags[0] = 1u;
+    if (overflow && write_samples) flags[1] = 1u;
+    outs[f] = o;
+}
+
+cudaError_t launch_parse_frames_narrow(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, uint16_t *d_scratch,
+                                       SubRec *d_subs, FrameOut *d_outs, uint32_t *d_flags, bool write_samples, cudaStream_t st) {
+    if (n_frames == 0) return cudaSuccess;
+    ZF_COUNT_LAUNCH();
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    const uint32_t warps = (n_frames + 31u) / 32u;
+    // the deep ring (64 entries: a refill every other body never runs dry) while one wave of it holds every frame
+    if (warps <= (uint32_t)sms * 14u)
+        k_parse_frames_narrow<64><<<warps, 32, 0, st>>>(d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_flags, write_samples ? 1 : 0);
+    else
+        k_parse_frames_narrow<32><<<warps, 32, 0, st>>>(d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_flags, write_samples ? 1 : 0);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, int32_t *d_scratch,

@@ -1,0 +1,253 @@
+// parse_narrow.cuh — pass A of the two-pass subframe decoder for streams of <= 16 bits per sample ("narrow" K2a).
+//
+// Same job and same error sites as parse_core.cuh's parse_frame (reference src/zflac.zig:425-551, :614-666): one lane
+// walks the serial bit chain of one frame and leaves, per subframe, a SubRec and the raw material of the predictor.
+// What differs:
+//   * the bit reader is PosReader (pos_reader.cuh): one register of state, I2FP instead of FLO, 13 instructions a row;
+//   * the scratch holds int16 values — residuals, warm-up samples, VERBATIM samples — half the bytes pass A writes and
+//     pass B (predict.cu, NARROW) reads back. A row of eight is one 16-byte store (sub_idx16() below).
+//   * a value that does not fit 16 bits raises `overflow`: the host then decodes the launch group again on the
+//     int32 path (parse_core.cuh). For audio of <= 16 bits that takes a residual beyond +-32767, i.e. never in practice.
+#pragma once
+#include "parse_core.cuh"
+#include "pos_reader.cuh"
+
+namespace zf {
+
+ZF_HD uint32_t misfit16(int32_t v) { return v != (int32_t)(int16_t)v ? 1u : 0u; }
+ZF_HD uint32_t pack16(int32_t lo, int32_t hi) {  // two int16 in one word (PRMT)
+#ifdef __CUDA_ARCH__
+    return __byte_perm((uint32_t)lo, (uint32_t)hi, 0x5410);
+#else
+    return ((uint32_t)lo & 0xFFFFu) | ((uint32_t)hi << 16);
+#endif
+}
+
+// Narrow scratch layout: per frame, groups of SIXTEEN time steps; inside a group the channels one after another, 16
+// consecutive uint16 values each (one 32-byte sector per channel and group):
+//     element(frame, ch, i) = 2 * scratch_base + (i / 16) * 16 * C + ch * 16 + (i % 16)        [uint16 units]
+// A row of eight is one 16-byte store, the two halves of a sector are written by the same lane a few hundred cycles apart
+// and merge in L2. (With groups of eight a sector was shared by two channels, written a whole subframe apart: every
+// 16-byte store became a DRAM read-modify-write, r2c: 1.8 GB read + 1.26 GB written for 0.64 GB of payload.)
+// The frame's region is the one the int32 layout would use (scratch_base counts 4-byte elements): room to spare.
+ZF_HD uint32_t sub_idx16(uint32_t i, uint32_t c16) { return (i >> 4) * c16 + (i & 15u); }
+
+template <class Src>
+ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__ out, uint32_t c16, uint32_t order,
+                                      uint32_t block_size, uint64_t len_bits, bool wr, uint32_t &overflow) {
+    const uint32_t method = br.read(2);
+    if (method >= 2) return ST_INVALID_RESIDUAL_CODING_METHOD;
+    const uint32_t pbits = 4 + method;
+    const uint32_t po = br.read(4);
+    const uint32_t psize = block_size >> po;
+    if ((psize << po) != block_size || psize < order) return ST_UNDEFINED_IN_REFERENCE;  // Q16
+    uint32_t i = order;
+    const uint32_t nparts = 1u << po;
+    uint32_t part = 0, end = order;  // "partition -1" ends where the residual starts
+    uint32_t k = 0;
+    RiceParams rp;
+    rp.set(0);
+    bool body_ok = false;       // k <= 16: a body can be accepted at all
+    uint32_t force_single = 0;  // rows that must take the one-row path (after a rejected body)
+    uint32_t nbody = 0;         // whole 8-row bodies to run before anything else needs a look
+    // The value extraction and the store of a body run one body late, inside the next body's chain: the chain is a string
+    // of dependent instructions with a shared-memory load in every row, the extraction of the previous body's eight float
+    // patterns is independent work the scheduler drops into its gaps. fp / ip: patterns and first row of the pending body.
+    uint32_t fp[8];
+    uint32_t ip = 0;
+    bool pend = false;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) fp[u] = 0;
+    uint32_t j_stale = br.entry_index();  // ring entry of the cursor one body ago: top_up() never waits for the newest position
+    // ONE loop over partitions and rows (see parse_core.cuh): lanes of a warp run their bodies together whatever their
+    // partition layouts are. The common iteration tests one counter; everything else (partition boundary, rows up to
+    // an 8-aligned index, partition tails, rows after a rejected body) is a detour that ends by recounting it.
+#pragma unroll 1
+    for (;;) {
+        if (nbody != 0) {
+            br.src.top_up_stale(j_stale);
+            j_stale = br.entry_index();
+            uint32_t fn[8], qn;
+            const bool ok = rice_chain8(br, rp, fn, qn);
+            {   // the pending body (straight-line code: only the store is predicated)
+                int32_t r[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) r[u] = rice_value(fp[u], rp);
+                if (pend && wr) {
+                    uint16_t *dst = out + (size_t)(ip >> 4) * c16 + (ip & 8u);  // ip is a multiple of 8: one 16-byte half sector
+                    uint4 v;
+                    v.x = pack16(r[0], r[1]);
+                    v.y = pack16(r[2], r[3]);
+                    v.z = pack16(r[4], r[5]);
+                    v.w = pack16(r[6], r[7]);
+                    *reinterpret_cast<uint4 *>(dst) = v;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) fp[u] = fn[u];
+            pend = ok;
+            ip = i;
+            br.Q = ok ? qn : br.Q;
+            i = ok ? i + 8 : i;
+            nbody = ok ? nbody - 1 : 0u;
+            force_single = ok ? force_single : 8u;
+            continue;
+        }
+        if (pend) {  // leaving the run of bodies: finish the last one (k is still its partition's)
+            if (wr) {
+                uint16_t *dst = out + (size_t)(ip >> 4) * c16 + (ip & 8u);
+                uint4 v;
+                v.x = pack16(rice_value(fp[0], rp), rice_value(fp[1], rp));
+                v.y = pack16(rice_value(fp[2], rp), rice_value(fp[3], rp));
+                v.z = pack16(rice_value(fp[4], rp), rice_value(fp[5], rp));
+                v.w = pack16(rice_value(fp[6], rp), rice_value(fp[7], rp));
+                *reinterpret_cast<uint4 *>(dst) = v;
+            }
+            pend = false;
+        }
+        if (i >= end) {  // partition boundary
+            if (part && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
+            if (part == nparts) break;
+            const uint32_t param = br.read(pbits);
+            end = (part + 1) * psize;
+            ++part;
+            if (param == (1u << pbits) - 1u) {  // escape: raw signed residuals of esc bits (:646-654)
+                const uint32_t esc = br.read(5);
+#pragma unroll 1
+                for (; i < end; ++i) {
+                    const int32_t r = esc ? br.read_signed(esc) : 0;
+                    overflow |= misfit16(r);
+                    if (wr) out[sub_idx16(i, c16)] = (uint16_t)r;
+                    if ((i & 255u) == 255u && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
+                }
+                continue;
+            }
+            k = param;
+            body_ok = k <= 16;
+            if (body_ok) rp.set(k);
+        } else {  // one row
+            const uint32_t win = br.peek();
+            const uint32_t z = clz32(win);
+            const uint32_t n = z + k + 1;
+            uint32_t cw;
+            if (n <= 32) {
+                cw = (z << k) | shr_c(shl_c(win, z + 1), 32 - k);
+                br.skip(n);
+            } else {  // a codeword longer than the window: unbounded unary part, then k bits
+                const uint32_t q = br.read_unary(len_bits);
+                if (q == 0xFFFFFFFFu) return ST_END_OF_STREAM;
+                const uint32_t r = br.read(k);
+                cw = (q << k) + r;
+                if ((q >> 16) != 0) overflow |= 1u;  // q << k wrapped or is far beyond 16 bits either way
+            }
+            overflow |= cw >> 16;
+            if (wr) out[sub_idx16(i, c16)] = (uint16_t)zigzag(cw);
+            ++i;
+            if (force_single) --force_single;
+        }
+        nbody = (body_ok && force_single == 0 && (i & 7u) == 0) ? (end > i ? (end - i) >> 3 : 0u) : 0u;
+        j_stale = br.entry_index();  // exact after a detour; inside a run of bodies it trails by one body
+    }
+    return ST_OK;
+}
+
+// One whole frame, subframes in channel order, then align + CRC-16 (:425-551). `scratch` is the uint16 view of the
+// launch's scratch buffer (sub_idx16() layout).
+template <class Src>
+ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, uint16_t *__restrict__ scratch, SubRec *__restrict__ subs,
+                               uint64_t len_bits, bool wr, uint64_t origin_byte, FrameOut &o, uint32_t &max_order, uint32_t &overflow) {
+    uint32_t status = ST_OK;
+    const uint32_t bs = fr.block_size;
+    const uint32_t bps = fr.bps;
+#pragma unroll 1
+    for (uint32_t ch = 0; ch < fr.channels && status == ST_OK; ++ch) {
+        const uint32_t hdr = br.read(8);  // zero:1 type:6 wasted_flag:1 (:426-430)
+        if (hdr & 0x80u) {
+            status = ST_INVALID_SUBFRAME_HEADER;
+            break;
+        }
+        const uint32_t type = (hdr >> 1) & 0x3Fu;
+        uint32_t wasted = 0;
+        if (hdr & 1u) {
+            const uint32_t u = br.read_unary(len_bits);
+            if (u == 0xFFFFFFFFu) { status = ST_END_OF_STREAM; break; }
+            if (u + 1 > 63) { status = ST_UNDEFINED_IN_REFERENCE; break; }
+            wasted = u + 1;  // :433
+        }
+        uint32_t depth = bps;  // :436-441
+        if ((fr.ch_code == 8 && ch == 1) || (fr.ch_code == 9 && ch == 0) || (fr.ch_code == 10 && ch == 1)) depth += 1;
+        uint16_t *out = scratch + 2u * fr.scratch_base + ch * 16u;  // sub_idx16() layout inside the frame's int32-sized region
+        const uint32_t c16 = 16u * fr.channels;
+        SubRec *sub = subs + ch;
+        uint32_t kind = kSubRaw, order = 0, shift = 0, wide_acc = 0;
+        int32_t constant = 0;
+
+        if (type == 0) {  // CONSTANT (:445-454): reads bps - wasted bits even on a side channel (Q8)
+            if (wasted >= bps) { status = ST_UNDEFINED_IN_REFERENCE; break; }
+            constant = br.read_signed(bps - wasted);
+            kind = kSubConst;
+        } else if (type == 1) {  // VERBATIM (:455-465)
+            if (wasted >= depth) { status = ST_UNDEFINED_IN_REFERENCE; break; }
+            const uint32_t n = depth - wasted;
+#pragma unroll 1
+            for (uint32_t i = 0; i < bs; ++i) {
+                const int32_t v = br.read_signed(n);
+                overflow |= misfit16(v);
+                if (wr) out[sub_idx16(i, c16)] = (uint16_t)v;
+                if ((i & 255u) == 255u && br.pos_bits() > len_bits) break;  // ran off the stream
+            }
+        } else if ((type >= 8 && type <= 12) || type >= 32) {  // FIXED (:466-498) / LPC (:499-541)
+            const bool is_lpc = type >= 32;
+            order = is_lpc ? type - 31 : type - 8;
+            if (wasted >= depth || order > bs) { status = ST_UNDEFINED_IN_REFERENCE; break; }
+            const uint32_t eff = depth - wasted;
+            kind = kSubPred;
+            max_order = max_order > order ? max_order : order;
+#pragma unroll 1
+            for (uint32_t t = 0; t < order; ++t) {  // warm-up samples (:473-479, :501-507)
+                const int32_t v = br.read_signed(eff);
+                overflow |= misfit16(v);
+                if (wr) out[sub_idx16(t, c16)] = (uint16_t)v;
+            }
+            if (is_lpc) {
+                const uint32_t precision = br.read(4) + 1;  // :508 (0b1111 is not rejected by the reference)
+                shift = br.read(5);                         // :510 unsigned (Q17)
+                wide_acc = eff + precision + ceil_log2(order) > 32 ? 1u : 0u;
+#pragma unroll 1
+                for (uint32_t t = 0; t < order; ++t) {      // t-th coefficient multiplies s[i-1-t] (:513-514)
+                    const int32_t v = br.read_signed(precision);
+                    if (wr) sub->coef[t] = (int16_t)v;
+                }
+            } else {
+                wide_acc = eff + 4 > 32 ? 1u : 0u;  // |sum| <= 15 * 2^(depth-1)
+                if (wr) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) sub->coef[j] = (int16_t)fixed_coef(order, j);
+                }
+            }
+            status = parse_residual_narrow(br, out, c16, order, bs, len_bits, wr, overflow);
+        } else {  // reserved (:542)
+            status = ST_INVALID_SUBFRAME_HEADER;
+        }
+        if (wr) {
+            sub->kind = (uint8_t)kind;
+            sub->order = (uint8_t)order;
+            sub->shift = (uint8_t)shift;
+            sub->wasted = (uint8_t)wasted;
+            sub->wide_acc = (uint8_t)wide_acc;
+            sub->constant = constant;
+        }
+    }
+    uint32_t stored_crc = 0;
+    if (status == ST_OK) {
+        br.align_byte();            // :546
+        stored_crc = br.read(16);   // :548, not checked by the reference
+    }
+    const uint64_t pos = br.pos_bits();
+    if (pos > len_bits) status = ST_END_OF_STREAM;  // whatever went wrong, the reference's reader failed first
+    o.end_offset = origin_byte + (pos >> 3);
+    o.status = status;
+    o.stored_crc16 = stored_crc;
+}
+
+}  // namespace zf

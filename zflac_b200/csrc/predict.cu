@@ -56,7 +56,8 @@ __device__ __forceinline__ void lpc_chunk(int32_t (&h)[HMAX], const int32_t (&cf
 // thread: 17 warps per SM); LARGE = true: the others (32 taps). Both kernels run over all frames and
 // a warp leaves at once when it belongs to the other one; `big_orders` (set by pass A) lets the LARGE
 // launch retire immediately when no subframe of the launch has an order above 12.
-template <bool LARGE, int CB>
+// NARROW: the scratch holds int16 values (parse_narrow.cuh): one 16-byte load per eight steps.
+template <bool LARGE, int CB, bool NARROW>
 __global__ void __launch_bounds__(32, LARGE ? 8 : 17)
 k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restrict__ outs, uint32_t n_frames,
                    const int32_t *__restrict__ scratch, const SubRec *__restrict__ subs, uint8_t *__restrict__ pcm,
@@ -93,7 +94,10 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             if (kind != kSubPred) order = 0;
             bs = fr.block_size;
             C = fr.channels;
-            src = scratch + fr.scratch_base + c * 8u;  // sub_idx() layout: 8 values of this channel per group of 8 * C
+            // sub_idx() layout: 8 values of this channel per group of 8 * C (elements: int32, or uint16 when NARROW)
+            // NARROW: sub_idx16() layout of parse_narrow.cuh inside the same (int32-sized) region: 16 values per channel and group
+            src = NARROW ? reinterpret_cast<const int32_t *>(reinterpret_cast<const uint16_t *>(scratch + fr.scratch_base) + c * 16u)
+                         : scratch + fr.scratch_base + c * 8u;
             elem_base = fr.sample_base + c;
             bps = fr.bps;
             if (fr.channels == 2) {  // :553-578
@@ -161,18 +165,29 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
     int4 na = make_int4(constant, constant, constant, constant), nb = na;
     if (loads) {
         na = *reinterpret_cast<const int4 *>(src);
-        nb = *reinterpret_cast<const int4 *>(src + 4);
+        if (!NARROW) nb = *reinterpret_cast<const int4 *>(src + 4);
     }
+    const bool folded = NARROW && loads;  // na = eight int16 values (constant subframes keep the value itself)
     uint32_t lossy = 0, buf = 0;
     uint8_t *const slot0 = tile + g * (chunk_bytes + 16) + c * CB;
     const uint32_t rs = C * CB;
 #pragma unroll 1
     for (uint32_t i0 = 0; i0 < bs_max; i0 += 8) {
-        const int32_t r[8] = {na.x, na.y, na.z, na.w, nb.x, nb.y, nb.z, nb.w};
+        int32_t r[8] = {na.x, na.y, na.z, na.w, nb.x, nb.y, nb.z, nb.w};
+        if (folded) {
+            const uint32_t w[4] = {(uint32_t)na.x, (uint32_t)na.y, (uint32_t)na.z, (uint32_t)na.w};
+#pragma unroll
+            for (int u = 0; u < 8; ++u) r[u] = (u & 1) ? ((int32_t)w[u >> 1] >> 16) : (int32_t)(int16_t)w[u >> 1];
+        }
         if (loads && i0 + 8 < bs) {  // next group (whole groups are in bounds: the frame's scratch covers roundup8(bs) steps)
-            const int32_t *nx = src + (size_t)((i0 >> 3) + 1) * c8;
-            na = *reinterpret_cast<const int4 *>(nx);
-            nb = *reinterpret_cast<const int4 *>(nx + 4);
+            if (NARROW) {  // the other half of the sector, or the first half of the next group's
+                const uint32_t i1 = i0 + 8;
+                na = *reinterpret_cast<const int4 *>(reinterpret_cast<const uint16_t *>(src) + (size_t)(i1 >> 4) * (2 * c8) + (i1 & 8u));
+            } else {
+                const int32_t *nx = src + (size_t)((i0 >> 3) + 1) * c8;
+                na = *reinterpret_cast<const int4 *>(nx);
+                nb = *reinterpret_cast<const int4 *>(nx + 4);
+            }
         }
         int32_t y[8];
         if (i0 < order_max) {  // warm-up steps present (first one or two iterations; four in the LARGE kernel)
@@ -267,18 +282,25 @@ cudaError_t launch_predict_epilogue(const PredictParams &p, cudaStream_t st) {
     if (cp_shift > 3) cp_shift = 3;
     const uint32_t G = 32u >> cp_shift;
     const uint32_t blocks = (uint32_t)(((uint64_t)p.n_frames + G - 1) / G);  // one warp per CTA
-#define ZF_PRED(LARGE, CB)                                                                                                       \
-    k_predict_epilogue<LARGE, CB><<<blocks, 32, 0, st>>>(p.frames, p.outs, p.n_frames, (const int32_t *)p.scratch,              \
-                                                         (const SubRec *)p.subs, (uint8_t *)p.pcm, p.msb_shift, cp_shift,       \
-                                                         p.lossy_flag, p.big_orders)
+#define ZF_PRED(LARGE, CB, NARROW)                                                                                               \
+    k_predict_epilogue<LARGE, CB, NARROW><<<blocks, 32, 0, st>>>(p.frames, p.outs, p.n_frames, (const int32_t *)p.scratch,      \
+                                                                 (const SubRec *)p.subs, (uint8_t *)p.pcm, p.msb_shift, cp_shift, \
+                                                                 p.lossy_flag, p.big_orders)
+    // narrow scratch: streams of <= 16 bits per sample, i.e. containers of 1 or 2 bytes
     ZF_COUNT_LAUNCH();
-    if (p.container_bytes == 1) ZF_PRED(false, 1);
-    else if (p.container_bytes == 2) ZF_PRED(false, 2);
-    else ZF_PRED(false, 4);
+    if (p.narrow) {
+        if (p.container_bytes == 1) ZF_PRED(false, 1, true);
+        else ZF_PRED(false, 2, true);
+    } else if (p.container_bytes == 1) ZF_PRED(false, 1, false);
+    else if (p.container_bytes == 2) ZF_PRED(false, 2, false);
+    else ZF_PRED(false, 4, false);
     ZF_COUNT_LAUNCH();
-    if (p.container_bytes == 1) ZF_PRED(true, 1);
-    else if (p.container_bytes == 2) ZF_PRED(true, 2);
-    else ZF_PRED(true, 4);
+    if (p.narrow) {
+        if (p.container_bytes == 1) ZF_PRED(true, 1, true);
+        else ZF_PRED(true, 2, true);
+    } else if (p.container_bytes == 1) ZF_PRED(true, 1, false);
+    else if (p.container_bytes == 2) ZF_PRED(true, 2, false);
+    else ZF_PRED(true, 4, false);
 #undef ZF_PRED
     return cudaGetLastError();
 }

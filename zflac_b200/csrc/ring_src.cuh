@@ -10,6 +10,7 @@
 // that only blocks on groups old enough to have landed.
 #pragma once
 #include "decode_core.cuh"
+#include "pos_reader.cuh"
 
 namespace zf {
 
@@ -275,6 +276,107 @@ struct QuadSrc {
         while (w >= staged) flush_and_load();
         return word(w);
     }
+};
+
+
+// ---------------------------------------------------------------------------------------------
+// PairSrc — word source of the narrow K2a (pos_reader.cuh, parse_narrow.cuh). One-warp CTAs; ring entry j of lane L
+// at ring[j % RING][L] holds stream words (j - 1, j) as {x, y}, both MSB-first, so ONE aligned 8-byte shared load
+// yields the 64 stream bits around any position. Filled through registers like StagedSrc: four 128-bit global loads
+// per sixteen words, issued one refill ahead of their sixteen 8-byte shared stores, every lane refilling on the same
+// (even) bodies. The ring is STATIC shared memory, so its base is an immediate of the LDS and the address of an entry
+// is two instructions: IMAD (255 - 8 * Q) and LOP3 ((that & ring mask) | lane * 8).
+// Word 0 sits at a 16-byte aligned global address.
+// ---------------------------------------------------------------------------------------------
+template <int RING>
+struct PairSrc {
+    static constexpr int kThreads = 32;
+    static constexpr uint32_t kRing = RING;
+    const uint8_t *g;   // global address of word 0 (16-byte aligned)
+    uint32_t avail;     // bytes readable from g (stream end), clamped
+    uint32_t staged;    // entries < staged are in the ring; words [staged, staged + 16) are in q[] (possibly still in flight)
+    uint32_t carry;     // word staged - 1, MSB-first
+    uint32_t lane8;     // lane * 8: byte offset of the lane's column inside a ring row
+    uint4 q[4];
+
+    static __device__ __forceinline__ uint2 *ring() {
+        __shared__ __align__(16) uint2 r[RING * 32];
+        return r;
+    }
+    __device__ __forceinline__ uint2 entry_at(uint32_t Q) const {  // entry (31 - Q) >> 5; byte offset of its row = ((255 - 8Q) & mask)
+        const uint32_t off = ((255u - 8u * Q) & ((RING - 1u) << 8)) | lane8;
+        return *reinterpret_cast<const uint2 *>(reinterpret_cast<const char *>(ring()) + off);
+    }
+    __device__ __forceinline__ uint2 entry(uint32_t j) const {
+        const uint32_t off = ((j & (RING - 1u)) << 8) | lane8;
+        return *reinterpret_cast<const uint2 *>(reinterpret_cast<const char *>(ring()) + off);
+    }
+    __device__ __forceinline__ void load16(uint32_t w) {  // words [w, w + 16) -> q; bytes past the stream end read as zero
+        const uint32_t off = w * 4u;
+        if (off + 64u <= avail) {
+            const uint4 *p = reinterpret_cast<const uint4 *>(g + off);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q[k] = __ldg(p + k);
+            if (off + 1024u <= avail) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + off + 576u));  // see StagedSrc
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q[k] = staged_tail_quad(g, off + 16u * k, avail);
+        }
+    }
+    __device__ __forceinline__ void flush_and_load() {  // q -> entries [staged, staged + 16); staged % 16 == 0: no wrap inside
+        char *row = reinterpret_cast<char *>(ring()) + (((staged & (RING - 1u)) << 8) | lane8);
+        uint32_t prev = carry;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t w0 = __byte_perm(q[k].x, 0, 0x0123), w1 = __byte_perm(q[k].y, 0, 0x0123);
+            const uint32_t w2 = __byte_perm(q[k].z, 0, 0x0123), w3 = __byte_perm(q[k].w, 0, 0x0123);
+            *reinterpret_cast<uint2 *>(row + 256 * (4 * k + 0)) = make_uint2(prev, w0);
+            *reinterpret_cast<uint2 *>(row + 256 * (4 * k + 1)) = make_uint2(w0, w1);
+            *reinterpret_cast<uint2 *>(row + 256 * (4 * k + 2)) = make_uint2(w1, w2);
+            *reinterpret_cast<uint2 *>(row + 256 * (4 * k + 3)) = make_uint2(w2, w3);
+            prev = w3;
+        }
+        carry = prev;
+        staged += 16;
+        load16(staged);
+    }
+    __device__ __forceinline__ void init(const uint8_t *base, uint64_t bytes, uint32_t lane) {
+        g = base;
+        avail = bytes > 0xFFFFFF80ull ? 0xFFFFFF80u : (uint32_t)bytes;
+        lane8 = lane * 8u;
+        staged = 0;
+        carry = 0;
+        load16(0);
+#pragma unroll 1
+        for (int k = 0; k < (RING >= 64 ? 3 : 1); ++k) flush_and_load();  // a frame starts with 48 (16) entries in the ring and 16 words on their way
+    }
+    // entries < j0 are consumed; afterwards entries [j0, j0 + kFastEntries) are resident.
+    // WHEN a lane refills is a warp decision. The scoreboard is per warp register: a refill's shared stores wait for the
+    // newest global load into q[] by ANY lane, so lanes refilling each on its own schedule (a quarter of them on every
+    // other body, r2c: 70 % of all stall samples sat here) make every refill wait out a DRAM round trip. Instead nobody
+    // refills until some lane runs low, and then every lane that has room does: the lanes of a warp consume at similar
+    // rates, so refills come once per ~16 consumed words (six bodies of 16-bit audio) and the loads of one refill have
+    // that long to land before the next one stores them.
+    static constexpr uint32_t kLow = RING >= 64 ? 20u : 12u;
+    __device__ __forceinline__ void top_up(uint32_t j0, uint32_t) {
+        const uint32_t ahead = staged - j0;
+        if (__any_sync(__activemask(), ahead < kLow) && ahead + 16u <= RING) flush_and_load();
+#pragma unroll 1
+        while (staged < j0 + kFastEntries) flush_and_load();  // only when the refills above fell behind (long codewords, slow-path rows)
+    }
+    // The same with a cursor that is one 8-row body old (the true one is at most 8 entries further): the refill decision
+    // does not wait for the newest position, so it is off the bit chain's critical path.
+    __device__ __forceinline__ void top_up_stale(uint32_t j_old) {
+        const uint32_t ahead = staged - j_old;  // true ahead >= ahead - 8
+        if (__any_sync(__activemask(), ahead < kLow + 8u) && ahead + 16u <= RING) flush_and_load();
+#pragma unroll 1
+        while (staged < j_old + 8u + kFastEntries) flush_and_load();
+    }
+    __device__ __forceinline__ void ensure(uint32_t j) {
+#pragma unroll 1
+        while (j >= staged) flush_and_load();
+    }
+    __device__ __forceinline__ void body_done(bool) {}
 };
 
 
