@@ -75,6 +75,7 @@ struct HostPairSrc {
         if (!(j >= guaranteed_lo && j < guaranteed_hi)) ++speculative;
         return make(j);
     }
+    static constexpr bool kStaleCursor = true;
     void body_done(bool ok) {
         if (ok) violations += speculative;
         speculative = 0;
@@ -82,7 +83,8 @@ struct HostPairSrc {
     void ensure(uint32_t j) { ensured = j; guaranteed_lo = guaranteed_hi = 0; }
     void top_up(uint32_t j0, uint32_t) { guaranteed_lo = j0; guaranteed_hi = j0 + zf::kFastEntries; ensured = 0xFFFFFFFFu; }
     // cursor of one body ago: the device keeps [j_old, j_old + 8 + kFastEntries) resident
-    void top_up_stale(uint32_t j_old) { guaranteed_lo = j_old; guaranteed_hi = j_old + 8 + zf::kFastEntries; ensured = 0xFFFFFFFFu; }
+    // (and the entry below j_old: a body reads its windows nine bits early)
+    void top_up_stale(uint32_t j_old) { guaranteed_lo = j_old ? j_old - 1 : 0; guaranteed_hi = j_old + 8 + zf::kFastEntries; ensured = 0xFFFFFFFFu; }
 };
 
 }  // namespace
@@ -133,10 +135,11 @@ int zf_host_parse_frame(const uint8_t *stream, const zf::FrameRec *fr, int32_t *
     return br.src.violations;
 }
 
-// Narrow pass A (parse_narrow.cuh) on the host: folded 16-bit residuals into `scratch` (uint16, sub_idx() layout).
-// Returns the unchecked-read violations (must be 0); *overflow != 0 when a value did not fit 16 bits.
+// Narrow pass A (parse_narrow.cuh) on the host: int16 rows into `scratch`. layout 0: the frame's own region
+// (kLayoutFrame, scratch_base 0); layout 1: the warp-interleaved one (kLayoutWarp) as lane `lane` of a warp whose region
+// starts at scratch. Returns the unchecked-read violations (must be 0); *overflow != 0 when a value did not fit 16 bits.
 int zf_host_parse_frame_narrow(const uint8_t *stream, const zf::FrameRec *fr, uint16_t *scratch, zf::SubRec *subs, int write_samples,
-                               zf::FrameOut *out, uint32_t *overflow) {
+                               zf::FrameOut *out, uint32_t *overflow, int layout, int lane) {
     const uint64_t start = fr->offset + fr->header_len;
     const uint64_t origin = start & ~15ull;  // the device source starts at a 16-byte aligned address
     const uint64_t bytes = fr->stream_end > origin ? fr->stream_end - origin : 0;
@@ -147,14 +150,14 @@ int zf_host_parse_frame_narrow(const uint8_t *stream, const zf::FrameRec *fr, ui
     br.src.ensured = 0xFFFFFFFFu;
     br.src.violations = 0;
     br.init_at((uint32_t)(start - origin));
+    zf::NarrowSink sink;
+    if (layout == zf::kLayoutWarp) sink.set_warp(scratch, 0, (uint32_t)lane, fr->block_size);
+    else sink.set_frame(scratch, 0, fr->channels);
     uint32_t max_order = 0;
     *overflow = 0;
-    zf::parse_frame_narrow(br, *fr, scratch, subs, bytes * 8, write_samples != 0, origin, *out, max_order, *overflow);
+    zf::parse_frame_narrow(br, *fr, sink, subs, bytes * 8, write_samples != 0, origin, *out, max_order, *overflow);
     return br.src.violations;
 }
-
-// the unfold pass B applies to a narrow scratch value
-int32_t zf_host_unfold(uint32_t cw) { return zf::zigzag(cw); }
 
 // Scalar restatement of what pass B (predict.cu) does to one scratch plane: predictor recurrence in
 // place, then the wasted-bits shift. Test-side stand-in for the CUDA kernel (the -m gpu tests pin the kernel).

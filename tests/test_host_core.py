@@ -47,7 +47,8 @@ def core():
     lib.zf_host_predict_plane.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
     lib.zf_host_predict_plane.restype = None
     assert lib.zf_host_subrec_size() == 80
-    lib.zf_host_parse_frame_narrow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    lib.zf_host_parse_frame_narrow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                               C.c_int, C.c_int]
     lib.zf_host_parse_frame_narrow.restype = C.c_int
     return lib
 
@@ -78,14 +79,25 @@ def host_decode(lib, data: bytes, ref, two_pass: bool = False, narrow: bool = Fa
             subs = np.zeros(8 * 80, dtype=np.uint8)
             done = False
             if narrow:
-                s16 = np.zeros((bs + 15) // 16 * 16 * ch, dtype=np.uint16)  # sub_idx16() layout: groups of 16 steps x channels x 16
+                # both row layouts of parse_narrow.cuh, alternating from frame to frame: the frame's own region (groups of
+                # 16 steps x channels x 16 values) and the warp-interleaved one (row t of channel c of lane L at
+                # ((c * nb + t) * 32 + L) * 16 bytes), here as a lane that changes with the frame
+                nb = pitch // 8
+                warp_layout = (int(fr["offset"]) // 7) % 2 == 1
+                lane = int(fr["offset"]) % 32
+                s16 = np.zeros(ch * nb * 32 * 8 if warp_layout else (bs + 15) // 16 * 16 * ch, dtype=np.uint16)
                 ovf = np.zeros(1, dtype=np.uint32)
                 viol = lib.zf_host_parse_frame_narrow(arr.ctypes.data, rec.ctypes.data, s16.ctypes.data, subs.ctypes.data, 1,
-                                                      out.ctypes.data, ovf.ctypes.data)
+                                                      out.ctypes.data, ovf.ctypes.data, int(warp_layout), lane)
                 assert viol == 0, "unchecked ring entry read outside the top_up guarantee"
                 if int(ovf[0]) == 0:
-                    val = s16.view(np.int16).astype(np.int32).reshape(-1, ch, 16)
-                    planes16 = val.transpose(1, 0, 2).reshape(ch, -1)[:, :pitch]   # [channel][time step]
+                    if warp_layout:
+                        rows = s16.view(np.int16).astype(np.int32).reshape(ch, nb, 32, 8)
+                        assert not rows[:, :, np.arange(32) != lane, :].any(), "wrote into another lane's rows"
+                        planes16 = rows[:, :, lane, :].reshape(ch, pitch)
+                    else:
+                        val = s16.view(np.int16).astype(np.int32).reshape(-1, ch, 16)
+                        planes16 = val.transpose(1, 0, 2).reshape(ch, -1)[:, :pitch]   # [channel][time step]
                     scratch = planes16.reshape(ch, pitch // 8, 8).transpose(1, 0, 2).reshape(-1).copy()  # the int32 sub_idx() layout
                     done = True
                 elif stats is not None:

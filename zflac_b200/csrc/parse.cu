@@ -50,9 +50,21 @@ k_parse_frames_narrow(const uint8_t *__restrict__ s, const FrameRec *__restrict_
                       uint16_t *__restrict__ scratch, SubRec *__restrict__ subs, FrameOut *__restrict__ outs,
                       uint32_t *__restrict__ flags, int write_samples) {
     const uint32_t f = blockIdx.x * 32u + threadIdx.x;
-    if (f >= n_frames) return;
-    const FrameRec fr = frames[f];
-    if (fr.block_size == 0) return;  // dropped candidate slot
+    FrameRec fr;
+    fr.block_size = 0;
+    fr.channels = 0;
+    fr.scratch_base = 0;
+    if (f < n_frames) fr = frames[f];
+    // layout of the warp's rows (parse_narrow.cuh): interleaved when its 32 frames are alike and their regions in order
+    const uint32_t bs0 = __shfl_sync(0xFFFFFFFFu, fr.block_size, 0), c0 = __shfl_sync(0xFFFFFFFFu, (uint32_t)fr.channels, 0);
+    const uint64_t base0 = __shfl_sync(0xFFFFFFFFu, fr.scratch_base, 0);
+    const uint64_t need = (uint64_t)threadIdx.x * c0 * ((bs0 + 7u) & ~7u);  // elements the lanes below would use on their own
+    const bool alike = fr.block_size != 0 && fr.block_size == bs0 && fr.channels == c0 && fr.scratch_base >= base0 + need;
+    const bool interleave = __all_sync(0xFFFFFFFFu, alike);
+    if (fr.block_size == 0) return;  // dropped candidate slot / past the end
+    NarrowSink sink;
+    if (interleave) sink.set_warp(scratch, base0, threadIdx.x, bs0);
+    else sink.set_frame(scratch, fr.scratch_base, fr.channels);
     const uint64_t start = fr.offset + fr.header_len;  // first subframe header
     const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(s + start) & 15u);
     const uint64_t origin = start - lead;
@@ -63,7 +75,7 @@ k_parse_frames_narrow(const uint8_t *__restrict__ s, const FrameRec *__restrict_
     const uint64_t len_bits = span * 8;
     FrameOut o;
     uint32_t max_order = 0, overflow = 0;
-    parse_frame_narrow(br, fr, scratch, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order, overflow);
+    parse_frame_narrow(br, fr, sink, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order, overflow);
     if (max_order > 12 && write_samples) flags[0] = 1u;
     if (overflow && write_samples) flags[1] = 1u;
     outs[f] = o;

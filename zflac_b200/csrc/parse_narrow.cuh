@@ -5,7 +5,7 @@
 // What differs:
 //   * the bit reader is PosReader (pos_reader.cuh): one register of state, I2FP instead of FLO, 13 instructions a row;
 //   * the scratch holds int16 values — residuals, warm-up samples, VERBATIM samples — half the bytes pass A writes and
-//     pass B (predict.cu, NARROW) reads back. A row of eight is one 16-byte store (sub_idx16() below).
+//     pass B (predict.cu, NARROW) reads back. A row of eight is one 16-byte store (layouts below).
 //   * a value that does not fit 16 bits raises `overflow`: the host then decodes the launch group again on the
 //     int32 path (parse_core.cuh). For audio of <= 16 bits that takes a residual beyond +-32767, i.e. never in practice.
 #pragma once
@@ -23,17 +23,58 @@ ZF_HD uint32_t pack16(int32_t lo, int32_t hi) {  // two int16 in one word (PRMT)
 #endif
 }
 
-// Narrow scratch layout: per frame, groups of SIXTEEN time steps; inside a group the channels one after another, 16
-// consecutive uint16 values each (one 32-byte sector per channel and group):
-//     element(frame, ch, i) = 2 * scratch_base + (i / 16) * 16 * C + ch * 16 + (i % 16)        [uint16 units]
-// A row of eight is one 16-byte store, the two halves of a sector are written by the same lane a few hundred cycles apart
-// and merge in L2. (With groups of eight a sector was shared by two channels, written a whole subframe apart: every
-// 16-byte store became a DRAM read-modify-write, r2c: 1.8 GB read + 1.26 GB written for 0.64 GB of payload.)
-// The frame's region is the one the int32 layout would use (scratch_base counts 4-byte elements): room to spare.
-ZF_HD uint32_t sub_idx16(uint32_t i, uint32_t c16) { return (i >> 4) * c16 + (i & 15u); }
+// Narrow scratch layouts. A lane writes one 16-byte row (eight int16) per body, a pass-B lane reads one per step; what
+// the layouts decide is how the rows of the 32 frames of a pass-A warp lie next to each other in memory, i.e. how many
+// memory requests one store / load instruction of a warp becomes. Measured (tools/ubench/chain.cu, r2g): the L1 handles
+// about one 32-byte-sector request per two cycles per SM, and a warp storing 32 rows into 32 frames' own regions costs
+// 32 of them — the scattered rows, not the bit chain, were what bounded K2a.
+//   kLayoutWarp  the 32 frames of the warp are INTERLEAVED row by row: row t of channel c of the frame in lane L at
+//                warp_base + ((c * nb + t) * 32 + L) * 16 bytes, nb = ceil(block_size / 8). Lanes run their bodies in
+//                step, so a store instruction writes 512 contiguous bytes; pass B's lanes (consecutive frames x channels)
+//                read runs of 16-byte rows too. Needs a warp whose 32 frames have one block size and channel count
+//                (any stream's frames but the last few); decided per warp, flagged in SubRec.pad[0].
+//   kLayoutFrame the frame's own region, groups of sixteen steps, channels one after another inside a group (one
+//                32-byte sector per channel and group, written by the same lane in two halves):
+//                frame_base + (t / 2) * 32 * C + c * 32 + (t % 2) * 16.
+// Both live inside the region the int32 layout would use (scratch_base counts 4-byte elements): room to spare.
+enum : uint8_t { kLayoutFrame = 0, kLayoutWarp = 1 };
+
+struct NarrowSink {
+    uint8_t *base;       // row 0 of channel 0 of this lane's frame
+    uint32_t ch_stride;  // bytes from a channel's row 0 to the next channel's
+    uint32_t row_shift;  // row t lives at (t >> row_shift) * row_stride + (t & row_mask) * 16
+    uint32_t row_mask;
+    uint32_t row_stride;
+    uint8_t layout;
+    ZF_HD void set_frame(void *scratch, uint64_t scratch_base, uint32_t channels) {
+        base = reinterpret_cast<uint8_t *>(scratch) + 4u * scratch_base;
+        ch_stride = 32u;
+        row_shift = 1u;
+        row_mask = 1u;
+        row_stride = 32u * channels;
+        layout = kLayoutFrame;
+    }
+    ZF_HD void set_warp(void *scratch, uint64_t warp_scratch_base, uint32_t lane, uint32_t block_size) {
+        base = reinterpret_cast<uint8_t *>(scratch) + 4u * warp_scratch_base + 16u * lane;
+        ch_stride = ((block_size + 7u) >> 3) * 512u;
+        row_shift = 0u;
+        row_mask = 0u;
+        row_stride = 512u;
+        layout = kLayoutWarp;
+    }
+};
+struct NarrowOut {  // one channel's rows
+    uint8_t *base;
+    uint32_t row_shift, row_mask, row_stride;
+    ZF_HD uint8_t *row(uint32_t i) const {  // the 16-byte row that holds step i
+        const uint32_t t = i >> 3;
+        return base + (size_t)(t >> row_shift) * row_stride + (t & row_mask) * 16u;
+    }
+    ZF_HD void put(uint32_t i, int32_t v) const { reinterpret_cast<uint16_t *>(row(i))[i & 7u] = (uint16_t)v; }
+};
 
 template <class Src>
-ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__ out, uint32_t c16, uint32_t order,
+ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, const NarrowOut &out, uint32_t order,
                                       uint32_t block_size, uint64_t len_bits, bool wr, uint32_t &overflow) {
     const uint32_t method = br.read(2);
     if (method >= 2) return ST_INVALID_RESIDUAL_CODING_METHOD;
@@ -58,15 +99,19 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__
     bool pend = false;
 #pragma unroll
     for (int u = 0; u < 8; ++u) fp[u] = 0;
-    uint32_t j_stale = br.entry_index();  // ring entry of the cursor one body ago: top_up() never waits for the newest position
+    uint32_t j_stale = br.entry_index();  // ring entry of the cursor one body ago: the refill decision never waits for the newest position
     // ONE loop over partitions and rows (see parse_core.cuh): lanes of a warp run their bodies together whatever their
     // partition layouts are. The common iteration tests one counter; everything else (partition boundary, rows up to
     // an 8-aligned index, partition tails, rows after a rejected body) is a detour that ends by recounting it.
 #pragma unroll 1
     for (;;) {
         if (nbody != 0) {
-            br.src.top_up_stale(j_stale);
-            j_stale = br.entry_index();
+            if (Src::kStaleCursor) {
+                br.src.top_up_stale(j_stale);
+                j_stale = br.entry_index();
+            } else {
+                br.src.top_up(br.entry_index(), 0u);
+            }
             uint32_t fn[8], qn;
             const bool ok = rice_chain8(br, rp, fn, qn);
             {   // the pending body (straight-line code: only the store is predicated)
@@ -74,13 +119,12 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__
 #pragma unroll
                 for (int u = 0; u < 8; ++u) r[u] = rice_value(fp[u], rp);
                 if (pend && wr) {
-                    uint16_t *dst = out + (size_t)(ip >> 4) * c16 + (ip & 8u);  // ip is a multiple of 8: one 16-byte half sector
                     uint4 v;
                     v.x = pack16(r[0], r[1]);
                     v.y = pack16(r[2], r[3]);
                     v.z = pack16(r[4], r[5]);
                     v.w = pack16(r[6], r[7]);
-                    *reinterpret_cast<uint4 *>(dst) = v;
+                    *reinterpret_cast<uint4 *>(out.row(ip)) = v;  // ip is a multiple of 8
                 }
             }
 #pragma unroll
@@ -95,13 +139,12 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__
         }
         if (pend) {  // leaving the run of bodies: finish the last one (k is still its partition's)
             if (wr) {
-                uint16_t *dst = out + (size_t)(ip >> 4) * c16 + (ip & 8u);
                 uint4 v;
                 v.x = pack16(rice_value(fp[0], rp), rice_value(fp[1], rp));
                 v.y = pack16(rice_value(fp[2], rp), rice_value(fp[3], rp));
                 v.z = pack16(rice_value(fp[4], rp), rice_value(fp[5], rp));
                 v.w = pack16(rice_value(fp[6], rp), rice_value(fp[7], rp));
-                *reinterpret_cast<uint4 *>(dst) = v;
+                *reinterpret_cast<uint4 *>(out.row(ip)) = v;
             }
             pend = false;
         }
@@ -117,7 +160,7 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__
                 for (; i < end; ++i) {
                     const int32_t r = esc ? br.read_signed(esc) : 0;
                     overflow |= misfit16(r);
-                    if (wr) out[sub_idx16(i, c16)] = (uint16_t)r;
+                    if (wr) out.put(i, r);
                     if ((i & 255u) == 255u && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
                 }
                 continue;
@@ -141,7 +184,7 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__
                 if ((q >> 16) != 0) overflow |= 1u;  // q << k wrapped or is far beyond 16 bits either way
             }
             overflow |= cw >> 16;
-            if (wr) out[sub_idx16(i, c16)] = (uint16_t)zigzag(cw);
+            if (wr) out.put(i, zigzag(cw));
             ++i;
             if (force_single) --force_single;
         }
@@ -151,10 +194,9 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, uint16_t *__restrict__
     return ST_OK;
 }
 
-// One whole frame, subframes in channel order, then align + CRC-16 (:425-551). `scratch` is the uint16 view of the
-// launch's scratch buffer (sub_idx16() layout).
+// One whole frame, subframes in channel order, then align + CRC-16 (:425-551). `sink` says where the frame's rows go.
 template <class Src>
-ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, uint16_t *__restrict__ scratch, SubRec *__restrict__ subs,
+ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const NarrowSink &sink, SubRec *__restrict__ subs,
                                uint64_t len_bits, bool wr, uint64_t origin_byte, FrameOut &o, uint32_t &max_order, uint32_t &overflow) {
     uint32_t status = ST_OK;
     const uint32_t bs = fr.block_size;
@@ -176,8 +218,11 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, uint16_t 
         }
         uint32_t depth = bps;  // :436-441
         if ((fr.ch_code == 8 && ch == 1) || (fr.ch_code == 9 && ch == 0) || (fr.ch_code == 10 && ch == 1)) depth += 1;
-        uint16_t *out = scratch + 2u * fr.scratch_base + ch * 16u;  // sub_idx16() layout inside the frame's int32-sized region
-        const uint32_t c16 = 16u * fr.channels;
+        NarrowOut out;
+        out.base = sink.base + (size_t)ch * sink.ch_stride;
+        out.row_shift = sink.row_shift;
+        out.row_mask = sink.row_mask;
+        out.row_stride = sink.row_stride;
         SubRec *sub = subs + ch;
         uint32_t kind = kSubRaw, order = 0, shift = 0, wide_acc = 0;
         int32_t constant = 0;
@@ -193,7 +238,7 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, uint16_t 
             for (uint32_t i = 0; i < bs; ++i) {
                 const int32_t v = br.read_signed(n);
                 overflow |= misfit16(v);
-                if (wr) out[sub_idx16(i, c16)] = (uint16_t)v;
+                if (wr) out.put(i, v);
                 if ((i & 255u) == 255u && br.pos_bits() > len_bits) break;  // ran off the stream
             }
         } else if ((type >= 8 && type <= 12) || type >= 32) {  // FIXED (:466-498) / LPC (:499-541)
@@ -207,7 +252,7 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, uint16_t 
             for (uint32_t t = 0; t < order; ++t) {  // warm-up samples (:473-479, :501-507)
                 const int32_t v = br.read_signed(eff);
                 overflow |= misfit16(v);
-                if (wr) out[sub_idx16(t, c16)] = (uint16_t)v;
+                if (wr) out.put(t, v);
             }
             if (is_lpc) {
                 const uint32_t precision = br.read(4) + 1;  // :508 (0b1111 is not rejected by the reference)
@@ -225,7 +270,7 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, uint16_t 
                     for (int j = 0; j < 4; ++j) sub->coef[j] = (int16_t)fixed_coef(order, j);
                 }
             }
-            status = parse_residual_narrow(br, out, c16, order, bs, len_bits, wr, overflow);
+            status = parse_residual_narrow(br, out, order, bs, len_bits, wr, overflow);
         } else {  // reserved (:542)
             status = ST_INVALID_SUBFRAME_HEADER;
         }
@@ -235,6 +280,7 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, uint16_t 
             sub->shift = (uint8_t)shift;
             sub->wasted = (uint8_t)wasted;
             sub->wide_acc = (uint8_t)wide_acc;
+            sub->pad[0] = sink.layout;
             sub->constant = constant;
         }
     }

@@ -25,6 +25,8 @@
 //
 // Host-testable (tests/host_core/): HostPairSrc there implements the same concept over plain memory.
 #pragma once
+#include <cstring>
+
 #include "decode_core.cuh"
 
 namespace zf {
@@ -107,24 +109,33 @@ struct PosReader {
     ZF_HD void align_byte() { Q &= ~7u; }  // -P rounded down to a multiple of 8 = P rounded up
 };
 
+// ---------------------------------------------------------------------------------------
 // Eight Rice codewords with parameter k <= 16, speculative and branch free; a body is rejected when a codeword did not
 // fit the 32-bit window or might not fit 16 bits, and the caller then redoes its rows one by one.
+//
+// What was measured on the way here (B200, tools/ubench/chain*.cu, cycles per row of one warp, chain only unless said):
+//   this chain 54.5 (31 of them address + LDS.64); FLO instead of I2FP 75; exponent by LOP3 + FADD (2^23 magic) 60.5;
+//   the same chain with the ring refilled by one cp.async.bulk per lane 89-113 (an elect loop of 9 instructions per
+//   lane and TMA's per-request cost); value extraction in a second phase through a shared-memory tile +25 (+37 with two
+//   warps per scheduler): with ~21 instructions a row, most on the half-rate ALU pipe, two warps per scheduler are
+//   bound by instruction throughput, not by the chain's latency — so the work below is counted in instructions.
+// ---------------------------------------------------------------------------------------
 struct RiceParams {
-    uint32_t C;      // 158 + k + 1: (Q - C) + exponent = Q - (leading zeros + 1 + k)
+    uint32_t C;      // 158 + k + 1: (Q - C) + exponent = Q - (zeros + 1 + k)
     uint32_t sh;     // 23 - k
     uint32_t nmask;  // ~(2^k - 1)
     uint32_t C2;     // 158 << k
     uint32_t fmin;   // smallest float pattern a body accepts: window fit (zeros <= 31 - k) and cw < 65536 guaranteed
-    ZF_HD void set(uint32_t k) {  // k <= 23
+    ZF_HD void set(uint32_t k) {  // k <= 16
         C = 159u + k;
         sh = 23u - k;
         nmask = ~((1u << k) - 1u);
         C2 = 158u << k;
-        // window: zeros <= 31 - k  <=>  exponent >= 127 + k.  16 bits: (zeros + 1) << k <= 65536  <=>  zeros <= (65536 >> k) - 1
+        // window: zeros <= 31 - k.  16 bits: (zeros + 1) << k <= 65536  <=>  zeros <= (65536 >> k) - 1
         const uint32_t zfit = 31u - k;
-        const uint32_t z16 = (65536u >> k) - 1u;  // k <= 16: >= 0; k > 16: 0xFFFFFFFF -> no body ever accepted (cw >= 2^k > 65535 possible)
-        const uint32_t zlim = k > 16 ? 0u : (zfit < z16 ? zfit : z16);
-        fmin = k > 16 ? 0xFFFFFFFFu : ((158u - zlim) << 23);
+        const uint32_t z16 = (65536u >> k) - 1u;
+        const uint32_t zlim = zfit < z16 ? zfit : z16;
+        fmin = (158u - zlim) << 23;
     }
 };
 
@@ -155,7 +166,8 @@ ZF_HDI bool rice_chain8(PosReader<Src> &br, const RiceParams &rp, uint32_t (&f)[
 }
 
 // The residual a float pattern stands for: x = f >> (23 - k) = exponent * 2^k + r, codeword (158 - exponent) * 2^k + r,
-// unfolded ((cw >> 1) ^ -(cw & 1), src/zflac.zig:659-663).
+// unfolded ((cw >> 1) ^ -(cw & 1), src/zflac.zig:659-663). (Written as h - (cw & 1) * cw to get an IMAD, the compiler
+// makes a compare and a select of it: slower, r2l.)
 ZF_HD int32_t rice_value(uint32_t f, const RiceParams &rp) {
     const uint32_t x = f >> rp.sh;
     const uint32_t y = x & rp.nmask;

@@ -19,6 +19,7 @@
 
 #include "kernels.cuh"
 #include "parse_core.cuh"
+#include "parse_narrow.cuh"
 
 namespace zf {
 
@@ -74,6 +75,8 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
 
     // ---- the lane's subframe
     const int32_t *src = scratch;
+    const uint8_t *row0 = reinterpret_cast<const uint8_t *>(scratch);  // NARROW: row t at row0 + (t >> row_shift) * row_stride + (t & row_mask) * 16
+    uint32_t row_shift = 0, row_mask = 0, row_stride = 0;
     uint32_t bs = 0, order = 0, shift = 0, wasted = 0, kind = kSubRaw, C = 1, wide_acc = 0, bps = 0, mode = 0;
     int32_t constant = 0;
     uint64_t elem_base = 0, frame_byte_base = 0;
@@ -95,9 +98,21 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             bs = fr.block_size;
             C = fr.channels;
             // sub_idx() layout: 8 values of this channel per group of 8 * C (elements: int32, or uint16 when NARROW)
-            // NARROW: sub_idx16() layout of parse_narrow.cuh inside the same (int32-sized) region: 16 values per channel and group
-            src = NARROW ? reinterpret_cast<const int32_t *>(reinterpret_cast<const uint16_t *>(scratch + fr.scratch_base) + c * 16u)
-                         : scratch + fr.scratch_base + c * 8u;
+            src = scratch + fr.scratch_base + c * 8u;
+            if (NARROW) {  // rows of eight int16, laid out per warp of pass A or per frame (parse_narrow.cuh, flag in SubRec.pad[0])
+                if (((hd.y >> 8) & 0xFFu) == kLayoutWarp) {
+                    const uint64_t base0 = frames[f & ~31u].scratch_base;
+                    row0 = reinterpret_cast<const uint8_t *>(scratch + base0) + ((size_t)c * ((fr.block_size + 7u) >> 3) * 32u + (f & 31u)) * 16u;
+                    row_shift = 0u;
+                    row_mask = 0u;
+                    row_stride = 512u;
+                } else {
+                    row0 = reinterpret_cast<const uint8_t *>(scratch + fr.scratch_base) + c * 32u;
+                    row_shift = 1u;
+                    row_mask = 1u;
+                    row_stride = 32u * fr.channels;
+                }
+            }
             elem_base = fr.sample_base + c;
             bps = fr.bps;
             if (fr.channels == 2) {  // :553-578
@@ -164,7 +179,7 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
     const uint32_t c8 = 8 * C;
     int4 na = make_int4(constant, constant, constant, constant), nb = na;
     if (loads) {
-        na = *reinterpret_cast<const int4 *>(src);
+        na = *reinterpret_cast<const int4 *>(NARROW ? reinterpret_cast<const int32_t *>(row0) : src);
         if (!NARROW) nb = *reinterpret_cast<const int4 *>(src + 4);
     }
     const bool folded = NARROW && loads;  // na = eight int16 values (constant subframes keep the value itself)
@@ -180,9 +195,9 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             for (int u = 0; u < 8; ++u) r[u] = (u & 1) ? ((int32_t)w[u >> 1] >> 16) : (int32_t)(int16_t)w[u >> 1];
         }
         if (loads && i0 + 8 < bs) {  // next group (whole groups are in bounds: the frame's scratch covers roundup8(bs) steps)
-            if (NARROW) {  // the other half of the sector, or the first half of the next group's
-                const uint32_t i1 = i0 + 8;
-                na = *reinterpret_cast<const int4 *>(reinterpret_cast<const uint16_t *>(src) + (size_t)(i1 >> 4) * (2 * c8) + (i1 & 8u));
+            if (NARROW) {
+                const uint32_t t = (i0 >> 3) + 1;
+                na = *reinterpret_cast<const int4 *>(row0 + (size_t)(t >> row_shift) * row_stride + (t & row_mask) * 16u);
             } else {
                 const int32_t *nx = src + (size_t)((i0 >> 3) + 1) * c8;
                 na = *reinterpret_cast<const int4 *>(nx);

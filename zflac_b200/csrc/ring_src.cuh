@@ -372,6 +372,7 @@ struct PairSrc {
 #pragma unroll 1
         while (staged < j_old + 8u + kFastEntries) flush_and_load();
     }
+    static constexpr bool kStaleCursor = RING >= 64;  // a 32-entry ring has no room for the 8 entries of slack a stale cursor costs
     __device__ __forceinline__ void ensure(uint32_t j) {
 #pragma unroll 1
         while (j >= staged) flush_and_load();
