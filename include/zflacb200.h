@@ -115,6 +115,10 @@ void zflacb200_shutdown(void);
 const char *zflacb200_status_name(int status); /* the Zig error name, e.g. "InvalidFrameHeader" */
 const char *zflacb200_last_error(void);        /* thread-local detail for CUDA_ERROR / INVALID_ARGUMENT */
 uint64_t zflacb200_kernel_launches(void);      /* kernels this library has launched since load (bench: gpu_launches) */
+/* diagnostics: launches of pass A (the frame-serial bit-chain kernel) by instantiation since load. variant 0:
+ * k_parse_frames<StagedSrc> (int32 scratch, one wave), 1: k_parse_frames<QuadSrc> (int32 scratch, more frames than one
+ * wave holds), 2: k_parse_frames_narrow<64> (streams of <= 16 bits), 3: k_parse_frames_narrow<32> (the same, large launches). */
+uint64_t zflacb200_pass_a_launches(int variant);
 
 /* Replaces the body of decode() (src/zflac.zig:217-310): signature + metadata walk,
  * frame index, subframe decode, decorrelation, MD5 gate, MSB-align shift.

@@ -52,3 +52,46 @@ def test_empty_and_metadata_only_streams(z):
     handle, info = C.c_void_p(), _native.Info()
     st = lib.zflacb200_open(None, 0, None, C.byref(handle), C.byref(info))
     assert lib.zflacb200_status_name(st).decode() == "EndOfStream" and not handle.value
+
+
+def _overstate_total(flac: np.ndarray, total: int) -> np.ndarray:
+    """STREAMINFO total (36 bits at bit 108 of the block body) replaced: a claim the bytes cannot back up."""
+    out = flac.copy()
+    body = 8  # signature + block header
+    v = int.from_bytes(out[body + 13: body + 18].tobytes(), "big")
+    v = (v & ~((1 << 36) - 1)) | (total & ((1 << 36) - 1))
+    out[body + 13: body + 18] = np.frombuffer(v.to_bytes(5, "big"), dtype=np.uint8)
+    return out
+
+
+@pytest.mark.parametrize("total", [(1 << 36) - 1, 50_000_000], ids=["2^36-1", "5e7"])
+def test_overstated_total_solo(z, total):
+    """the fast path must not size its buffers from a total the bytes cannot hold; the stream goes the robust
+    way and ends like the reference's loop does (EndOfStream when the bytes run out before the stated total)."""
+    from oracle import oracle
+    from tools import flacgen as fg
+    s = fg.generate(fg.c2(2.0), want_pcm=False)
+    bad = _overstate_total(s.flac, total)
+    # the reference allocates total * channels samples up front (:329-334): OutOfMemory where the allocator refuses
+    # (the oracle's malloc here: 275 GB), else it decodes until the bytes run out: EndOfStream (:343-350). Never a CUDA error.
+    assert oracle.decode(bad).error in ("EndOfStream", "OutOfMemory")
+    with pytest.raises((z.EndOfStream, z.OutOfMemory)):
+        z.decode(bad)
+    with pytest.raises((z.EndOfStream, z.OutOfMemory)):
+        z.decode_into(bad, np.empty(1 << 20, dtype=np.int16))
+    assert np.array_equal(z.decode(s.flac).samples, oracle.decode(s.flac).samples)  # the library is fine afterwards
+
+
+def test_overstated_total_in_a_batch(z):
+    """One member with an absurd total must not take the batch (or its launch group) down with it."""
+    from tools import flacgen as fg
+    files = [fg.generate(fg.c5_file(i), want_pcm=True) for i in range(6)]
+    streams = [f.flac for f in files]
+    streams[2] = _overstate_total(streams[2], (1 << 36) - 1)
+    streams[4] = _overstate_total(streams[4], 3_000_000_000)
+    res = z.decode_batch(streams)
+    for i, (f, r) in enumerate(zip(files, res)):
+        if i in (2, 4):
+            assert isinstance(r, (z.EndOfStream, z.OutOfMemory)), r
+        else:
+            assert np.array_equal(r.samples, f.pcm)

@@ -19,7 +19,7 @@ MD5_ON_DEVICE = 0x100
 
 EXPORTS = [
     "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown",
-    "zflacb200_status_name", "zflacb200_last_error", "zflacb200_kernel_launches", "zflacb200_open", "zflacb200_read",
+    "zflacb200_status_name", "zflacb200_last_error", "zflacb200_kernel_launches", "zflacb200_pass_a_launches", "zflacb200_open", "zflacb200_read",
     "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_frames", "zflacb200_batch_open",
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
     "zflacb200_batch_close", "zflacb200_batch_pcm_bound", "zflacb200_batch_decode",
@@ -90,6 +90,8 @@ def load():
     lib.zflacb200_status_name.restype = C.c_char_p
     lib.zflacb200_last_error.restype = C.c_char_p
     lib.zflacb200_kernel_launches.restype = C.c_uint64
+    lib.zflacb200_pass_a_launches.restype = C.c_uint64
+    lib.zflacb200_pass_a_launches.argtypes = [C.c_int]
     lib.zflacb200_open.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.POINTER(C.c_void_p), C.POINTER(Info)]
     lib.zflacb200_open.restype = C.c_int
     lib.zflacb200_open_frames.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Options), C.c_uint64, C.POINTER(C.c_void_p),

@@ -29,12 +29,15 @@ using namespace zf;
 
 namespace zf {
 std::atomic<unsigned long long> g_kernel_launches{0};
+std::atomic<unsigned long long> g_pass_a_launches[kPassAVariants];
 }
 
 namespace {
 
 thread_local std::string g_last_error;
-std::mutex g_mutex;
+// One lock per DEVICE (not per process): calls on different devices run side by side, calls on one device take turns
+// (they share its streams, pinned arena and mailbox). The reference's decode() is re-entrant; so is this.
+std::mutex g_dev_mutex[64];
 
 struct DeviceCtx {
     bool ready = false;
@@ -111,10 +114,31 @@ void *pin_take(DeviceCtx &c, size_t bytes) {
     c.pin_used += bytes;
     return r;
 }
-void pin_rewind_all() {
-    for (auto &c : g_ctx)
-        if (c.ready) pin_rewind(c);
-}
+thread_local bool g_alloc_oom = false;  // an allocation the device could not satisfy (DevBuf::alloc): OutOfMemory, not CudaError
+
+// Scope of one C-ABI call: resolves the device the call runs on, takes that device's lock, rewinds its pinned arena,
+// and puts the CALLER's current device back when the call ends (the library switches devices inside).
+struct ApiScope {
+    int device = 0, prev = -1;
+    std::unique_lock<std::mutex> lk;
+    explicit ApiScope(int want) {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            cudaGetLastError();
+            prev = -1;
+        }
+        device = want >= 0 ? want : prev;
+        if (device < 0 || device >= 64) device = 0;
+        lk = std::unique_lock<std::mutex>(g_dev_mutex[device]);
+        g_last_error.clear();
+        g_alloc_oom = false;
+        if (g_ctx[device].ready) pin_rewind(g_ctx[device]);
+    }
+    ~ApiScope() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+    int done(int rc) const { return rc == ZFLACB200_CUDA_ERROR && g_alloc_oom ? (int)ZFLACB200_OUT_OF_MEMORY : rc; }
+};
+int opt_device(const zflacb200_options *opt) { return opt ? opt->device : -1; }
 // host -> device; `src` may be a temporary (it is copied into the arena before this returns)
 cudaError_t put_small(DeviceCtx &c, void *d_dst, const void *src, size_t bytes, cudaStream_t st) {
     if (bytes == 0) return cudaSuccess;
@@ -130,6 +154,16 @@ const void *get_small(DeviceCtx &c, const void *d_src, size_t bytes, cudaStream_
     if (zf::launch_copy_small(slot, d_src, bytes, st) != cudaSuccess) return nullptr;
     return slot;
 }
+// STREAMINFO's total is untrusted input and the fast path sizes its buffers from it: a frame holds at most 65535 samples
+// per channel and takes at least 10 bytes (header 6, one subframe byte, CRC-16, ...), so a total beyond what the bytes
+// could hold sends the stream to the robust path, which sizes everything from the frames it actually finds (and reports
+// EndOfStream like the reference, :341-350) — instead of asking the driver for terabytes.
+bool plausible_total(uint64_t total, uint64_t audio_bytes) { return total <= 65535ull * (audio_bytes / 10 + 1); }
+
+// (g_alloc_oom: an allocation the device could not satisfy, remembered per thread so that callers can tell it from a
+// real CUDA error: fast path -> robust path, and OutOfMemory rather than CudaError at the C ABI)
+constexpr int kFastOom = -2;
+
 // ---- where one stream's MD5 chain runs (hostmd5.h): on a host thread unless the stream is short or the caller insists
 bool md5_on_host(uint32_t flags, uint64_t pcm_bytes) {
     const char *e = getenv("ZFLACB200_HOST_MD5_MIN_BYTES");  // test knob, read on every call
@@ -599,7 +633,15 @@ struct DevBuf {  // stream-ordered allocation released on scope exit
             p = nullptr;
         }
         st = s;
-        CU_CHECK(dev_alloc(&p, bytes ? bytes : 16, s));
+        const cudaError_t e = dev_alloc(&p, bytes ? bytes : 16, s);
+        if (e == cudaErrorMemoryAllocation) {
+            cudaGetLastError();  // not sticky
+            p = nullptr;
+            g_alloc_oom = true;
+            g_last_error = "device out of memory (" + std::to_string(bytes) + " bytes requested)";
+            return ZFLACB200_OUT_OF_MEMORY;
+        }
+        CU_CHECK(e);
         return ZFLACB200_OK;
     }
     void *release() {
@@ -745,13 +787,14 @@ int run_fast_group_once(FastGroup &g, Events &ev) {
         max_channels = std::max<uint32_t>(max_channels, sd.si_channels);
         max_depth = std::max<uint32_t>(max_depth, sd.si_depth);
     }
-    if (stage.prepare(g.wide, g.flags, n, st, max_depth, g.allow_narrow) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+    g_alloc_oom = false;
+    if (stage.prepare(g.wide, g.flags, n, st, max_depth, g.allow_narrow) != ZFLACB200_OK) return g_alloc_oom ? kFastOom : ZFLACB200_CUDA_ERROR;
     if (b_sd.alloc(sizeof(StreamDesc) * ns, st) || g.b_recs.alloc(sizeof(FrameRec) * (size_t)n, st) ||
         g.b_outs.alloc(sizeof(FrameOut) * (size_t)n, st) || b_scratch.alloc(g.scratch_elems * (g.wide ? 8 : 4), st) ||
         g.b_pcm.alloc(g.pcm_elems * g.container_bytes + 64, st) || b_sum.alloc(sizeof(StreamSummary) * ns, st) ||
         g.b_ok.alloc(n, st) || b_flag.alloc(sizeof(uint32_t), st) || b_jobs.alloc(sizeof(Md5Job) * ns, st) ||
         b_digest.alloc(16 * (size_t)ns, st))
-        return ZFLACB200_CUDA_ERROR;
+        return g_alloc_oom ? kFastOom : ZFLACB200_CUDA_ERROR;
     tr.mark("alloc");
     CU_CHECK(put_small(ctx, b_sd.p, g.streams.data(), sizeof(StreamDesc) * ns, st));
     CU_CHECK(cudaMemsetAsync(b_sum.p, 0, sizeof(StreamSummary) * ns, st));
@@ -977,7 +1020,8 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
 
     // ---- fast path: device-side hinted chain, verified after decoding (no host walk, no CRC-16 pre-pass)
     if (n_cand > 0 && pl.si.total > 0 && (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0 &&
-        pl.si.total * (pl.si.channels_m1 + 1) < (1ull << 40)) {
+        pl.si.total * (pl.si.channels_m1 + 1) < (1ull << 40) && plausible_total(pl.si.total, len - std::min<uint64_t>(len, pl.audio_offset)) &&
+        pl.si.total <= 65535ull * n_cand) {
         FastGroup g;
         g.device = device;
         g.st = st;
@@ -1002,11 +1046,9 @@ int open_impl(const uint8_t *data, size_t len, const zflacb200_options *opt, zfl
         sd.si_depth = (uint8_t)depth;
         g.streams.push_back(sd);
         g.hash_bytes.push_back(aligned == 24 ? 3 : container_bytes);  // :268-277
-        {
-            const int r = run_fast_group(g, ev);
-            if (r != ZFLACB200_OK) return r;
-        }
-        if (g.accepted(0)) {
+        const int fast_rc = run_fast_group(g, ev);
+        if (fast_rc != ZFLACB200_OK && fast_rc != kFastOom) return fast_rc;
+        if (fast_rc == ZFLACB200_OK && g.accepted(0)) {
             const StreamSummary &sum = g.sums[0];
             info->ms_scan = ev_ms(ev.e[1], ev.e[2]);
             info->ms_link = g.ms_hint;
@@ -1329,6 +1371,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         if (host_parse_header(src, it.audio_offset, h0) == ZFLACB200_OK)
             it.wide = (h0.bd_code == 0 ? it.depth : kBps[h0.bd_code]) == 32;
         it.eligible = it.si.total > 0 && it.si.total * (it.si.channels_m1 + 1) < (1ull << 40) &&
+                      plausible_total(it.si.total, lens[i] - std::min<uint64_t>(lens[i], it.audio_offset)) &&
                       (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0;
         if (it.eligible) {
             const uint32_t key = ((uint32_t)it.si.channels_m1 << 20) | (it.wide ? 1u << 16 : 0u) | (it.container << 8) | it.msb_shift;
@@ -1437,6 +1480,10 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
             tr.mark("group_setup");
             {
                 const int r = run_fast_group(g, ev);
+                if (r == kFastOom) {  // the group's buffers do not fit: its streams are decoded one by one on the robust path
+                    for (size_t i : members) items[i].eligible = false;
+                    continue;
+                }
                 if (r != ZFLACB200_OK) return r;
             }
             tr.mark("run_fast_group");
@@ -1495,7 +1542,13 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
     for (size_t i = 0; i < n; ++i) {
         if (statuses[i] != ZFLACB200_OK || b->items[i].group >= 0) continue;
         zflacb200_stream *h = nullptr;
+        g_alloc_oom = false;
         statuses[i] = open_impl(blob + offsets[i], lens[i], &solo_opt, &h, &infos[i]);
+        if (statuses[i] == ZFLACB200_CUDA_ERROR && g_alloc_oom) {  // this stream does not fit the device: the others go on
+            statuses[i] = ZFLACB200_OUT_OF_MEMORY;
+            g_alloc_oom = false;
+            continue;
+        }
         if (statuses[i] == ZFLACB200_CUDA_ERROR) return ZFLACB200_CUDA_ERROR;
         if (statuses[i] == ZFLACB200_OK) {
             b->items[i].solo = h;
@@ -2046,15 +2099,16 @@ int zflacb200_device_count(void) {
 }
 
 int zflacb200_init(int device) {
-    std::lock_guard<std::mutex> lock(g_mutex);
+    ApiScope api(device);
     int d;
-    return ensure_device(device, &d);
+    return ensure_device(api.device, &d);
 }
 
 void zflacb200_shutdown(void) {
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_cache.release_all();
-    for (int d = 0; d < 64; ++d)
+    int prev = -1;
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    for (int d = 0; d < 64; ++d) {
+        std::lock_guard<std::mutex> lock(g_dev_mutex[d]);
         if (g_ctx[d].ready) {
             cudaSetDevice(d);
             cudaStreamDestroy(g_ctx[d].stream);
@@ -2072,6 +2126,9 @@ void zflacb200_shutdown(void) {
             cudaEventDestroy(g_ctx[d].ev_join);
             g_ctx[d] = DeviceCtx();
         }
+    }
+    g_cache.release_all();  // after the streams are gone: every block is idle
+    if (prev >= 0) cudaSetDevice(prev);
 }
 
 const char *zflacb200_status_name(int status) {
@@ -2100,29 +2157,29 @@ const char *zflacb200_last_error(void) { return g_last_error.c_str(); }
 
 uint64_t zflacb200_kernel_launches(void) { return g_kernel_launches.load(); }
 
+uint64_t zflacb200_pass_a_launches(int variant) {
+    return variant >= 0 && variant < kPassAVariants ? g_pass_a_launches[variant].load() : 0;
+}
+
 int zflacb200_open(const uint8_t *data, size_t len, const zflacb200_options *opt, zflacb200_stream **out, zflacb200_info *info) {
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_last_error.clear();
-    pin_rewind_all();
+    ApiScope api(opt_device(opt));
     if (out && info && (((opt ? opt->flags : 0) | env_flags()) & ZFLACB200_INPUT_ON_DEVICE)) {  // long device-resident stream: chunked
         *out = nullptr;
         const int p = decode_pipelined(data, len, opt, nullptr, 0, info, out);
-        if (p != kNotPipelined) return p;
-        if (*out) { zflacb200_stream *h = *out; *out = nullptr; dev_free(h->d_pcm, nullptr); delete h; }
+        if (p != kNotPipelined) return api.done(p);
+        if (*out) { zflacb200_stream *h = *out; *out = nullptr; dev_free(h->d_pcm, g_ctx[api.device].stream); delete h; }
     }
-    return open_impl(data, len, opt, out, info);
+    return api.done(open_impl(data, len, opt, out, info));
 }
 
 int zflacb200_open_frames(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_offset,
                           zflacb200_stream **out, zflacb200_info *info) {
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_last_error.clear();
-    pin_rewind_all();
+    ApiScope api(opt_device(opt));
     if (byte_offset == kNotRaw || byte_offset > len) {
         g_last_error = "byte_offset past the end of the data";
         return ZFLACB200_INVALID_ARGUMENT;
     }
-    return open_impl(data, len, opt, out, info, byte_offset);
+    return api.done(open_impl(data, len, opt, out, info, byte_offset));
 }
 
 int zflacb200_read(zflacb200_stream *s, void *dst, size_t dst_bytes) {
@@ -2131,7 +2188,7 @@ int zflacb200_read(zflacb200_stream *s, void *dst, size_t dst_bytes) {
         g_last_error = "destination smaller than pcm_bytes";
         return ZFLACB200_INVALID_ARGUMENT;
     }
-    std::lock_guard<std::mutex> lock(g_mutex);
+    ApiScope api(s->device);
     CU_CHECK(cudaSetDevice(s->device));
     if (s->pcm_bytes) CU_CHECK(cudaMemcpy(dst, s->d_pcm, s->pcm_bytes, cudaMemcpyDeviceToHost));
     return ZFLACB200_OK;
@@ -2175,7 +2232,7 @@ int zflacb200_read_as(zflacb200_stream *s, int format, void *dst, size_t dst_byt
         return ZFLACB200_INVALID_ARGUMENT;
     }
     if (need == 0) return ZFLACB200_OK;
-    std::lock_guard<std::mutex> lock(g_mutex);
+    ApiScope api(s->device);
     CU_CHECK(cudaSetDevice(s->device));
     cudaStream_t st = g_ctx[s->device].stream;
     DevBuf b_out;
@@ -2195,7 +2252,7 @@ int zflacb200_device_pcm(zflacb200_stream *s, void **dev_ptr, size_t *bytes) {
 
 void zflacb200_close(zflacb200_stream *s) {
     if (!s) return;
-    std::lock_guard<std::mutex> lock(g_mutex);
+    ApiScope api(s->device);
     cudaSetDevice(s->device);
     if (s->d_pcm) dev_free(s->d_pcm, g_ctx[s->device].stream);
     if (s->d_recs) dev_free(s->d_recs, g_ctx[s->device].stream);
@@ -2206,11 +2263,9 @@ void zflacb200_close(zflacb200_stream *s) {
 
 int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *opt, void *dst, size_t dst_capacity, zflacb200_info *info) {
     {
-        std::lock_guard<std::mutex> lock(g_mutex);
-        g_last_error.clear();
-        pin_rewind_all();
+        ApiScope api(opt_device(opt));
         const int p = decode_pipelined(data, len, opt, dst, dst_capacity, info);
-        if (p != kNotPipelined) return p;
+        if (p != kNotPipelined) return api.done(p);
     }
     zflacb200_stream *h = nullptr;
     const int e = zflacb200_open(data, len, opt, &h, info);
@@ -2224,10 +2279,8 @@ int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *o
 
 int zflacb200_decode_range(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_lo, uint64_t byte_hi,
                            void *dst, size_t dst_capacity, zflacb200_range *range, zflacb200_info *info) {
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_last_error.clear();
-    pin_rewind_all();
-    return decode_range_impl(data, len, opt, byte_lo, byte_hi, dst, dst_capacity, range, info);
+    ApiScope api(opt_device(opt));
+    return api.done(decode_range_impl(data, len, opt, byte_lo, byte_hi, dst, dst_capacity, range, info));
 }
 
 // The reference's chain rule across shards: the first frame sits at the audio offset and holds sample 0 (:340), every
@@ -2250,9 +2303,7 @@ int zflacb200_stitch(const zflacb200_range *r, size_t n, uint64_t audio_offset) 
 
 int zflacb200_batch_open(const uint8_t *blob, const uint8_t *device_blob, const uint64_t *offsets, const uint64_t *lens,
                          size_t n, const zflacb200_options *opt, zflacb200_batch **out, zflacb200_info *infos, int *statuses) {
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_last_error.clear();
-    pin_rewind_all();
+    ApiScope api(opt_device(opt));
     return batch_open_impl(blob, device_blob, offsets, lens, n, opt, out, infos, statuses);
 }
 
@@ -2279,9 +2330,7 @@ int zflacb200_batch_decode(const uint8_t *blob, const uint64_t *offsets, const u
                            const zflacb200_options *opt, void *dst, size_t dst_bytes, uint64_t *pcm_offsets,
                            zflacb200_info *infos, int *statuses) {
     if (!blob || !offsets || !lens || !pcm_offsets || !infos || !statuses || (!dst && dst_bytes)) return ZFLACB200_INVALID_ARGUMENT;
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_last_error.clear();
-    pin_rewind_all();
+    ApiScope api(opt_device(opt));
     HostTrace tr("batch_decode");
     int device = -1;
     {
@@ -2412,7 +2461,7 @@ int zflacb200_batch_read_all(zflacb200_batch *b, void *dst, size_t dst_bytes, ui
         g_last_error = "destination smaller than zflacb200_batch_pcm_bytes()";
         return ZFLACB200_INVALID_ARGUMENT;
     }
-    std::lock_guard<std::mutex> lock(g_mutex);
+    ApiScope api(b->device);
     CU_CHECK(cudaSetDevice(b->device));
     cudaStream_t st = g_ctx[b->device].stream;
     uint64_t pos = 0;
@@ -2455,7 +2504,7 @@ int zflacb200_batch_read_stream(zflacb200_batch *b, size_t i, void *dst, size_t 
     const int e = batch_item_ptr(b, i, &p, &bytes);
     if (e != ZFLACB200_OK) return e;
     if (dst_bytes < bytes || (!dst && bytes)) return ZFLACB200_INVALID_ARGUMENT;
-    std::lock_guard<std::mutex> lock(g_mutex);
+    ApiScope api(b->device);
     CU_CHECK(cudaSetDevice(b->device));
     if (bytes) CU_CHECK(cudaMemcpy(dst, p, bytes, cudaMemcpyDeviceToHost));
     return ZFLACB200_OK;
@@ -2470,7 +2519,7 @@ void zflacb200_batch_close(zflacb200_batch *b) {
     if (!b) return;
     for (auto &it : b->items)
         if (it.solo) zflacb200_close(it.solo);
-    std::lock_guard<std::mutex> lock(g_mutex);
+    ApiScope api(b->device);
     cudaSetDevice(b->device);
     for (auto &g : b->groups)
         if (g.d_pcm) dev_free(g.d_pcm, g_ctx[b->device].stream);
@@ -2597,7 +2646,7 @@ int zflacb200_vorbis_comments(const uint8_t *data, size_t len, zflacb200_span *v
 int zflacb200_frames(zflacb200_stream *s, zflacb200_frame *dst, size_t capacity, size_t *n_frames) {
     if (!s || !n_frames) return ZFLACB200_INVALID_ARGUMENT;
     if (s->frames_on_device) {  // fast path: build the table from the device records on first use
-        std::lock_guard<std::mutex> lock(g_mutex);
+        ApiScope api(s->device);
         CU_CHECK(cudaSetDevice(s->device));
         std::vector<FrameRec> recs(s->n_recs);
         std::vector<FrameOut> outs(s->n_recs);

@@ -9,6 +9,9 @@ namespace zf {
 // every kernel launch of the library is counted here (zflacb200_kernel_launches)
 extern std::atomic<unsigned long long> g_kernel_launches;
 #define ZF_COUNT_LAUNCH() (::zf::g_kernel_launches.fetch_add(1, std::memory_order_relaxed))
+// which instantiation of pass A a launch took (zflacb200_pass_a_launches): the parity tests make every variant run
+enum { kPassAStaged = 0, kPassAQuad = 1, kPassANarrow64 = 2, kPassANarrow32 = 3, kPassAVariants = 4 };
+extern std::atomic<unsigned long long> g_pass_a_launches[kPassAVariants];
 
 // scan.cu
 cudaError_t scan_init_constants();

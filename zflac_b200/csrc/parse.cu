@@ -94,6 +94,7 @@ cudaError_t launch_parse_frames_narrow(const uint8_t *d_stream, const FrameRec *
     }
     const uint32_t warps = (n_frames + 31u) / 32u;
     // the deep ring (64 entries: a refill every other body never runs dry) while one wave of it holds every frame
+    g_pass_a_launches[warps <= (uint32_t)sms * 14u ? kPassANarrow64 : kPassANarrow32].fetch_add(1, std::memory_order_relaxed);
     if (warps <= (uint32_t)sms * 14u)
         k_parse_frames_narrow<64><<<warps, 32, 0, st>>>(d_stream, d_frames, n_frames, d_scratch, d_subs, d_outs, d_flags, write_samples ? 1 : 0);
     else
@@ -117,6 +118,7 @@ cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frame
     // carry three CTAs (3 warps per scheduler instead of 2) and the whole launch waits 26 % longer for them
     // (sm__cycles_active max 1.77 M vs avg 1.40 M, r02m); 1 212 one-warp CTAs spread the 28 extra warps over 28 SMs.
     constexpr int kStagedThreads = 32;
+    g_pass_a_launches[blocks <= (uint32_t)sms * 4u ? kPassAStaged : kPassAQuad].fetch_add(1, std::memory_order_relaxed);
     if (blocks <= (uint32_t)sms * 4u) {
         const uint32_t warps = (n_frames + kStagedThreads - 1) / kStagedThreads;
         k_parse_frames<StagedSrc<kStagedThreads>><<<warps, kStagedThreads, kStagedRing * kStagedThreads * sizeof(uint32_t), st>>>(
