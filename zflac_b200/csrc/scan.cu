@@ -98,17 +98,20 @@ __device__ __noinline__ bool parse_header_at(const uint8_t *__restrict__ s, uint
 }
 
 // ------------------------------------------------------------------ K1
-// One CTA scans one 64 KB tile as 4 groups of 4 rows of 256 threads x 16 bytes, every global load a
-// coalesced 128-bit vector, four of them in flight per thread. Sync codes are found four bytes at a
-// time with plain integer arithmetic; only the (rare) hits run the full header check. Candidates
-// leave in stream order: per group a warp scan of the four packed row counts, ONE block barrier for
-// the whole tile, one decoupled look-back across tiles. (With 16 KB tiles the two barriers and the
-// look-back per tile were the kernel: barrier stalls 10 per issued instruction, r02g.)
+// One CTA scans one 64 KB tile as 16 rows of 256 threads x 16 bytes, every global load a coalesced 128-bit vector,
+// the loads of the next four rows in flight while four rows are tested.
+//
+// The kernel is a streaming read and was instruction bound (r02z: 70 M warp instructions for 284 MB, 23 % of the HBM
+// peak): every row paid the exact test, per-row counts and five 64-bit shuffle steps of an ordered scan although a
+// candidate turns up once per ~7 KB. Now a row costs a FILTER — four instructions per four stream positions that say
+// whether any byte is 0xFF and followed by a byte >= 0xF8 — and nothing else; a thread whose filter fires (2^-9 per
+// row) runs the exact sync test and the header check (grammar + CRC-8), and a validated header sets ONE BIT in a
+// bitmap of the tile in shared memory. Order comes for free afterwards: thread t owns bits [256 t, 256 t + 256), a
+// block scan of the population counts ranks them, one decoupled look-back across tiles places the tile, and the few
+// headers are parsed once more where they are written.
 constexpr int kScanThreads = 256;
-constexpr int kScanRows = 4;     // rows per group
-constexpr int kScanGroups = 4;   // groups per tile
-constexpr int kScanGroupBytes = kScanThreads * 16 * kScanRows;
-constexpr int kScanTileBytes = kScanGroupBytes * kScanGroups;
+constexpr int kScanRows = 16;
+constexpr int kScanTileBytes = kScanThreads * 16 * kScanRows;  // 65536
 
 constexpr unsigned long long kFlagAgg = 1ull << 62;
 constexpr unsigned long long kFlagPrefix = 2ull << 62;
@@ -116,7 +119,7 @@ constexpr unsigned long long kValueMask = (1ull << 62) - 1;
 
 // 0x80 in every byte i where byte i of cur == 0xFF and byte i of nxt (the following stream byte) is 0xF8 or 0xF9:
 // t has a zero byte exactly there, and ~(((t & 0x7F..) + 0x7F..) | t | 0x7F..) is the exact zero-byte test (no borrow
-// between bytes). Six plain integer instructions per four stream positions.
+// between bytes).
 __device__ __forceinline__ uint32_t sync_hits4(uint32_t cur, uint32_t nxt) {
     const uint32_t t = ~cur | ((nxt | 0x01010101u) ^ 0xF9F9F9F9u);
     return ~(((t & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | t | 0x7F7F7F7Fu);
@@ -124,112 +127,161 @@ __device__ __forceinline__ uint32_t sync_hits4(uint32_t cur, uint32_t nxt) {
 __device__ __forceinline__ uint32_t hits_to_mask4(uint32_t z) {  // 4-bit mask, bit i <-> byte i
     return (((z >> 7) & 0x01010101u) * 0x01020408u) >> 24;
 }
+// Filter: non-zero (after the caller's & 0x80808080) iff some byte i has cur == 0xFF and nxt in {0xF8, 0xF9}: the sync
+// code. t = cur & ((nxt | 1) ^ 6) has an 0xFF byte exactly there ((0xF9 ^ 0x06) == 0xFF), and (~t - 0x01..) & t & 0x80..
+// is non-zero iff ~t has a zero byte. Four instructions per four stream positions (c1 / c6 live in registers so that
+// (nxt | c1) ^ c6 is one LOP3); WHICH byte it was is left to the slow path (borrows may flag bytes above the real one).
+__device__ __forceinline__ uint32_t sync_filter4(uint32_t cur, uint32_t nxt, uint32_t c1, uint32_t c6) {
+    const uint32_t t = cur & ((nxt | c1) ^ c6);
+    return (0u - (t + 0x01010102u)) & t;
+}
 
-__global__ void __launch_bounds__(kScanThreads, 4)
+// The exact test + header check of one 16-byte chunk whose filter fired (rare): sets the bit of every validated header.
+// Chunks are queued by the scanning threads and checked afterwards, one chunk per thread, so that a hit costs the
+// scanning warp a handful of instructions instead of a header check executed for one lane of it.
+static __device__ __noinline__ void scan_check_chunk(const uint8_t *__restrict__ s, uint64_t pos, uint64_t tile_base, uint64_t scan_begin,
+                                                     uint64_t scan_end, uint64_t len, uint32_t *bits) {
+    uint32_t w[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < 17 && pos + i < len; ++i) w[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+    const uint32_t z0 = sync_hits4(w[0], __funnelshift_r(w[0], w[1], 8)), z1 = sync_hits4(w[1], __funnelshift_r(w[1], w[2], 8));
+    const uint32_t z2 = sync_hits4(w[2], __funnelshift_r(w[2], w[3], 8)), z3 = sync_hits4(w[3], __funnelshift_r(w[3], w[4], 8));
+    uint32_t raw = hits_to_mask4(z0) | (hits_to_mask4(z1) << 4) | (hits_to_mask4(z2) << 8) | (hits_to_mask4(z3) << 12);
+    while (raw) {
+        const int b = __ffs(raw) - 1;
+        raw &= raw - 1;
+        const uint64_t p = pos + b;
+        Cand c;
+        if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) {
+            const uint32_t rel = (uint32_t)(p - tile_base);
+            atomicOr(&bits[rel >> 5], 1u << (rel & 31u));
+        }
+    }
+}
+constexpr uint32_t kScanQueue = 512;  // chunks a tile can queue (a tile of audio has ~10 frames and ~2 chance matches); beyond: checked in place
+
+__global__ void __launch_bounds__(kScanThreads, 3)
 k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_end, uint64_t len, uint64_t tile0, uint32_t n_tiles,
             Cand *__restrict__ out, uint32_t cap, uint32_t *__restrict__ total_out,
             unsigned long long *__restrict__ tile_state, uint32_t *__restrict__ ticket) {
     __shared__ uint32_t s_tile;
-    __shared__ unsigned long long s_warp_sum[kScanGroups][kScanThreads / 32];  // 4 x 16-bit row counts per warp and group
+    __shared__ __align__(16) uint32_t s_bits[kScanTileBytes / 32];  // one bit per byte of the tile: a validated header starts there
+    __shared__ uint32_t s_wsum[kScanThreads / 32];
     __shared__ unsigned long long s_base;
-    __shared__ Cand s_first[kScanThreads];
+    __shared__ uint32_t s_nq;
+    __shared__ uint16_t s_queue[kScanQueue];  // chunk index (tile byte / 16) of every chunk whose filter fired
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(ticket, 1u);  // tiles start in order: look-back below cannot deadlock
+    if (tid == 0) {
+        s_tile = atomicAdd(ticket, 1u);  // tiles start in order: look-back below cannot deadlock
+        s_nq = 0;
+    }
+    uint32_t c1, c6;  // filter constants the compiler must keep in registers (see sync_filter4)
+    asm("mov.b32 %0, 0x01010101;" : "=r"(c1));
+    asm("mov.b32 %0, 0x06060606;" : "=r"(c6));
+    {
+        uint4 *z = reinterpret_cast<uint4 *>(s_bits) + tid * 2;  // thread t clears the eight words it will own
+        z[0] = make_uint4(0, 0, 0, 0);
+        z[1] = make_uint4(0, 0, 0, 0);
+    }
     __syncthreads();
     const uint32_t tile = s_tile;
     if (tile >= n_tiles) return;
     const uint64_t tile_base = tile0 + (uint64_t)tile * kScanTileBytes;
     const bool interior = tile_base + kScanTileBytes + 16 <= len;
 
-    uint64_t first_off = ~0ull;  // stream offset of the candidate kept in s_first[tid]
-    uint32_t valid[kScanGroups][kScanRows / 2];   // per row a 16-bit mask of validated candidates in my 16 bytes, two rows per word
-    unsigned long long incl[kScanGroups];         // inclusive warp scan of the packed row counts (16 bits per row)
-    unsigned long long mine[kScanGroups];
+    auto queue_chunk = [&](uint64_t pos) {  // rare
+        const uint32_t q = atomicAdd(&s_nq, 1u);
+        if (q < kScanQueue) s_queue[q] = (uint16_t)((pos - tile_base) >> 4);
+        else scan_check_chunk(s, pos, tile_base, scan_begin, scan_end, len, s_bits);
+    };
+    if (interior) {  // the whole tile and the byte after it are inside the stream: no length checks
+        const uint4 *src = reinterpret_cast<const uint4 *>(s + tile_base) + tid;
+        const uint8_t *edge = s + tile_base + (uint64_t)tid * 16 + 16;  // lane 31: the byte after the warp's 512 (the next warp's first)
+        uint4 v[4], nx[4];
+        uint32_t e[4] = {0, 0, 0, 0}, ne[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int g = 0; g < kScanGroups; ++g) {
-        const uint64_t group_base = tile_base + (uint64_t)g * kScanGroupBytes;
-        // ---- all loads of the group first (4 independent 128-bit loads in flight per thread)
-        uint4 v[kScanRows];
-        if (interior) {  // the whole tile and the byte after it are inside the stream: no per-row length checks
-            const uint4 *src = reinterpret_cast<const uint4 *>(s + group_base) + tid;
+        for (int r = 0; r < 4; ++r) {
+            v[r] = __ldg(src + r * kScanThreads);
+            if (lane == 31) e[r] = __ldg(edge + r * (kScanThreads * 16));
+        }
+#pragma unroll 1
+        for (int r0 = 0; r0 < kScanRows; r0 += 4) {
+            if (r0 + 4 < kScanRows) {  // the next four rows (and their edge bytes) are on their way while these four are tested
 #pragma unroll
-            for (int r = 0; r < kScanRows; ++r) v[r] = __ldg(src + r * kScanThreads);
-        } else {
-#pragma unroll
-            for (int r = 0; r < kScanRows; ++r) {
-                const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-                v[r] = make_uint4(0, 0, 0, 0);
-                if (pos + 16 <= len) {
-                    v[r] = __ldg(reinterpret_cast<const uint4 *>(s + pos));
-                } else if (pos < len) {  // stream tail: bytes past len read as zero
-                    uint32_t t[4] = {0, 0, 0, 0};
-                    for (int i = 0; i < 16 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
-                    v[r] = make_uint4(t[0], t[1], t[2], t[3]);
+                for (int r = 0; r < 4; ++r) {
+                    nx[r] = __ldg(src + (r0 + 4 + r) * kScanThreads);
+                    if (lane == 31) ne[r] = __ldg(edge + (r0 + 4 + r) * (kScanThreads * 16));
                 }
             }
-        }
-        unsigned long long counts = 0;   // 16 bits per row
-        valid[g][0] = valid[g][1] = 0;
 #pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1);  // the byte after my 16: the next lane's first
+                if (lane == 31) nb = e[r];
+                const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
+                const uint32_t f = (sync_filter4(w0, __funnelshift_r(w0, w1, 8), c1, c6) | sync_filter4(w1, __funnelshift_r(w1, w2, 8), c1, c6) |
+                                    sync_filter4(w2, __funnelshift_r(w2, w3, 8), c1, c6) | sync_filter4(w3, __funnelshift_r(w3, nb, 8), c1, c6)) &
+                                   0x80808080u;
+                if (f) queue_chunk(tile_base + (uint64_t)(r0 + r) * (kScanThreads * 16) + (uint64_t)tid * 16);
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                v[r] = nx[r];
+                e[r] = ne[r];
+            }
+        }
+    } else {
+#pragma unroll 1
         for (int r = 0; r < kScanRows; ++r) {
-            const uint64_t pos = group_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-            // the byte after my 16: the next lane's first byte; lane 31 fetches it (L1/L2 hit: a neighbour loads that line)
-            uint32_t nb;
-            if (interior) {  // every lane reads it (an L1 hit: the neighbour loaded that line): no shuffle, no one-lane branch
-                nb = __ldg(s + pos + 16);
-            } else {
-                nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1) & 0xFFu;
-                if (lane == 31) nb = (pos + 16 < len) ? s[pos + 16] : 0u;
+            const uint64_t pos = tile_base + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (pos + 16 <= len) {
+                v = __ldg(reinterpret_cast<const uint4 *>(s + pos));
+            } else if (pos < len) {  // stream tail: bytes past len read as zero
+                uint32_t t[4] = {0, 0, 0, 0};
+                for (int i = 0; i < 16 && pos + i < len; ++i) t[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+                v = make_uint4(t[0], t[1], t[2], t[3]);
             }
-            const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
-            const uint32_t z0 = sync_hits4(w0, __funnelshift_r(w0, w1, 8)), z1 = sync_hits4(w1, __funnelshift_r(w1, w2, 8));
-            const uint32_t z2 = sync_hits4(w2, __funnelshift_r(w2, w3, 8)), z3 = sync_hits4(w3, __funnelshift_r(w3, nb, 8));
-            uint32_t raw = 0;
-            if (z0 | z1 | z2 | z3)  // a sync pattern in my 16 bytes: 2^-11; in the warp's 512 bytes: 1.6 %
-                raw = hits_to_mask4(z0) | (hits_to_mask4(z1) << 4) | (hits_to_mask4(z2) << 8) | (hits_to_mask4(z3) << 12);
-            uint32_t ok = 0;
-            while (raw) {  // rare: ~2^-15 per byte on compressed data
-                const int b = __ffs(raw) - 1;
-                raw &= raw - 1;
-                const uint64_t p = pos + b;
-                Cand c;
-                if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) {
-                    ok |= 1u << b;
-                    if (first_off == ~0ull) {  // almost every thread that has a candidate has exactly one: keep it for the output pass
-                        first_off = p;
-                        s_first[tid] = c;
-                    }
-                }
-            }
-            valid[g][r >> 1] |= ok << (16 * (r & 1));
-            counts |= (unsigned long long)__popc(ok) << (16 * r);
+            uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v.x, 1);
+            if (lane == 31) nb = (pos + 16 < len) ? s[pos + 16] : 0u;
+            const uint32_t f = (sync_filter4(v.x, __funnelshift_r(v.x, v.y, 8), c1, c6) | sync_filter4(v.y, __funnelshift_r(v.y, v.z, 8), c1, c6) |
+                                sync_filter4(v.z, __funnelshift_r(v.z, v.w, 8), c1, c6) | sync_filter4(v.w, __funnelshift_r(v.w, nb, 8), c1, c6)) &
+                               0x80808080u;
+            if (f) queue_chunk(pos);
         }
-        // ---- warp-level inclusive scan of the four row counts at once (row counts <= 4096 fit 16 bits)
-        unsigned long long in = counts;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, in, d);
-            if (lane >= d) in += t;
-        }
-        if (lane == 31) s_warp_sum[g][warp] = in;
-        incl[g] = in;
-        mine[g] = counts;
+    }
+    __syncthreads();
+    // ---- the queued chunks, one per thread: exact sync test, header grammar, CRC-8 -> bits
+    {
+        const uint32_t nq = s_nq < kScanQueue ? s_nq : kScanQueue;
+        for (uint32_t q = tid; q < nq; q += kScanThreads)
+            scan_check_chunk(s, tile_base + (uint64_t)s_queue[q] * 16, tile_base, scan_begin, scan_end, len, s_bits);
     }
     __syncthreads();
 
-    // ---- candidates in the whole tile (what the look-back publishes)
-    uint32_t running = 0;
-#pragma unroll
-    for (int g = 0; g < kScanGroups; ++g) {
-        unsigned long long all = 0;
-#pragma unroll
-        for (int w = 0; w < kScanThreads / 32; ++w) all += s_warp_sum[g][w];
-        running += (uint32_t)(all & 0xFFFFu) + (uint32_t)((all >> 16) & 0xFFFFu) + (uint32_t)((all >> 32) & 0xFFFFu) + (uint32_t)(all >> 48);
+    // ---- ranks: thread t owns tile bytes [256 t, 256 t + 256) = bitmap words [8 t, 8 t + 8)
+    uint32_t mine[8];
+    {
+        const uint4 a = reinterpret_cast<const uint4 *>(s_bits)[tid * 2], b = reinterpret_cast<const uint4 *>(s_bits)[tid * 2 + 1];
+        mine[0] = a.x; mine[1] = a.y; mine[2] = a.z; mine[3] = a.w;
+        mine[4] = b.x; mine[5] = b.y; mine[6] = b.z; mine[7] = b.w;
     }
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) cnt += __popc(mine[k]);
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
 
     // ---- decoupled look-back by warp 0: tile t publishes its aggregate, then 32 predecessors at a
     // time are inspected until one of them carries an inclusive prefix
     if (warp == 0) {
+        uint32_t running = 0;
+#pragma unroll
+        for (int w = 0; w < kScanThreads / 32; ++w) running += s_wsum[w];
         unsigned long long base = 0;
         volatile unsigned long long *st = tile_state;
         if (tile > 0) {
@@ -258,35 +310,21 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
         }
     }
     __syncthreads();
-    const unsigned long long base = s_base;
+    if (cnt == 0) return;
 
-    // ---- ranks inside the tile: groups in order, rows in order inside a group, threads in order inside a row
-    uint32_t before = 0;  // candidates in earlier groups / rows of this tile
-#pragma unroll
-    for (int g = 0; g < kScanGroups; ++g) {
-        unsigned long long warp_off = 0, all = 0;
-#pragma unroll
-        for (int w = 0; w < kScanThreads / 32; ++w) {
-            const unsigned long long t = s_warp_sum[g][w];
-            if (w < warp) warp_off += t;
-            all += t;
-        }
-        const unsigned long long excl = warp_off + incl[g] - mine[g];
-#pragma unroll
-        for (int r = 0; r < kScanRows; ++r) {
-            uint32_t ok = (valid[g][r >> 1] >> (16 * (r & 1))) & 0xFFFFu;
-            unsigned long long slot = base + before + (uint32_t)((excl >> (16 * r)) & 0xFFFFu);
-            before += (uint32_t)((all >> (16 * r)) & 0xFFFFu);
-            const uint64_t pos = tile_base + (uint64_t)g * kScanGroupBytes + (uint64_t)r * (kScanThreads * 16) + (uint64_t)tid * 16;
-            while (ok) {
-                const int b = __ffs(ok) - 1;
-                ok &= ok - 1;
-                Cand c;
-                if (first_off == pos + b) c = s_first[tid];
-                else parse_header_at(s, pos + b, len, c);
-                if (slot < cap) out[slot] = c;
-                ++slot;
-            }
+    // ---- the tile's headers in stream order
+    unsigned long long slot = s_base + (incl - cnt);
+    for (int w = 0; w < warp; ++w) slot += s_wsum[w];
+#pragma unroll 1
+    for (int k = 0; k < 8; ++k) {
+        uint32_t m = mine[k];
+        while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            Cand c;
+            parse_header_at(s, tile_base + (uint64_t)tid * 256 + (uint64_t)k * 32 + b, len, c);  // validated above
+            if (slot < cap) out[slot] = c;
+            ++slot;
         }
     }
 }
