@@ -58,6 +58,24 @@ def build(force: bool = False) -> str:
 
 
 _lib = None
+_lib_timed = None
+_LIB_TIMED_PATH = os.path.join(_HERE, "_build", "libzflac_oracle_timed.so")
+
+
+def lib_timed():
+    """The build bench.py TIMES as the CPU arm (-DZO_TIMED: no overflow bookkeeping, LPC loop instantiated per order like
+    the reference's comptime unroll). Same entry points and results as lib(); tests/test_oracle_golden.py pins it too."""
+    global _lib_timed
+    if _lib_timed is None:
+        build()
+        if not os.path.exists(_LIB_TIMED_PATH) or os.path.getmtime(_LIB_TIMED_PATH) < os.path.getmtime(os.path.join(_HERE, "zflac_oracle.cpp")):
+            subprocess.run(["make", "-C", _HERE, "-B"], check=True, capture_output=True)
+        _lib_timed = C.CDLL(_LIB_TIMED_PATH)
+        _lib_timed.zo_decode.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.POINTER(_Result)]
+        _lib_timed.zo_decode.restype = C.c_int
+        _lib_timed.zo_free.argtypes = [C.POINTER(_Result)]
+        _lib_timed.zo_free.restype = None
+    return _lib_timed
 
 
 def lib():
@@ -111,12 +129,14 @@ def _as_buffer(data):
     return arr
 
 
-def decode(data, trace_frames: bool = False, keep_on_md5_mismatch: bool = False, copy_samples: bool = True) -> OracleResult:
-    """Oracle twin of zflac.decode(allocator, reader) (zflac.zig:217)."""
+def decode(data, trace_frames: bool = False, keep_on_md5_mismatch: bool = False, copy_samples: bool = True,
+           timed: bool = False) -> OracleResult:
+    """Oracle twin of zflac.decode(allocator, reader) (zflac.zig:217). timed: the -DZO_TIMED build (lib_timed())."""
     arr = _as_buffer(data)
     res = _Result()
     flags = (FLAG_TRACE_FRAMES if trace_frames else 0) | (FLAG_KEEP_ON_MD5_MISMATCH if keep_on_md5_mismatch else 0)
-    status = lib().zo_decode(arr.ctypes.data, arr.size, flags, C.byref(res))
+    the_lib = lib_timed() if timed else lib()
+    status = the_lib.zo_decode(arr.ctypes.data, arr.size, flags, C.byref(res))
     out = OracleResult(status=status, error=STATUS_NAMES.get(status, f"Unknown({status})"),
                        overflow_flag=res.overflow_flag, md5_computed=bytes(res.md5_computed),
                        md5_streaminfo=bytes(res.md5_streaminfo), audio_offset=res.audio_offset,
@@ -137,7 +157,7 @@ def decode(data, trace_frames: bool = False, keep_on_md5_mismatch: bool = False,
             nf = int(res.n_frames)
             fb = (C.c_uint8 * (nf * _FRAME_DTYPE.itemsize)).from_address(C.addressof(res.frames.contents)) if nf else b""
             out.frames = np.frombuffer(fb, dtype=_FRAME_DTYPE).copy() if nf else np.zeros(0, dtype=_FRAME_DTYPE)
-    lib().zo_free(C.byref(res))
+    the_lib.zo_free(C.byref(res))
     return out
 
 

@@ -69,3 +69,24 @@ def test_truncated_stream_errors():
     assert oracle.decode(b"fLaX" + data[4:]).error == "InvalidSignature"
     # total sample count is known, so running out of bytes mid-stream is EndOfStream (zflac.zig:344)
     assert oracle.decode(data[: len(data) // 2]).error == "EndOfStream"
+
+
+@pytest.mark.parametrize("entry", corpus_entries(), ids=corpus_ids())
+def test_timed_build_is_the_same_decoder(entry):
+    """The -DZO_TIMED build (what bench.py times as the CPU arm: no overflow bookkeeping, LPC loop instantiated per order
+    like the reference's comptime unroll) against the same golden vectors and the instrumented build."""
+    data = corpus_bytes(entry)
+    a, b = oracle.decode(data), oracle.decode(data, timed=True)
+    assert a.error == b.error == (entry["expect_error"] or "OK")
+    if a.error == "OK":
+        assert hashlib.sha256(b.samples.tobytes()).hexdigest() == entry["pcm_sha256"]
+        assert np.array_equal(a.samples, b.samples) and a.md5_computed == b.md5_computed
+        assert (a.channels, a.sample_rate, a.bits_per_sample) == (b.channels, b.sample_rate, b.bits_per_sample)
+
+
+def test_timed_build_on_the_bench_workloads():
+    from tools import flacgen as fg
+    for p in (fg.c2(4.0), fg.c3(0.5), fg.c5_file(3)):
+        s = fg.generate(p, want_pcm=True)
+        r = oracle.decode(s.flac, timed=True)
+        assert r.error == "OK" and np.array_equal(r.samples, s.pcm)
