@@ -8,7 +8,7 @@
  *
  * and its result type DecodedFLAC { channels, sample_rate, bits_per_sample,
  * samples: union{s8,s16,s32}, _samples_backing } (src/zflac.zig:12-28). A Zig
- * shim (zig/zflac.zig) keeps that signature and calls the
+ * shim (zig/zflac.zig + zig/build.zig.fragment) keeps that signature and calls the
  * functions below; nothing in the signatures is a CUDA or torch type.
  *
  * Everything behind these calls runs on the GPU (sm_100a kernels). There is no
@@ -143,6 +143,13 @@ void zflacb200_close(zflacb200_stream *s);
 int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *opt,
                      void *dst, size_t dst_capacity, zflacb200_info *info);
 
+/* Host only, no device: the bytes of PCM STREAMINFO promises (total samples x channels x container), so that a caller can
+ * allocate `dst` for zflacb200_decode() up front the way the reference sizes its buffer (src/zflac.zig:329-334). *bytes = 0
+ * when the stream states no total (:329 falls back to 4096 samples and grows) or the walk over the metadata fails — the
+ * caller then takes the two-phase open / read path, which also reports the error. A stream may decode to MORE than it
+ * states (:394-402); zflacb200_decode() then answers ZFLACB200_OUT_OF_MEMORY with info.pcm_bytes set. */
+int zflacb200_pcm_bound(const uint8_t *data, size_t len, uint64_t *bytes);
+
 /* File-parallel batch (BASELINE config 5): n independent streams decoded in ONE pipeline pass
  * on one device — one sync scan over the packed bytes, one K2 / K3 launch over the frames of all
  * streams, one MD5 chain per stream running side by side. Each stream is what one call of the
@@ -275,6 +282,41 @@ typedef struct zflacb200_span {
 } zflacb200_span;
 int zflacb200_vorbis_comments(const uint8_t *data, size_t len, zflacb200_span *vendor, zflacb200_span *dst, size_t capacity,
                               size_t *n_comments);
+
+/* PICTURE blocks (RFC 9639 8.8), one entry per block in stream order: the fixed fields and the byte spans of the MIME
+ * type, the description (UTF-8) and the picture data inside `data`. A block whose internal lengths overrun it is
+ * InvalidMetadataHeader (the reference skips the block unread, src/zflac.zig:243-247: decode() is not affected). */
+typedef struct zflacb200_picture {
+    uint32_t picture_type; /* 0..20, 3 = front cover */
+    uint32_t width, height, depth, colors;
+    uint32_t pad;
+    zflacb200_span mime, description, image;
+} zflacb200_picture;
+int zflacb200_pictures(const uint8_t *data, size_t len, zflacb200_picture *dst, size_t capacity, size_t *n_pictures);
+
+/* CUESHEET (RFC 9639 8.7): the sheet's fixed fields and its tracks; index points of track t are
+ * indices[tracks[t].first_index .. + tracks[t].n_indices). Offsets are in samples (per channel). */
+typedef struct zflacb200_cuesheet {
+    char media_catalog_number[129]; /* NUL-terminated */
+    uint8_t is_cd;
+    uint8_t pad[6];
+    uint64_t lead_in_samples;
+    uint32_t n_tracks, n_indices;
+} zflacb200_cuesheet;
+typedef struct zflacb200_cue_track {
+    uint64_t offset_samples;
+    char isrc[13]; /* NUL-terminated */
+    uint8_t number, is_audio, pre_emphasis;
+    uint32_t first_index, n_indices;
+} zflacb200_cue_track;
+typedef struct zflacb200_cue_index {
+    uint64_t offset_samples; /* relative to the track's offset */
+    uint32_t number;
+    uint32_t pad;
+} zflacb200_cue_index;
+/* *found = 0 when the stream has no CUESHEET block. tracks / indices may be NULL (counts only, in *sheet). */
+int zflacb200_cuesheet_read(const uint8_t *data, size_t len, zflacb200_cuesheet *sheet, zflacb200_cue_track *tracks,
+                            size_t track_capacity, zflacb200_cue_index *indices, size_t index_capacity, int *found);
 
 /* Frame index of an opened stream (diagnostics / tests): one entry per decoded frame. */
 typedef struct zflacb200_frame {

@@ -98,3 +98,82 @@ def test_head_errors_in_the_reference_order(z):
     assert m["comments_error"] == "InvalidMetadataHeader" and m["audio_offset"] == 54
     m = z.metadata(b"fLaC" + bytes([0x80, 0, 0, 99]) + bytes(34))  # Q13: STREAMINFO is 34 bytes whatever its length field says
     assert m["audio_offset"] == 42 and m["blocks"][0]["length"] == 99 and m["blocks"][0]["stored_bytes"] == 34
+
+
+def _py_pictures(data: bytes):
+    blocks, _ = py_walk(data)
+    out = []
+    for t, off, _length, stored, _last in blocks:
+        if t != 6:
+            continue
+        p = off
+        ptype, mlen = struct.unpack(">II", data[p: p + 8]); p += 8
+        mime = data[p: p + mlen]; p += mlen
+        (dlen,) = struct.unpack(">I", data[p: p + 4]); p += 4
+        desc = data[p: p + dlen]; p += dlen
+        w, h, d, c, ilen = struct.unpack(">IIIII", data[p: p + 20]); p += 20
+        assert p + ilen <= off + stored
+        out.append((ptype, mime, desc, w, h, d, c, p, ilen))
+    return out
+
+
+@pytest.mark.parametrize("entry", [e for e in corpus_entries() if not e["expect_error"]],
+                         ids=[i for i, e in zip(corpus_ids(), corpus_entries()) if not e["expect_error"]])
+def test_pictures_and_cuesheet(z, entry):
+    """PICTURE (subset 56-59: JPG / PNG / GIF / AVIF) and CUESHEET against an independent walk; the image bytes carry
+    their format's magic number, so the spans point at real pictures."""
+    data = corpus_bytes(entry)
+    want = _py_pictures(data)
+    got = z.pictures(data)
+    assert len(got) == len(want)
+    for g, (ptype, mime, desc, w, h, d, c, ioff, ilen) in zip(got, want):
+        assert (g["picture_type"], g["width"], g["height"], g["depth"], g["colors"]) == (ptype, w, h, d, c)
+        assert g["mime"].encode() == mime and g["description"].encode("utf-8") == desc and g["image"] == (ioff, ilen)
+        magic = {"image/jpeg": b"\xff\xd8\xff", "image/png": b"\x89PNG", "image/gif": b"GIF8"}.get(g["mime"])
+        if magic:
+            assert data[ioff: ioff + len(magic)] == magic
+    if entry["group"] == "subset" and entry["id"] in ("56", "57", "58", "59"):
+        assert len(got) >= 1
+    blocks, _ = py_walk(data)
+    sheet = z.cuesheet(data)
+    assert (sheet is not None) == any(b[0] == 5 for b in blocks)
+
+
+def test_cuesheet_synthetic(z):
+    """No corpus file available here carries a CUESHEET: build one (RFC 9639 8.7) in front of a real stream."""
+    e = next(x for x in corpus_entries() if (x["group"], x["id"]) == ("subset", "01"))
+    data = corpus_bytes(e)
+    tracks = [(0, 1, b"USRC17607839", 0x00, [(0, 1)]), (441000, 2, b"\0" * 12, 0x40, [(0, 0), (588, 1)]), (882000, 170, b"\0" * 12, 0x00, [])]
+    body = b"1234567890123".ljust(128, b"\0") + struct.pack(">Q", 88200) + bytes([0x80]) + bytes(258) + bytes([len(tracks)])
+    for off, num, isrc, flags, idx in tracks:
+        body += struct.pack(">QB", off, num) + isrc + bytes([flags]) + bytes(13) + bytes([len(idx)])
+        for ioff, inum in idx:
+            body += struct.pack(">QB", ioff, inum) + bytes(3)
+    # insert after STREAMINFO (clear nothing: STREAMINFO is not the last block in subset/01)
+    cue = bytes([5]) + len(body).to_bytes(3, "big") + body
+    assert not data[4] >> 7
+    new = data[:42] + cue + data[42:]
+    sheet = z.cuesheet(new)
+    assert sheet["media_catalog_number"] == "1234567890123" and sheet["is_cd"] and sheet["lead_in_samples"] == 88200
+    assert [(t["offset_samples"], t["number"], t["is_audio"], t["pre_emphasis"]) for t in sheet["tracks"]] == [
+        (0, 1, True, False), (441000, 2, True, True), (882000, 170, True, False)]
+    assert sheet["tracks"][0]["isrc"] == "USRC17607839"
+    assert sheet["tracks"][1]["indices"] == [dict(offset_samples=0, number=0), dict(offset_samples=588, number=1)]
+    assert z.metadata(new)["audio_offset"] == z.metadata(data)["audio_offset"] + len(cue)
+    with pytest.raises(z.InvalidMetadataHeader):       # track table overruns the block
+        z.cuesheet(data[:42] + bytes([5]) + (400).to_bytes(3, "big") + body[:400] + data[42:])
+
+
+def test_pcm_bound(z):
+    from zflac_b200 import _native
+    import ctypes as C
+    lib = _native.load()
+    for e in corpus_entries():
+        data = corpus_bytes(e)
+        arr = np.frombuffer(data, dtype=np.uint8)
+        b = C.c_uint64(123)
+        assert lib.zflacb200_pcm_bound(arr.ctypes.data, arr.size, C.byref(b)) == 0
+        if e["expect_error"] in ("InvalidSignature", "InvalidMetadataHeader", "MissingStreaminfo"):
+            assert b.value == 0
+        elif not e["expect_error"] and b.value:
+            assert b.value <= e["n_samples"] * e["container_bytes"]  # never more than what decodes (faulty/05 decodes more)

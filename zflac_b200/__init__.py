@@ -256,6 +256,46 @@ def metadata(data) -> dict:
     return out
 
 
+def pictures(data) -> list:
+    """Additive, host only: the PICTURE blocks (RFC 9639 8.8) the reference skips (src/zflac.zig:243-247). `image` is a
+    (offset, length) span of the picture's bytes inside `data`."""
+    lib = _native.load()
+    arr = _as_u8(data)
+    n = C.c_size_t()
+    st = lib.zflacb200_pictures(arr.ctypes.data, arr.size, None, 0, C.byref(n))
+    if st != 0:
+        _raise(st)
+    pics = (_native.Picture * max(n.value, 1))()
+    lib.zflacb200_pictures(arr.ctypes.data, arr.size, pics, n.value, C.byref(n))
+    raw = arr.tobytes() if n.value else b""
+    return [dict(picture_type=p.picture_type, width=p.width, height=p.height, depth=p.depth, colors=p.colors,
+                 mime=raw[p.mime.offset: p.mime.offset + p.mime.length].decode("ascii", "replace"),
+                 description=raw[p.description.offset: p.description.offset + p.description.length].decode("utf-8", "replace"),
+                 image=(p.image.offset, p.image.length)) for p in pics[: n.value]]
+
+
+def cuesheet(data):
+    """Additive, host only: the CUESHEET block (RFC 9639 8.7), or None when the stream has none."""
+    lib = _native.load()
+    arr = _as_u8(data)
+    sheet, found = _native.CueSheet(), C.c_int()
+    st = lib.zflacb200_cuesheet_read(arr.ctypes.data, arr.size, C.byref(sheet), None, 0, None, 0, C.byref(found))
+    if st != 0:
+        _raise(st)
+    if not found.value:
+        return None
+    tracks = (_native.CueTrack * max(sheet.n_tracks, 1))()
+    idx = (_native.CueIndex * max(sheet.n_indices, 1))()
+    lib.zflacb200_cuesheet_read(arr.ctypes.data, arr.size, C.byref(sheet), tracks, sheet.n_tracks, idx, sheet.n_indices, C.byref(found))
+    return dict(media_catalog_number=sheet.media_catalog_number.decode("ascii", "replace"), is_cd=bool(sheet.is_cd),
+                lead_in_samples=sheet.lead_in_samples,
+                tracks=[dict(offset_samples=t.offset_samples, number=t.number, isrc=t.isrc.decode("ascii", "replace"),
+                             is_audio=bool(t.is_audio), pre_emphasis=bool(t.pre_emphasis),
+                             indices=[dict(offset_samples=i.offset_samples, number=i.number)
+                                      for i in idx[t.first_index: t.first_index + t.n_indices]])
+                        for t in tracks[: sheet.n_tracks]])
+
+
 class DeviceStream:
     """A decoded stream whose PCM stays in HBM (zflacb200_open with ZFLACB200_INPUT_ON_DEVICE)."""
 

@@ -20,11 +20,11 @@ MD5_ON_DEVICE = 0x100
 EXPORTS = [
     "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown",
     "zflacb200_status_name", "zflacb200_last_error", "zflacb200_kernel_launches", "zflacb200_pass_a_launches", "zflacb200_open", "zflacb200_read",
-    "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_frames", "zflacb200_batch_open",
+    "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_pcm_bound", "zflacb200_frames", "zflacb200_batch_open",
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
     "zflacb200_batch_close", "zflacb200_batch_pcm_bound", "zflacb200_batch_decode",
     "zflacb200_decode_range", "zflacb200_stitch", "zflacb200_open_frames",
-    "zflacb200_format_bytes", "zflacb200_read_as", "zflacb200_metadata", "zflacb200_seektable", "zflacb200_vorbis_comments",
+    "zflacb200_format_bytes", "zflacb200_read_as", "zflacb200_metadata", "zflacb200_seektable", "zflacb200_vorbis_comments", "zflacb200_pictures", "zflacb200_cuesheet_read",
 ]
 
 
@@ -60,6 +60,25 @@ class SeekPoint(C.Structure):
 
 class Span(C.Structure):
     _fields_ = [("offset", C.c_uint64), ("length", C.c_uint64)]
+
+
+class Picture(C.Structure):
+    _fields_ = [("picture_type", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32), ("depth", C.c_uint32),
+                ("colors", C.c_uint32), ("pad", C.c_uint32), ("mime", Span), ("description", Span), ("image", Span)]
+
+
+class CueSheet(C.Structure):
+    _fields_ = [("media_catalog_number", C.c_char * 129), ("is_cd", C.c_uint8), ("pad", C.c_uint8 * 6),
+                ("lead_in_samples", C.c_uint64), ("n_tracks", C.c_uint32), ("n_indices", C.c_uint32)]
+
+
+class CueTrack(C.Structure):
+    _fields_ = [("offset_samples", C.c_uint64), ("isrc", C.c_char * 13), ("number", C.c_uint8), ("is_audio", C.c_uint8),
+                ("pre_emphasis", C.c_uint8), ("first_index", C.c_uint32), ("n_indices", C.c_uint32)]
+
+
+class CueIndex(C.Structure):
+    _fields_ = [("offset_samples", C.c_uint64), ("number", C.c_uint32), ("pad", C.c_uint32)]
 
 
 class Frame(C.Structure):
@@ -111,6 +130,13 @@ def load():
     lib.zflacb200_vorbis_comments.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Span), C.POINTER(Span), C.c_size_t,
                                               C.POINTER(C.c_size_t)]
     lib.zflacb200_vorbis_comments.restype = C.c_int
+    lib.zflacb200_pictures.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(Picture), C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.zflacb200_pictures.restype = C.c_int
+    lib.zflacb200_cuesheet_read.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(CueSheet), C.POINTER(CueTrack), C.c_size_t,
+                                            C.POINTER(CueIndex), C.c_size_t, C.POINTER(C.c_int)]
+    lib.zflacb200_cuesheet_read.restype = C.c_int
+    lib.zflacb200_pcm_bound.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]
+    lib.zflacb200_pcm_bound.restype = C.c_int
     lib.zflacb200_device_pcm.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
     lib.zflacb200_device_pcm.restype = C.c_int
     lib.zflacb200_close.argtypes = [C.c_void_p]

@@ -2277,6 +2277,23 @@ int zflacb200_decode(const uint8_t *data, size_t len, const zflacb200_options *o
     return r;
 }
 
+int zflacb200_pcm_bound(const uint8_t *data, size_t len, uint64_t *bytes) {
+    if ((!data && len) || !bytes) return ZFLACB200_INVALID_ARGUMENT;
+    *bytes = 0;
+    ByteSource src;
+    src.host = data;
+    src.len = len;
+    Streaminfo si;
+    uint64_t audio_offset = 0;
+    if (parse_metadata(src, si, audio_offset) != ZFLACB200_OK) return ZFLACB200_OK;  // the decode call reports it
+    const uint32_t aligned = (si.depth_m1 + 1 + 7u) & ~7u;
+    const uint64_t cb = aligned == 8 ? 1 : aligned == 16 ? 2 : 4;
+    const uint64_t n = si.total * (si.channels_m1 + 1);
+    if (si.total == 0 || !plausible_total(si.total, len - std::min<uint64_t>(len, audio_offset)) || n >= (1ull << 40)) return ZFLACB200_OK;
+    *bytes = n * cb;
+    return ZFLACB200_OK;
+}
+
 int zflacb200_decode_range(const uint8_t *data, size_t len, const zflacb200_options *opt, uint64_t byte_lo, uint64_t byte_hi,
                            void *dst, size_t dst_capacity, zflacb200_range *range, zflacb200_info *info) {
     ApiScope api(opt_device(opt));
@@ -2638,6 +2655,98 @@ int zflacb200_vorbis_comments(const uint8_t *data, size_t len, zflacb200_span *v
             pos += 4 + (uint64_t)clen;
         }
         *n_comments = got;
+        break;
+    }
+    return ZFLACB200_OK;
+}
+
+int zflacb200_pictures(const uint8_t *data, size_t len, zflacb200_picture *dst, size_t capacity, size_t *n_pictures) {
+    if (!data || !n_pictures) return ZFLACB200_INVALID_ARGUMENT;
+    *n_pictures = 0;
+    std::vector<zflacb200_metadata_block> blocks;
+    uint64_t ao = 0;
+    const int e = walk_metadata(data, len, blocks, ao);
+    if (e != ZFLACB200_OK) return e;
+    size_t got = 0;
+    for (const zflacb200_metadata_block &mb : blocks) {
+        if (mb.type != 6) continue;
+        const uint64_t end = mb.offset + mb.stored_bytes;
+        uint64_t pos = mb.offset;
+        auto be32 = [&](uint32_t &v) {  // big-endian, like every FLAC-native field
+            if (end - pos < 4) return false;
+            v = (uint32_t)be_uint(data + pos, 4);
+            pos += 4;
+            return true;
+        };
+        auto span = [&](zflacb200_span &sp) {
+            uint32_t n = 0;
+            if (!be32(n) || end - pos < n) return false;
+            sp.offset = pos;
+            sp.length = n;
+            pos += n;
+            return true;
+        };
+        zflacb200_picture p;
+        memset(&p, 0, sizeof(p));
+        if (!be32(p.picture_type) || !span(p.mime) || !span(p.description) || !be32(p.width) || !be32(p.height) || !be32(p.depth) ||
+            !be32(p.colors) || !span(p.image))
+            return ZFLACB200_INVALID_METADATA_HEADER;
+        if (dst && got < capacity) dst[got] = p;
+        ++got;
+    }
+    *n_pictures = got;
+    return ZFLACB200_OK;
+}
+
+int zflacb200_cuesheet_read(const uint8_t *data, size_t len, zflacb200_cuesheet *sheet, zflacb200_cue_track *tracks,
+                            size_t track_capacity, zflacb200_cue_index *indices, size_t index_capacity, int *found) {
+    if (!data || !sheet || !found) return ZFLACB200_INVALID_ARGUMENT;
+    *found = 0;
+    memset(sheet, 0, sizeof(*sheet));
+    std::vector<zflacb200_metadata_block> blocks;
+    uint64_t ao = 0;
+    const int e = walk_metadata(data, len, blocks, ao);
+    if (e != ZFLACB200_OK) return e;
+    for (const zflacb200_metadata_block &mb : blocks) {
+        if (mb.type != 5) continue;
+        // 128 catalog + 8 lead-in + 1 flags + 258 reserved + 1 track count = 396 bytes, then per track
+        // 8 offset + 1 number + 12 ISRC + 1 flags + 13 reserved + 1 index count = 36, then per index 8 + 1 + 3 reserved = 12
+        const uint64_t end = mb.offset + mb.stored_bytes;
+        uint64_t pos = mb.offset;
+        if (end - pos < 396) return ZFLACB200_INVALID_METADATA_HEADER;
+        memcpy(sheet->media_catalog_number, data + pos, 128);
+        sheet->media_catalog_number[128] = 0;
+        sheet->lead_in_samples = be_uint(data + pos + 128, 8);
+        sheet->is_cd = data[pos + 136] >> 7;
+        const uint32_t nt = data[pos + 395];
+        pos += 396;
+        uint32_t ni = 0;
+        for (uint32_t t = 0; t < nt; ++t) {
+            if (end - pos < 36) return ZFLACB200_INVALID_METADATA_HEADER;
+            zflacb200_cue_track tr;
+            memset(&tr, 0, sizeof(tr));
+            tr.offset_samples = be_uint(data + pos, 8);
+            tr.number = data[pos + 8];
+            memcpy(tr.isrc, data + pos + 9, 12);
+            tr.is_audio = (data[pos + 21] >> 7) ? 0 : 1;
+            tr.pre_emphasis = (data[pos + 21] >> 6) & 1;
+            tr.first_index = ni;
+            tr.n_indices = data[pos + 35];
+            pos += 36;
+            if (end - pos < 12ull * tr.n_indices) return ZFLACB200_INVALID_METADATA_HEADER;
+            for (uint32_t k = 0; k < tr.n_indices; ++k, pos += 12) {
+                if (indices && ni + k < index_capacity) {
+                    indices[ni + k].offset_samples = be_uint(data + pos, 8);
+                    indices[ni + k].number = data[pos + 8];
+                    indices[ni + k].pad = 0;
+                }
+            }
+            ni += tr.n_indices;
+            if (tracks && t < track_capacity) tracks[t] = tr;
+        }
+        sheet->n_tracks = nt;
+        sheet->n_indices = ni;
+        *found = 1;
         break;
     }
     return ZFLACB200_OK;
