@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--files", type=int, default=10000, help="c5: number of files in the batch (whole job)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling legs (strong_c2r, strong_c5) of the default line")
+    ap.add_argument("--no-pin", action="store_true", help="do not pin the rank's threads to the GPU's NUMA node")
     return ap.parse_args()
 
 
@@ -116,6 +118,52 @@ class ClockSampler:
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
                 "samples": len(sm)}
+
+
+def pin_to_gpu_numa(index: int):
+    """Threads of this rank (and the pinned buffers it allocates afterwards: first touch) onto the CPUs NVML lists as local
+    to the GPU. Returns what was done, for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1 and 64 * w + b < n_cpu}
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if cpus and cpus != allowed:
+            os.sched_setaffinity(0, cpus)
+            return {"pinned": True, "cpus": len(cpus), "of": len(allowed)}
+        return {"pinned": False, "cpus": len(allowed), "why": "the GPU's CPU set is every CPU this process may use (one NUMA node, or a cpuset)"}
+    except Exception as e:  # noqa: BLE001
+        return {"pinned": False, "why": f"{type(e).__name__}: {e}"}
+
+
+def pcie_floor_ms(torch, dev, h_in, n_out_bytes, reps=5):
+    """Concurrent H2D of the stream and D2H of the PCM, nothing else: what the wire alone costs at this N (every rank runs
+    it at the same time; the caller takes the max over ranks)."""
+    d_in = torch.empty(h_in.numel(), dtype=torch.uint8, device=dev)
+    d_out = torch.empty(n_out_bytes, dtype=torch.uint8, device=dev)
+    h_out = torch.empty(n_out_bytes, dtype=torch.uint8).pin_memory()
+    s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    best = None
+    for _ in range(reps + 1):
+        torch.cuda.synchronize()
+        e0, e1, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        s1.wait_event(e0)
+        s2.wait_event(e0)
+        with torch.cuda.stream(s1):
+            d_in.copy_(h_in, non_blocking=True)
+            e1.record()
+        with torch.cuda.stream(s2):
+            h_out.copy_(d_out, non_blocking=True)
+            e2.record()
+        torch.cuda.synchronize()
+        ms = max(e0.elapsed_time(e1), e0.elapsed_time(e2))
+        best = ms if best is None else min(best, ms)
+    return best
 
 
 def kernel_names():
@@ -241,6 +289,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: zflac_b200 has no CPU fallback (use --impl reference for the CPU oracle)")
     torch.cuda.set_device(local_rank)
+    numa = {"pinned": False, "why": "--no-pin"} if args.no_pin else pin_to_gpu_numa(local_rank)  # before any pinned allocation
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -357,6 +406,16 @@ def main():
             ms_e2e_md5, _, _, _ = timed(lambda: step_e2e(True), args.md5_steps, 0)
             e2e["value_with_md5"] = round(world * n_samples / (ms_e2e_md5 * 1e-3) / 1e6, 2)
             e2e["ms_per_step_with_md5"] = round(ms_e2e_md5, 3)
+        # what the wire alone costs at this N: every rank moves its bytes both ways at the same time, nothing else runs
+        barrier()
+        floor = pcie_floor_ms(torch, dev, h_flac, pcm_bytes)
+        if world > 1:
+            tf = torch.tensor([floor], device=dev, dtype=torch.float64)
+            dist.all_reduce(tf, op=dist.ReduceOp.MAX)
+            floor = float(tf.item())
+        e2e["pcie_floor_ms"] = round(floor, 3)
+        e2e["vs_pcie_floor"] = round(ms_e2e / floor, 3)
+        e2e["numa"] = numa
     t_end = time.time()
     sampler.stop()
     # samples cover every timed region of this run (device-resident, MD5-gated, end-to-end)
@@ -378,6 +437,17 @@ def main():
                "build": "-DZO_TIMED (no overflow bookkeeping, LPC per order); instrumented_build_value: the build the tests use",
                "instrumented_build_value": round(ns / dt_i / 1e6, 3),
                "host_cores": os.cpu_count()}
+
+    # ---------------------------------------------------------------- strong scaling: the two shardings north_star names
+    strong = {}
+    if not args.no_strong and args.workload == "c2":
+        from tools import bench_strong
+        del d_flac, h_flac, h_pcm
+        torch.cuda.empty_cache()
+        strong["strong_c2r"] = bench_strong.strong_c2r(rank, world, local_rank, dev, stream, barrier, steps=max(3, args.steps // 2), warmup=2,
+                                                       seconds=args.seconds or 3600.0)
+        strong["strong_c5"] = bench_strong.strong_c5(rank, world, local_rank, dev, stream, barrier, steps=max(3, args.steps // 2), warmup=2,
+                                                     files=args.files)
 
     if rank != 0:
         if world > 1:
@@ -411,6 +481,7 @@ def main():
                             "l2": "inputs larger than L2 (no flush needed)" if flac_bytes > 126 * 2**20 else "input smaller than L2",
                             "generator_s": round(t_gen, 2)},
         "gated": gated,
+        **strong,
         "compressed_gbs": round(world * flac_bytes / (ms_dev * 1e-3) / 1e9, 3),
         "value_with_frame_crc16": round(world * n_samples / (ms_dev_crc * 1e-3) / 1e6, 2), "ms_per_step_with_frame_crc16": round(ms_dev_crc, 4),
         "value_with_md5": round(world * n_samples / (ms_dev_md5 * 1e-3) / 1e6, 2) if ms_dev_md5 else None,

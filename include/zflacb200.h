@@ -75,6 +75,10 @@ typedef enum zflacb200_status {
                                         * thread over the PCM as it lands in host memory (the default for streams >= 256 KiB of PCM;
                                         * batches always hash on the device, one chain per lane) */
 
+#define ZFLACB200_RANGE_INTO_WHOLE 0x200u /* zflacb200_decode_range: `dst` is the buffer of the WHOLE stream's PCM (dst_capacity its size) and the
+                                          * shard is written at its own place, byte range.first_sample * channels * container: the ranks of a
+                                          * sharded decode fill ONE gathered buffer (e.g. shared pinned memory) with no copy afterwards */
+
 typedef struct zflacb200_options {
     uint32_t struct_size; /* sizeof(zflacb200_options) */
     uint32_t flags;       /* 0 = defaults (VERIFY_MD5) */

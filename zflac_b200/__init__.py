@@ -180,13 +180,15 @@ class RangeResult:
 
 
 def decode_range(data, byte_lo: int, byte_hi: int, dst: np.ndarray | None = None, *, device: int = -1,
-                 stream: int | None = None) -> RangeResult:
+                 stream: int | None = None, into_whole: bool = False) -> RangeResult:
     """Decodes the frames of ONE stream whose header starts in [byte_lo, byte_hi) (zflacb200_decode_range). `dst`, if
     given, receives the shard's PCM (bytes; pinned memory for full PCIe speed); else a buffer sized from the byte range's
     share of the stream's PCM (+ two maximum blocks) is allocated."""
     lib = _native.load()
     arr = _as_u8(data)
-    opt = _options(SKIP_MD5, device, stream)
+    if into_whole and dst is None:
+        raise ValueError("into_whole needs the whole stream's PCM buffer as dst")
+    opt = _options(SKIP_MD5 | (_native.RANGE_INTO_WHOLE if into_whole else 0), device, stream)
     info, rng = _native.Info(), _native.Range()
     rng.struct_size = C.sizeof(_native.Range)
     own = dst is None
@@ -204,7 +206,8 @@ def decode_range(data, byte_lo: int, byte_hi: int, dst: np.ndarray | None = None
         _raise(st)
     samples = None
     if rng.accepted and rng.n_frames:
-        samples = dst.view(np.uint8).reshape(-1)[:int(info.pcm_bytes)].view(_DTYPES[info.container_bytes])
+        off = int(rng.first_sample) * int(info.channels or 0) * int(info.container_bytes) if into_whole else 0
+        samples = dst.view(np.uint8).reshape(-1)[off: off + int(info.pcm_bytes)].view(_DTYPES[info.container_bytes])
     return RangeResult(bool(rng.accepted), int(rng.first_frame_offset), int(rng.end_offset), int(rng.first_sample),
                        int(rng.n_samples), int(rng.n_frames), int(rng.total_samples), samples, _info_dict(info))
 

@@ -2022,7 +2022,8 @@ int decode_range_impl(const uint8_t *data, size_t len, const zflacb200_options *
     out->first_frame_offset = lohi[1];
     info->n_samples = n_elems;
     info->pcm_bytes = n_elems * cb;
-    if (dst_capacity < n_elems * cb) {
+    const uint64_t dst_off = (flags & ZFLACB200_RANGE_INTO_WHOLE) ? lohi[0] * cb : 0;  // the shard's place in the whole stream's PCM
+    if (dst_capacity < dst_off + n_elems * cb) {
         g_last_error = "destination too small for the shard's PCM";
         return ZFLACB200_OUT_OF_MEMORY;
     }
@@ -2062,7 +2063,7 @@ int decode_range_impl(const uint8_t *data, size_t len, const zflacb200_options *
     GET_SMALL(h_sum, ctx, b_sum.p, sizeof(StreamSummary), st);
     GET_SMALL(h_lossy, ctx, b_flag.p, sizeof(uint32_t), st);
     GET_SMALL(h_ovf, ctx, stage.two_pass ? (const void *)stage.overflow_flag() : b_flag.p, sizeof(uint32_t), st);
-    CU_CHECK(cudaMemcpyAsync(dst, b_pcm.p, n_elems * cb, cudaMemcpyDeviceToHost, st));  // an unaccepted shard's bytes are garbage
+    CU_CHECK(cudaMemcpyAsync((uint8_t *)dst + dst_off, b_pcm.p, n_elems * cb, cudaMemcpyDeviceToHost, st));  // an unaccepted shard's bytes are garbage
     CU_CHECK(cudaEventRecord(ev.e[7], st));
     CU_CHECK(cudaStreamSynchronize(st));
     tr.mark("decode+readback");
