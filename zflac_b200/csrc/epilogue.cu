@@ -288,63 +288,106 @@ __device__ void md5_run(const Md5Job &j, uint8_t *digest, uint32_t (*stage)[16])
 
 // Batch variant: one LANE per stream. Every chain is serial, but 32 of them share each instruction; with thousands
 // of short files this is ~30x fewer issue slots than one warp per chain (lanes 1..31 idle during md5_block).
+//
+// The message bytes reach the lanes through shared memory: per round the warp copies the next 512 bytes of EVERY lane's
+// stream with cp.async — for each stream one instruction whose 32 lanes read 512 contiguous bytes — one round ahead of
+// the hashing, and a lane then reads its own row. Loading from the lanes themselves (each lane four 16-byte loads from
+// its own file per block, r02z) cost 2 350 cycles per block where the chain needs 1 055: every load instruction touched
+// 32 different pages, and its slowest lane set the pace.
+constexpr int kLaneChunk = 512;            // bytes per stream and round: eight 64-byte blocks
+constexpr int kLaneRow = kLaneChunk + 16;  // row pitch: the 16-byte loads of eight neighbouring lanes hit different banks
+
+// the blocks from `first_block` on (what is not PCM memory as it is: repacked samples, the padding), one lane's own way
 template <int HB>
-__device__ void md5_lane(const Md5Job &j, uint8_t *digest) {
+__device__ void md5_lane_tail(const Md5Job &j, uint32_t (&st)[4], uint64_t first_block) {
     const uint64_t msg_len = j.n_samples * HB;
     const uint64_t padded_len = (msg_len + 9 + 63) & ~63ull;
     const uint64_t n_blocks = padded_len >> 6;
-    const bool raw = (HB == (int)j.container_bytes) && j.unshift == 0 && ((uintptr_t)j.pcm & 15) == 0;
-    uint32_t st[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
     uint32_t m[16];
-    uint4 nx[4];
-    const uint4 *p = reinterpret_cast<const uint4 *>(j.pcm);
-    const uint64_t raw_blocks = raw ? msg_len >> 6 : 0;  // whole blocks that are PCM memory as it is
-    if (raw_blocks) {
+    for (uint64_t blk = first_block; blk < n_blocks; ++blk) {
+        const uint64_t byte0 = blk << 6;
+        uint32_t slow[16];  // dynamic indexing stays in this (local-memory) array: m[] keeps its registers
+        for (int wi = 0; wi < 16; ++wi) {
+            uint32_t w = 0;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) nx[q] = __ldg(p + q);
-    }
-    for (uint64_t blk = 0; blk < n_blocks; ++blk) {
-        if (blk < raw_blocks) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                m[4 * q + 0] = nx[q].x; m[4 * q + 1] = nx[q].y; m[4 * q + 2] = nx[q].z; m[4 * q + 3] = nx[q].w;
-            }
-            if (blk + 1 < raw_blocks) {  // next block's 64 bytes are in flight while this one is hashed
-#pragma unroll
-                for (int q = 0; q < 4; ++q) nx[q] = __ldg(p + 4 * (blk + 1) + q);
-            }
-        } else {
-            const uint64_t byte0 = blk << 6;
-            uint32_t slow[16];  // dynamic indexing stays in this (local-memory) array: m[] keeps its registers
-            for (int wi = 0; wi < 16; ++wi) {
-                uint32_t w = 0;
-#pragma unroll
-                for (int bb = 0; bb < 4; ++bb) w |= md5_msg_byte<HB>(j, byte0 + 4 * wi + bb, msg_len, padded_len) << (8 * bb);
-                slow[wi] = w;
-            }
-#pragma unroll
-            for (int wi = 0; wi < 16; ++wi) m[wi] = slow[wi];
+            for (int bb = 0; bb < 4; ++bb) w |= md5_msg_byte<HB>(j, byte0 + 4 * wi + bb, msg_len, padded_len) << (8 * bb);
+            slow[wi] = w;
         }
+#pragma unroll
+        for (int wi = 0; wi < 16; ++wi) m[wi] = slow[wi];
         md5_block(st, m);
     }
+}
+
+__global__ void __launch_bounds__(32)
+k_md5_lanes(const Md5Job *__restrict__ jobs, uint32_t n_jobs, uint8_t *__restrict__ digests) {
+    __shared__ __align__(16) uint8_t stage[2][32][kLaneRow];
+    const uint32_t lane = threadIdx.x;
+    const uint32_t job = blockIdx.x * 32 + lane;
+    Md5Job j;
+    j.pcm = nullptr;
+    j.n_samples = 0;
+    j.container_bytes = j.hash_bytes = 2;
+    j.unshift = j.pad = 0;
+    if (job < n_jobs) j = jobs[job];
+    const uint32_t hb = j.hash_bytes;
+    // whole blocks that are PCM memory as it is
+    const bool raw = job < n_jobs && hb == j.container_bytes && j.unshift == 0 && ((uintptr_t)j.pcm & 15) == 0;
+    const uint64_t raw_blocks = raw ? (j.n_samples * hb) >> 6 : 0;
+    const uint64_t raw_bytes = raw_blocks << 6;
+    const uint32_t my_rounds = (uint32_t)((raw_blocks + 7) >> 3);  // < 2^32: a stream of 2 TB would not be in a batch
+    const uint32_t n_rounds = __reduce_max_sync(0xFFFFFFFFu, my_rounds);
+    const unsigned long long my_ptr = (unsigned long long)(uintptr_t)j.pcm;
+    uint32_t st[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+
+    auto issue = [&](uint32_t round, int buf) {  // 512 bytes of every stream, 16 per lane, zero-filled past a stream's raw part
+        const unsigned long long off = (unsigned long long)round * kLaneChunk + lane * 16u;
+#pragma unroll 4
+        for (int o = 0; o < 32; ++o) {
+            const unsigned long long po = __shfl_sync(0xFFFFFFFFu, my_ptr, o);
+            const unsigned long long rb = __shfl_sync(0xFFFFFFFFu, (unsigned long long)raw_bytes, o);
+            const uint32_t n = off + 16u <= rb ? 16u : 0u;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&stage[buf][o][lane * 16u]);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(po + (n ? off : 0ull)), "r"(n) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (n_rounds) issue(0, 0);
+    for (uint32_t r = 0; r < n_rounds; ++r) {
+        if (r + 1 < n_rounds) {  // the next round is in flight while this one is hashed
+            issue(r + 1, (r + 1) & 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncwarp();
+        const uint4 *row = reinterpret_cast<const uint4 *>(stage[r & 1][lane]);
+#pragma unroll 1
+        for (int b = 0; b < 8; ++b) {
+            if ((uint64_t)r * 8 + b < raw_blocks) {
+                uint32_t m[16];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint4 v = row[4 * b + q];
+                    m[4 * q + 0] = v.x; m[4 * q + 1] = v.y; m[4 * q + 2] = v.z; m[4 * q + 3] = v.w;
+                }
+                md5_block(st, m);
+            }
+        }
+        __syncwarp();  // everyone is done with this buffer before round r + 2 lands in it
+    }
+    if (job >= n_jobs) return;
+    switch (hb) {
+        case 1: md5_lane_tail<1>(j, st, raw_blocks); break;
+        case 2: md5_lane_tail<2>(j, st, raw_blocks); break;
+        case 3: md5_lane_tail<3>(j, st, raw_blocks); break;
+        default: md5_lane_tail<4>(j, st, raw_blocks); break;
+    }
+    uint8_t *digest = digests + 16 * (size_t)job;
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int k = 0; k < 4; ++k) digest[4 * i + k] = (uint8_t)(st[i] >> (8 * k));
-}
-
-__global__ void __launch_bounds__(64)
-k_md5_lanes(const Md5Job *__restrict__ jobs, uint32_t n_jobs, uint8_t *__restrict__ digests) {
-    const uint32_t job = blockIdx.x * 64 + threadIdx.x;
-    if (job >= n_jobs) return;
-    const Md5Job j = jobs[job];
-    uint8_t *dg = digests + 16 * (size_t)job;
-    switch (j.hash_bytes) {
-        case 1: md5_lane<1>(j, dg); break;
-        case 2: md5_lane<2>(j, dg); break;
-        case 3: md5_lane<3>(j, dg); break;
-        default: md5_lane<4>(j, dg); break;
-    }
 }
 
 constexpr int kMd5WarpsPerBlock = 2;
@@ -369,7 +412,7 @@ cudaError_t launch_md5(const Md5Job *d_jobs, uint32_t n_jobs, uint8_t *d_digests
     if (n_jobs == 0) return cudaSuccess;
     ZF_COUNT_LAUNCH();
     if (n_jobs >= 256) {  // enough chains to give every lane its own
-        k_md5_lanes<<<(n_jobs + 63) / 64, 64, 0, st>>>(d_jobs, n_jobs, d_digests);
+        k_md5_lanes<<<(n_jobs + 31) / 32, 32, 0, st>>>(d_jobs, n_jobs, d_digests);
         return cudaGetLastError();
     }
     k_md5<<<(n_jobs + kMd5WarpsPerBlock - 1) / kMd5WarpsPerBlock, 32 * kMd5WarpsPerBlock, 0, st>>>(d_jobs, n_jobs, d_digests);

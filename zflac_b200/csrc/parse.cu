@@ -56,14 +56,18 @@ k_parse_frames_narrow(const uint8_t *__restrict__ s, const FrameRec *__restrict_
     fr.scratch_base = 0;
     if (f < n_frames) fr = frames[f];
     // layout of the warp's rows (parse_narrow.cuh): interleaved when its 32 frames are alike and their regions in order
-    const uint32_t bs0 = __shfl_sync(0xFFFFFFFFu, fr.block_size, 0), c0 = __shfl_sync(0xFFFFFFFFu, (uint32_t)fr.channels, 0);
+    // (one channel count, 32 live frames, regions in stream order, and together at least as large as 32 columns of the
+    // LONGEST frame's rows: 16 * C * roundup8(max block size) elements — true when most frames have the stream's block
+    // size, e.g. a warp that holds the short last frames of a few files of a batch)
+    const uint32_t c0 = __shfl_sync(0xFFFFFFFFu, (uint32_t)fr.channels, 0);
+    const uint32_t bs_max = __reduce_max_sync(0xFFFFFFFFu, fr.block_size);
     const uint64_t base0 = __shfl_sync(0xFFFFFFFFu, fr.scratch_base, 0);
-    const uint64_t need = (uint64_t)threadIdx.x * c0 * ((bs0 + 7u) & ~7u);  // elements the lanes below would use on their own
-    const bool alike = fr.block_size != 0 && fr.block_size == bs0 && fr.channels == c0 && fr.scratch_base >= base0 + need;
-    const bool interleave = __all_sync(0xFFFFFFFFu, alike);
+    const uint64_t end31 = __shfl_sync(0xFFFFFFFFu, fr.scratch_base + (uint64_t)fr.channels * ((fr.block_size + 7u) & ~7u), 31);
+    const bool alike = fr.block_size != 0 && fr.channels == c0 && fr.scratch_base >= base0;
+    const bool interleave = __all_sync(0xFFFFFFFFu, alike) && end31 >= base0 + 16ull * c0 * ((bs_max + 7u) & ~7u);
     if (fr.block_size == 0) return;  // dropped candidate slot / past the end
     NarrowSink sink;
-    if (interleave) sink.set_warp(scratch, base0, threadIdx.x, bs0);
+    if (interleave) sink.set_warp(scratch, base0, threadIdx.x, bs_max);
     else sink.set_frame(scratch, fr.scratch_base, fr.channels);
     const uint64_t start = fr.offset + fr.header_len;  // first subframe header
     const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(s + start) & 15u);

@@ -29,10 +29,11 @@ ZF_HD uint32_t pack16(int32_t lo, int32_t hi) {  // two int16 in one word (PRMT)
 // about one 32-byte-sector request per two cycles per SM, and a warp storing 32 rows into 32 frames' own regions costs
 // 32 of them — the scattered rows, not the bit chain, were what bounded K2a.
 //   kLayoutWarp  the 32 frames of the warp are INTERLEAVED row by row: row t of channel c of the frame in lane L at
-//                warp_base + ((c * nb + t) * 32 + L) * 16 bytes, nb = ceil(block_size / 8). Lanes run their bodies in
-//                step, so a store instruction writes 512 contiguous bytes; pass B's lanes (consecutive frames x channels)
-//                read runs of 16-byte rows too. Needs a warp whose 32 frames have one block size and channel count
-//                (any stream's frames but the last few); decided per warp, flagged in SubRec.pad[0].
+//                warp_base + ((c * nb + t) * 32 + L) * 16 bytes, nb = ceil(longest block of the warp / 8). Lanes run their
+//                bodies in step, so a store instruction writes 512 contiguous bytes; pass B's lanes (consecutive frames x
+//                channels) read runs of 16-byte rows too. Needs a warp of 32 live frames with one channel count whose
+//                regions together hold 32 columns of the longest frame (so: most frames of the stream's block size);
+//                decided per warp, flagged in SubRec.pad[0] with nb in pad[1..2].
 //   kLayoutFrame the frame's own region, groups of sixteen steps, channels one after another inside a group (one
 //                32-byte sector per channel and group, written by the same lane in two halves):
 //                frame_base + (t / 2) * 32 * C + c * 32 + (t % 2) * 16.
@@ -45,18 +46,21 @@ struct NarrowSink {
     uint32_t row_shift;  // row t lives at (t >> row_shift) * row_stride + (t & row_mask) * 16
     uint32_t row_mask;
     uint32_t row_stride;
+    uint16_t rows;       // kLayoutWarp: rows per channel of the warp's columns = ceil(longest block / 8), in SubRec.pad[1..2]
     uint8_t layout;
     ZF_HD void set_frame(void *scratch, uint64_t scratch_base, uint32_t channels) {
         base = reinterpret_cast<uint8_t *>(scratch) + 4u * scratch_base;
+        rows = 0;
         ch_stride = 32u;
         row_shift = 1u;
         row_mask = 1u;
         row_stride = 32u * channels;
         layout = kLayoutFrame;
     }
-    ZF_HD void set_warp(void *scratch, uint64_t warp_scratch_base, uint32_t lane, uint32_t block_size) {
+    ZF_HD void set_warp(void *scratch, uint64_t warp_scratch_base, uint32_t lane, uint32_t max_block_size) {
         base = reinterpret_cast<uint8_t *>(scratch) + 4u * warp_scratch_base + 16u * lane;
-        ch_stride = ((block_size + 7u) >> 3) * 512u;
+        rows = (uint16_t)((max_block_size + 7u) >> 3);  // <= 8192
+        ch_stride = rows * 512u;
         row_shift = 0u;
         row_mask = 0u;
         row_stride = 512u;
@@ -281,6 +285,8 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const Nar
             sub->wasted = (uint8_t)wasted;
             sub->wide_acc = (uint8_t)wide_acc;
             sub->pad[0] = sink.layout;
+            sub->pad[1] = (uint8_t)(sink.rows & 0xFFu);
+            sub->pad[2] = (uint8_t)(sink.rows >> 8);
             sub->constant = constant;
         }
     }

@@ -102,7 +102,7 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             if (NARROW) {  // rows of eight int16, laid out per warp of pass A or per frame (parse_narrow.cuh, flag in SubRec.pad[0])
                 if (((hd.y >> 8) & 0xFFu) == kLayoutWarp) {
                     const uint64_t base0 = frames[f & ~31u].scratch_base;
-                    row0 = reinterpret_cast<const uint8_t *>(scratch + base0) + ((size_t)c * ((fr.block_size + 7u) >> 3) * 32u + (f & 31u)) * 16u;
+                    row0 = reinterpret_cast<const uint8_t *>(scratch + base0) + ((size_t)c * (hd.y >> 16) * 32u + (f & 31u)) * 16u;
                     row_shift = 0u;
                     row_mask = 0u;
                     row_stride = 512u;
