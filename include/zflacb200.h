@@ -116,6 +116,7 @@ int zflacb200_abi_version(void);
 int zflacb200_init(int device);
 int zflacb200_device_count(void);
 void zflacb200_shutdown(void);
+void zflacb200_trim(void); /* hands the library's idle device blocks (its block cache) back to the driver; handles stay valid */
 const char *zflacb200_status_name(int status); /* the Zig error name, e.g. "InvalidFrameHeader" */
 const char *zflacb200_last_error(void);        /* thread-local detail for CUDA_ERROR / INVALID_ARGUMENT */
 uint64_t zflacb200_kernel_launches(void);      /* kernels this library has launched since load (bench: gpu_launches) */

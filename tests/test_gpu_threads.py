@@ -51,3 +51,18 @@ def test_concurrent_callers(n_threads):
         t.join()
     assert not errors, errors[:5]
     assert torch.cuda.current_device() == 0  # the library put the caller's device back
+
+
+def test_trim_hands_idle_blocks_back_and_decoding_goes_on():
+    """zflacb200_trim: the block cache gives its idle blocks back to the driver; the next call allocates afresh."""
+    import torch
+    import zflac_b200 as z
+    p = fg.c2(20.0)
+    s = fg.generate(p, want_pcm=True)
+    assert np.array_equal(z.decode(s.flac).samples, s.pcm)
+    torch.cuda.synchronize()
+    free_cached, _ = torch.cuda.mem_get_info()
+    z.trim()
+    free_trimmed, _ = torch.cuda.mem_get_info()
+    assert free_trimmed > free_cached  # the PCM / scratch blocks of the call above went back
+    assert np.array_equal(z.decode(s.flac).samples, s.pcm)

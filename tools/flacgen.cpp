@@ -11,7 +11,8 @@
 // Everything is a pure function of fg_params (seeded xoshiro256**, per-frame streams), so the
 // same parameters give the same bytes on any machine and with any thread count.
 //
-// Build: g++ -O3 -std=c++17 -shared -fPIC -pthread (tools/flacgen.py does it).
+// Build: g++ -O3 -ffp-contract=off -std=c++17 -shared -fPIC -pthread (tools/flacgen.py does it). The CUDA generator
+// (flacgen_cuda.cu) writes the same bytes: what the two share, and why FMA contraction is off, is in flacgen_common.h.
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -23,32 +24,10 @@
 #include <thread>
 #include <vector>
 
+#include "flacgen_common.h"
+
 extern "C" {
 
-typedef struct fg_params {
-    uint32_t struct_size;
-    uint32_t sample_rate;
-    uint32_t channels;             // 1..8
-    uint32_t bps;                  // 4..32 (STREAMINFO and frame headers agree)
-    uint32_t block_size;           // fixed block size (variable_blocksize = 0)
-    uint32_t lpc_order;            // 1..32: order of LPC subframes
-    uint32_t qlp_precision;        // 1..15
-    uint32_t rice_method;          // 0: 4-bit parameters, 1: 5-bit parameters
-    uint32_t min_partition_order;
-    uint32_t max_partition_order;  // the encoder picks the cheapest valid order in [min, max]
-    uint32_t stereo_mode;          // 0 independent, 1 left/side, 2 side/right, 3 mid/side, 4 cycle 0..3 per frame
-    uint32_t subframe_mix;         // 0: every subframe LPC(lpc_order); 1: LPC / FIXED 0-4 / VERBATIM / CONSTANT mix
-    uint32_t wasted_bits;          // 0 none; 1: frames carry 1..9 wasted bits (cycling)
-    uint32_t variable_blocksize;   // 0 fixed; 1: blocking strategy 1, sizes cycle 16/192/576/1000/4096/4608/16384
-    uint32_t escape_every;         // 0 never; n: every n-th partition is written escaped (raw)
-    uint32_t signal;               // 0: tones + shaped noise; 1: wide dynamic range (noise level sweeps with the frame)
-    uint32_t set_total;            // 1: STREAMINFO total samples set; 0: unknown (0)
-    uint32_t n_threads;            // 0 = hardware concurrency
-    uint64_t n_samples;            // per channel
-    uint64_t seed;
-    double amplitude;              // tone amplitude as a fraction of full scale (0..0.45)
-    double noise;                  // noise sigma as a fraction of full scale
-} fg_params;
 
 typedef struct fg_result {
     uint8_t *flac;
@@ -65,64 +44,22 @@ typedef struct fg_result {
 int fg_generate(const fg_params *p, int want_pcm, fg_result *out);
 int fg_generate_batch(const fg_params *ps, uint32_t n, int want_pcm, fg_result *outs, uint32_t n_threads);
 void fg_free(fg_result *r);
+void fg_set_trace(uint32_t *buf, uint64_t n_records);
 }
 
 namespace {
 
-// ------------------------------------------------------------------ RNG
-struct Xo {
-    uint64_t s[4];
-    static uint64_t splitmix(uint64_t &x) {
-        uint64_t z = (x += 0x9E3779B97F4A7C15ull);
-        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-        return z ^ (z >> 31);
-    }
-    explicit Xo(uint64_t seed) {
-        for (auto &v : s) v = splitmix(seed);
-    }
-    static uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
-    uint64_t next() {
-        const uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17;
-        s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3];
-        s[2] ^= t;
-        s[3] = rotl(s[3], 45);
-        return r;
-    }
-    // ~N(0,1): sum of four 16-bit uniforms, centred and scaled (Irwin-Hall, var = 4/12)
-    double gauss() {
-        const uint64_t r = next();
-        const double u = (double)(r & 0xFFFF) + (double)((r >> 16) & 0xFFFF) + (double)((r >> 32) & 0xFFFF) + (double)(r >> 48);
-        return (u - 2.0 * 65535.0) * (1.0 / (65536.0 * 0.5773502691896258));
-    }
-};
+using fgc::Xo;
+using fgc::zigzag;
+using fgc::bits_needed_signed;
+using fgc::container_of;
 
 // ------------------------------------------------------------------ checksums
-uint8_t g_crc8[256];
 uint16_t g_crc16[8][256];
 struct TableInit {
-    TableInit() {
-        for (int i = 0; i < 256; ++i) {
-            uint32_t c = (uint32_t)i;
-            for (int k = 0; k < 8; ++k) c = (c & 0x80) ? ((c << 1) ^ 0x07) & 0xFF : (c << 1) & 0xFF;
-            g_crc8[i] = (uint8_t)c;
-            uint32_t d = (uint32_t)i << 8;
-            for (int k = 0; k < 8; ++k) d = (d & 0x8000) ? ((d << 1) ^ 0x8005) & 0xFFFF : (d << 1) & 0xFFFF;
-            g_crc16[0][i] = (uint16_t)d;
-        }
-        for (int t = 1; t < 8; ++t)
-            for (int i = 0; i < 256; ++i) {
-                const uint16_t v = g_crc16[t - 1][i];
-                g_crc16[t][i] = (uint16_t)((v << 8) ^ g_crc16[0][v >> 8]);
-            }
-    }
+    TableInit() { fgc::crc16_make_tables(g_crc16); }
 } g_table_init;
 
-uint8_t crc8(const uint8_t *p, size_t n) {
-    uint8_t c = 0;
-    for (size_t i = 0; i < n; ++i) c = g_crc8[c ^ p[i]];
-    return c;
-}
 uint16_t crc16(const uint8_t *p, size_t n) {
     uint16_t c = 0;
     size_t i = 0;
@@ -135,80 +72,7 @@ uint16_t crc16(const uint8_t *p, size_t n) {
     return c;
 }
 
-struct Md5 {
-    uint32_t a = 0x67452301u, b = 0xefcdab89u, c = 0x98badcfeu, d = 0x10325476u;
-    uint64_t total = 0;
-    uint8_t buf[64];
-    size_t fill = 0;
-    static uint32_t rl(uint32_t x, int s) { return (x << s) | (x >> (32 - s)); }
-    void block(const uint8_t *p) {
-        uint32_t m[16];
-        memcpy(m, p, 64);
-        uint32_t A = a, B = b, C = c, D = d;
-#define FG_F(x, y, z) ((z) ^ ((x) & ((y) ^ (z))))
-#define FG_G(x, y, z) ((y) ^ ((z) & ((x) ^ (y))))
-#define FG_H(x, y, z) ((x) ^ (y) ^ (z))
-#define FG_I(x, y, z) ((y) ^ ((x) | ~(z)))
-#define FG_S(f, w, x, y, z, g, k, s) w = x + rl(w + f(x, y, z) + m[g] + k, s)
-        FG_S(FG_F, A, B, C, D, 0, 0xd76aa478u, 7);  FG_S(FG_F, D, A, B, C, 1, 0xe8c7b756u, 12);
-        FG_S(FG_F, C, D, A, B, 2, 0x242070dbu, 17); FG_S(FG_F, B, C, D, A, 3, 0xc1bdceeeu, 22);
-        FG_S(FG_F, A, B, C, D, 4, 0xf57c0fafu, 7);  FG_S(FG_F, D, A, B, C, 5, 0x4787c62au, 12);
-        FG_S(FG_F, C, D, A, B, 6, 0xa8304613u, 17); FG_S(FG_F, B, C, D, A, 7, 0xfd469501u, 22);
-        FG_S(FG_F, A, B, C, D, 8, 0x698098d8u, 7);  FG_S(FG_F, D, A, B, C, 9, 0x8b44f7afu, 12);
-        FG_S(FG_F, C, D, A, B, 10, 0xffff5bb1u, 17); FG_S(FG_F, B, C, D, A, 11, 0x895cd7beu, 22);
-        FG_S(FG_F, A, B, C, D, 12, 0x6b901122u, 7); FG_S(FG_F, D, A, B, C, 13, 0xfd987193u, 12);
-        FG_S(FG_F, C, D, A, B, 14, 0xa679438eu, 17); FG_S(FG_F, B, C, D, A, 15, 0x49b40821u, 22);
-        FG_S(FG_G, A, B, C, D, 1, 0xf61e2562u, 5);  FG_S(FG_G, D, A, B, C, 6, 0xc040b340u, 9);
-        FG_S(FG_G, C, D, A, B, 11, 0x265e5a51u, 14); FG_S(FG_G, B, C, D, A, 0, 0xe9b6c7aau, 20);
-        FG_S(FG_G, A, B, C, D, 5, 0xd62f105du, 5);  FG_S(FG_G, D, A, B, C, 10, 0x02441453u, 9);
-        FG_S(FG_G, C, D, A, B, 15, 0xd8a1e681u, 14); FG_S(FG_G, B, C, D, A, 4, 0xe7d3fbc8u, 20);
-        FG_S(FG_G, A, B, C, D, 9, 0x21e1cde6u, 5);  FG_S(FG_G, D, A, B, C, 14, 0xc33707d6u, 9);
-        FG_S(FG_G, C, D, A, B, 3, 0xf4d50d87u, 14); FG_S(FG_G, B, C, D, A, 8, 0x455a14edu, 20);
-        FG_S(FG_G, A, B, C, D, 13, 0xa9e3e905u, 5); FG_S(FG_G, D, A, B, C, 2, 0xfcefa3f8u, 9);
-        FG_S(FG_G, C, D, A, B, 7, 0x676f02d9u, 14); FG_S(FG_G, B, C, D, A, 12, 0x8d2a4c8au, 20);
-        FG_S(FG_H, A, B, C, D, 5, 0xfffa3942u, 4);  FG_S(FG_H, D, A, B, C, 8, 0x8771f681u, 11);
-        FG_S(FG_H, C, D, A, B, 11, 0x6d9d6122u, 16); FG_S(FG_H, B, C, D, A, 14, 0xfde5380cu, 23);
-        FG_S(FG_H, A, B, C, D, 1, 0xa4beea44u, 4);  FG_S(FG_H, D, A, B, C, 4, 0x4bdecfa9u, 11);
-        FG_S(FG_H, C, D, A, B, 7, 0xf6bb4b60u, 16); FG_S(FG_H, B, C, D, A, 10, 0xbebfbc70u, 23);
-        FG_S(FG_H, A, B, C, D, 13, 0x289b7ec6u, 4); FG_S(FG_H, D, A, B, C, 0, 0xeaa127fau, 11);
-        FG_S(FG_H, C, D, A, B, 3, 0xd4ef3085u, 16); FG_S(FG_H, B, C, D, A, 6, 0x04881d05u, 23);
-        FG_S(FG_H, A, B, C, D, 9, 0xd9d4d039u, 4);  FG_S(FG_H, D, A, B, C, 12, 0xe6db99e5u, 11);
-        FG_S(FG_H, C, D, A, B, 15, 0x1fa27cf8u, 16); FG_S(FG_H, B, C, D, A, 2, 0xc4ac5665u, 23);
-        FG_S(FG_I, A, B, C, D, 0, 0xf4292244u, 6);  FG_S(FG_I, D, A, B, C, 7, 0x432aff97u, 10);
-        FG_S(FG_I, C, D, A, B, 14, 0xab9423a7u, 15); FG_S(FG_I, B, C, D, A, 5, 0xfc93a039u, 21);
-        FG_S(FG_I, A, B, C, D, 12, 0x655b59c3u, 6); FG_S(FG_I, D, A, B, C, 3, 0x8f0ccc92u, 10);
-        FG_S(FG_I, C, D, A, B, 10, 0xffeff47du, 15); FG_S(FG_I, B, C, D, A, 1, 0x85845dd1u, 21);
-        FG_S(FG_I, A, B, C, D, 8, 0x6fa87e4fu, 6);  FG_S(FG_I, D, A, B, C, 15, 0xfe2ce6e0u, 10);
-        FG_S(FG_I, C, D, A, B, 6, 0xa3014314u, 15); FG_S(FG_I, B, C, D, A, 13, 0x4e0811a1u, 21);
-        FG_S(FG_I, A, B, C, D, 4, 0xf7537e82u, 6);  FG_S(FG_I, D, A, B, C, 11, 0xbd3af235u, 10);
-        FG_S(FG_I, C, D, A, B, 2, 0x2ad7d2bbu, 15); FG_S(FG_I, B, C, D, A, 9, 0xeb86d391u, 21);
-#undef FG_S
-        a += A; b += B; c += C; d += D;
-    }
-    void update(const uint8_t *p, size_t n) {
-        total += n;
-        if (fill) {
-            const size_t k = std::min(n, 64 - fill);
-            memcpy(buf + fill, p, k);
-            fill += k; p += k; n -= k;
-            if (fill == 64) { block(buf); fill = 0; }
-        }
-        for (; n >= 64; p += 64, n -= 64) block(p);
-        if (n) { memcpy(buf, p, n); fill = n; }
-    }
-    void finish(uint8_t out[16]) {
-        const uint64_t bits = total * 8;
-        uint8_t pad[72] = {0x80};
-        const size_t padn = (fill < 56) ? 56 - fill : 120 - fill;
-        update(pad, padn);
-        uint8_t lenb[8];
-        for (int i = 0; i < 8; ++i) lenb[i] = (uint8_t)(bits >> (8 * i));
-        update(lenb, 8);
-        const uint32_t v[4] = {a, b, c, d};
-        for (int i = 0; i < 4; ++i)
-            for (int k = 0; k < 4; ++k) out[4 * i + k] = (uint8_t)(v[i] >> (8 * k));
-    }
-};
+using fgc::Md5;
 
 // ------------------------------------------------------------------ bit writer (MSB first)
 struct BitWriter {
@@ -240,12 +104,6 @@ struct BitWriter {
     }
 };
 
-int bits_needed_signed(int64_t lo, int64_t hi) {  // two's complement width holding [lo, hi]
-    int b = 1;
-    while (b < 64 && (lo < -(1ll << (b - 1)) || hi > (1ll << (b - 1)) - 1)) ++b;
-    return b;
-}
-
 // ------------------------------------------------------------------ frame plan
 struct FramePlan {
     uint64_t first_sample;
@@ -253,13 +111,11 @@ struct FramePlan {
     uint64_t index;  // frame number
 };
 
-const uint32_t kVarSizes[7] = {16, 192, 576, 1000, 4096, 4608, 16384};
-
 std::vector<FramePlan> plan_frames(const fg_params &p) {
     std::vector<FramePlan> v;
     uint64_t pos = 0, idx = 0;
     while (pos < p.n_samples) {
-        uint32_t bs = p.variable_blocksize ? kVarSizes[idx % 7] : p.block_size;
+        uint32_t bs = p.variable_blocksize ? fgc::var_block_size(idx) : p.block_size;
         if ((uint64_t)bs > p.n_samples - pos) bs = (uint32_t)(p.n_samples - pos);
         v.push_back({pos, bs, idx});
         pos += bs;
@@ -273,68 +129,29 @@ std::vector<FramePlan> plan_frames(const fg_params &p) {
 // Samples of one frame, all channels, as exact integers of `bps` bits.
 void synth_frame(const fg_params &p, const FramePlan &f, std::vector<std::vector<int64_t>> &ch) {
     const uint32_t C = p.channels, n = f.block_size;
-    const double full = std::ldexp(1.0, (int)p.bps - 1);
-    Xo rng(p.seed * 0x9E3779B97F4A7C15ull + f.index * 0xD1B54A32D192ED03ull + 1);
-    double amp = p.amplitude * full, sigma = p.noise * full;
-    if (p.signal == 1) {  // wide dynamic range: noise level sweeps over the frames, tones stay
-        const int span = std::max(1, (int)p.bps - 4);
-        sigma = std::ldexp(0.6, (int)(f.index % (uint64_t)span)) ;
-        if (sigma > 0.2 * full) sigma = 0.2 * full;
-    }
-    const double limit = (C == 2 && p.stereo_mode != 0) ? 0.49 * full : 0.98 * full;  // side must fit the container (Q9)
-    static const double kFreq[3] = {220.0, 1318.5, 5274.0};
-    static const double kRel[3] = {1.0, 0.5, 0.25};
+    const fgc::SignalConsts k = fgc::signal_consts(p);
+    const double sigma = fgc::frame_sigma(p, k, f.index);
+    Xo rng(fgc::frame_rng_seed(p.seed, f.index));
     ch.assign(C, std::vector<int64_t>(n));
     std::vector<double> base(n);
     for (uint32_t c = 0; c < C; ++c) {
         const bool follow = (C == 2 && c == 1);  // R = 0.8 L + its own noise: gives mid/side something to win
-        // tones by phasor rotation from the absolute sample index (continuous across frames)
-        double re[3], im[3], cr[3], ci[3];
-        for (int t = 0; t < 3; ++t) {
-            const double w = 2.0 * M_PI * kFreq[t] * (1.0 + 0.013 * c) / (double)p.sample_rate;
-            const double ph = std::fmod(w * (double)f.first_sample, 2.0 * M_PI) + 0.7 * c;
-            re[t] = std::cos(ph); im[t] = std::sin(ph);
-            cr[t] = std::cos(w); ci[t] = std::sin(w);
-        }
-        double z1 = 0, z2 = 0;  // AR(2) noise shaping: y = e + 1.2 z1 - 0.5 z2  (spectral tilt)
-        const double ar_gain = 0.45;
-        const double sg = follow ? sigma * 0.66 : sigma;
+        const fgc::ToneStep st = fgc::tone_step(p, c);
+        fgc::ChannelSynth cs;
+        cs.init(fgc::tone_state(p, c, f.first_sample), sigma, follow);
         for (uint32_t i = 0; i < n; ++i) {
-            double v = 0;
-            if (!follow) {
-                for (int t = 0; t < 3; ++t) {
-                    v += kRel[t] * im[t];
-                    const double nr = re[t] * cr[t] - im[t] * ci[t];
-                    im[t] = re[t] * ci[t] + im[t] * cr[t];
-                    re[t] = nr;
-                }
-                v *= amp / 1.75;
-            } else {
-                v = 0.8 * base[i];
-            }
-            const double e = rng.gauss();
-            const double y = e + 1.2 * z1 - 0.5 * z2;
-            z2 = z1; z1 = y;
-            v += sg * ar_gain * y;
+            const double v = cs.next(rng, st, k, follow, base[i]);
             if (c == 0) base[i] = v;
-            if (v > limit - 1) v = limit - 1;
-            if (v < -limit) v = -limit;
-            ch[c][i] = (int64_t)std::llrint(v);
+            ch[c][i] = fgc::quantize_sample(v, k.limit);
         }
     }
-    if (p.subframe_mix) {  // some frames carry a constant channel (never one that becomes a side channel, Q8)
-        if (f.index % 5 == 2) {
-            const uint32_t c = (uint32_t)((f.index / 5) % C);
-            const int64_t v = ch[c][0];
-            std::fill(ch[c].begin(), ch[c].end(), v);
-        }
+    {   // some frames of a subframe_mix stream carry a constant channel
+        const uint32_t c = fgc::constant_channel_of(p, f.index);
+        if (c < C) std::fill(ch[c].begin(), ch[c].end(), ch[c][0]);
     }
-    if (p.wasted_bits) {  // low bits cleared on every channel of the frame
-        const int w = 1 + (int)(f.index % 9);
-        if (w < (int)p.bps - 2)
-            for (auto &s : ch)
-                for (auto &x : s) x = (x >> w) * ((int64_t)1 << w);
-    }
+    if (const uint32_t w = fgc::wasted_of_frame(p, f.index))  // low bits cleared on every channel of the frame
+        for (auto &s : ch)
+            for (auto &x : s) x = (x >> w) * ((int64_t)1 << w);
 }
 
 // ------------------------------------------------------------------ subframe encoding
@@ -345,19 +162,15 @@ struct RicePlan {
     uint64_t bits;
 };
 
-inline uint64_t zigzag(int64_t r) { return ((uint64_t)r << 1) ^ (uint64_t)(r >> 63); }
-
 // Cheapest partitioning of the residual res[0..n) (first `pred_order` entries absent).
 RicePlan plan_rice(const fg_params &p, const std::vector<int64_t> &res, uint32_t bs, uint32_t pred_order, uint64_t salt) {
-    const uint32_t kmax = p.rice_method ? 30 : 14;
-    const uint32_t pbits = p.rice_method ? 5 : 4;
+    const uint32_t kmax = fgc::rice_kmax(p);
+    const uint32_t pbits = fgc::rice_pbits(p);
     RicePlan best;
     best.bits = ~0ull;
-    auto valid = [&](uint32_t po) {  // must divide the block; first partition may not be negative (Q16)
-        return ((bs >> po) << po) == bs && (bs >> po) >= pred_order && (bs >> po) > 0;
-    };
-    uint32_t lo = p.min_partition_order, hi = std::min<uint32_t>(p.max_partition_order, 15);
-    while (lo > 0 && !valid(lo)) --lo;  // short last block: fall back to the largest valid order below
+    auto valid = [&](uint32_t po) { return fgc::partition_order_valid(bs, po, pred_order); };
+    uint32_t lo, hi;
+    fgc::partition_order_range(p, bs, pred_order, lo, hi);
     for (uint32_t po = lo; po <= hi; ++po) {
         if (!valid(po)) break;
         RicePlan rp;
@@ -376,12 +189,8 @@ RicePlan plan_rice(const fg_params &p, const std::vector<int64_t> &res, uint32_t
                 mn = std::min(mn, res[i]);
                 mx = std::max(mx, res[i]);
             }
-            uint32_t k = 0;
-            if (cnt) {
-                const uint64_t mean = sum / cnt;
-                while (k < 40 && (mean >> (k + 1)) != 0) ++k;  // k ~ floor(log2(mean)); k+1 is tried below
-            }
-            const bool force_esc = p.escape_every && ((salt + q) % p.escape_every == p.escape_every - 1);
+            uint32_t k = fgc::rice_k_of_mean(sum, cnt);
+            const bool force_esc = fgc::partition_forced_escape(p, salt, q);
             if (k > kmax || force_esc) {
                 rp.param[q] = 0xFFFFFFFFu;
                 const int eb = (mn == 0 && mx == 0) ? 0 : bits_needed_signed(mn, mx);
@@ -408,7 +217,7 @@ RicePlan plan_rice(const fg_params &p, const std::vector<int64_t> &res, uint32_t
 
 void write_residual(const fg_params &p, BitWriter &bw, const RicePlan &rp, const std::vector<int64_t> &res, uint32_t bs,
                     uint32_t pred_order) {
-    const uint32_t pbits = p.rice_method ? 5 : 4;
+    const uint32_t pbits = fgc::rice_pbits(p);
     bw.put(p.rice_method ? 1 : 0, 2);
     bw.put(rp.order, 4);
     const uint32_t np = 1u << rp.order, psz = bs >> rp.order;
@@ -440,60 +249,34 @@ void write_residual(const fg_params &p, BitWriter &bw, const RicePlan &rp, const
 // shift chosen so the largest coefficient uses the full precision, error feedback on rounding).
 bool fit_lpc(const std::vector<int64_t> &s, uint32_t n, uint32_t order, uint32_t precision, int32_t *qcoef, uint32_t &shift) {
     std::vector<double> w(n);
-    for (uint32_t i = 0; i < n; ++i) {
-        const double t = (double)i / (double)(n - 1 ? n - 1 : 1);
-        const double win = 0.5 - 0.5 * std::cos(2.0 * M_PI * t);  // Hann
-        w[i] = win * (double)s[i];
-    }
+    for (uint32_t i = 0; i < n; ++i) w[i] = fgc::hann(i, n) * (double)s[i];
     double ac[33];
     for (uint32_t lag = 0; lag <= order; ++lag) {
         double a = 0;
         for (uint32_t i = lag; i < n; ++i) a += w[i] * w[i - lag];
         ac[lag] = a;
     }
-    if (ac[0] <= 0) return false;
-    ac[0] *= 1.0 + 1e-9;
-    double lpc[33] = {0}, tmp[33];
-    double err = ac[0];
-    for (uint32_t i = 0; i < order; ++i) {
-        double r = -ac[i + 1];
-        for (uint32_t j = 0; j < i; ++j) r -= lpc[j] * ac[i - j];
-        r /= err;
-        memcpy(tmp, lpc, sizeof(double) * i);
-        lpc[i] = r;
-        for (uint32_t j = 0; j < i; ++j) lpc[j] = tmp[j] + r * tmp[i - 1 - j];
-        err *= (1.0 - r * r);
-        if (err <= 0) { err = 1e-9; }
-    }
-    double cmax = 0;
-    for (uint32_t i = 0; i < order; ++i) cmax = std::max(cmax, std::fabs(lpc[i]));
-    if (cmax <= 0) return false;
-    int log2c;
-    std::frexp(cmax, &log2c);  // cmax = m * 2^log2c, m in [0.5, 1)
-    int sh = (int)precision - log2c - 1;
-    if (sh > 15) sh = 15;
-    if (sh < 0) return false;  // would need a negative shift: not representable for the reference (Q17)
-    const int32_t qmax = (1 << (precision - 1)) - 1, qmin = -(1 << (precision - 1));
-    double errf = 0;
-    for (uint32_t i = 0; i < order; ++i) {
-        errf += -lpc[i] * (double)(1 << sh);
-        long q = std::lrint(errf);
-        if (q > qmax) q = qmax;
-        if (q < qmin) q = qmin;
-        qcoef[i] = (int32_t)q;
-        errf -= (double)q;
-    }
-    shift = (uint32_t)sh;
-    return true;
+    return fgc::lpc_from_autocorr(ac, order, precision, qcoef, shift);
 }
-
-const int kFixed[5][4] = {{0, 0, 0, 0}, {1, 0, 0, 0}, {2, -1, 0, 0}, {3, -3, 1, 0}, {4, -6, 4, -1}};
 
 // Encodes one subframe of `depth` bits. `allow_constant` is false on side channels (Q8).
 // acc_bits: width of the reference's accumulator type (16/32/64, Q10): predictors whose worst-case sum
 // does not fit are not used.
+// Debug trace (fg_set_trace): eight words per subframe — type code, wasted bits, precision, shift, partition order,
+// bits written, a checksum of the subframe's samples, a checksum of the quantised coefficients. The CUDA generator
+// fills the same records, so a byte mismatch between the two can be pinned to a stage.
+uint32_t *g_trace = nullptr;
+uint64_t g_trace_records = 0;
+
 void encode_subframe(const fg_params &p, BitWriter &bw, const std::vector<int64_t> &sig, uint32_t bs, uint32_t depth,
-                     bool allow_constant, uint32_t acc_bits, uint64_t salt) {
+                     bool allow_constant, uint32_t acc_bits, uint64_t salt, uint32_t *tr) {
+    uint32_t tr_dummy[8];
+    if (!tr) tr = tr_dummy;
+    memset(tr, 0, 32);
+    struct BitsAtExit {  // bits this call wrote
+        BitWriter &bw; uint32_t *tr; uint64_t start;
+        ~BitsAtExit() { tr[5] = (uint32_t)(bw.out.size() * 8 + (uint64_t)bw.n - start); }
+    } at_exit{bw, tr, bw.out.size() * 8 + (uint64_t)bw.n};
     // wasted bits
     uint32_t wasted = 0;
     {
@@ -510,7 +293,10 @@ void encode_subframe(const fg_params &p, BitWriter &bw, const std::vector<int64_
     bool constant = true;
     for (uint32_t i = 1; i < bs && constant; ++i) constant = s[i] == s[0];
 
+    tr[1] = wasted;
+    for (uint32_t i = 0; i < bs; ++i) tr[6] += (uint32_t)s[i] * (i + 1);
     auto header = [&](uint32_t type) {
+        tr[0] = type;
         bw.put(0, 1);
         bw.put(type, 6);
         bw.put(wasted ? 1 : 0, 1);
@@ -528,27 +314,15 @@ void encode_subframe(const fg_params &p, BitWriter &bw, const std::vector<int64_
         return;
     }
     // choose the predictor
-    uint32_t kind = 2, order = p.lpc_order;  // 0 verbatim, 1 fixed, 2 lpc
-    if (p.subframe_mix) {
-        const uint64_t sel = salt % 8;
-        if (sel == 7) kind = 0;
-        else if (sel >= 2 && sel <= 6) { kind = 1; order = (uint32_t)(sel - 2); }
-        else if (sel == 1) order = 1 + (uint32_t)((salt / 8) % p.lpc_order);
-    }
-    if (order > 32) order = 32;
-    if (kind == 2 && (order == 0 || bs <= order)) kind = 0;
-    if (kind == 1 && bs <= order) kind = 0;
-    if (kind == 0) { verbatim(); return; }
+    const fgc::Choice choice = fgc::choose_predictor(p, salt, bs, eff, acc_bits);
+    uint32_t kind = choice.kind, order = choice.order;
+    if (kind == fgc::kVerbatim) { verbatim(); return; }
 
     int32_t qc[32] = {0};
     uint32_t shift = 0;
-    if (kind == 2) {
-        uint32_t prec = p.qlp_precision;
-        // keep |sum| <= 2^(eff-1 + prec-1 + ceil(log2(order))) inside the reference's accumulator (Q10)
-        uint32_t lg = 0;
-        while ((1u << lg) < order) ++lg;
-        while (prec > 1 && eff + prec + lg > acc_bits) --prec;
-        if (eff + prec + lg > acc_bits || !fit_lpc(s, bs, order, prec, qc, shift)) { kind = 1; order = std::min<uint32_t>(2, order); }
+    if (kind == fgc::kLpc) {
+        const uint32_t prec = choice.prec;
+        if (!fit_lpc(s, bs, order, prec, qc, shift)) { kind = fgc::kFixed; order = std::min<uint32_t>(2, order); }
         else {
             // store the precision actually used
             std::vector<int64_t> res(bs, 0);
@@ -562,22 +336,26 @@ void encode_subframe(const fg_params &p, BitWriter &bw, const std::vector<int64_
             }
             if (!ok) { verbatim(); return; }
             header(32 + order - 1);
+            tr[2] = prec;
+            tr[3] = shift;
+            for (uint32_t j = 0; j < order; ++j) tr[7] += (uint32_t)qc[j] * (j + 1);
             for (uint32_t i = 0; i < order; ++i) bw.put_signed(s[i], (int)eff);
             bw.put(prec - 1, 4);
             bw.put(shift, 5);
             for (uint32_t j = 0; j < order; ++j) bw.put_signed(qc[j], (int)prec);
             const RicePlan rp = plan_rice(p, res, bs, order, salt);
+            tr[4] = rp.order;
             write_residual(p, bw, rp, res, bs, order);
             return;
         }
     }
     // fixed predictor
-    if (eff + 4 > acc_bits - 1) { verbatim(); return; }
+    if (!fgc::fixed_allowed(eff, acc_bits)) { verbatim(); return; }
     std::vector<int64_t> res(bs, 0);
     bool ok = true;
     for (uint32_t i = order; i < bs && ok; ++i) {
         int64_t acc = 0;
-        for (uint32_t j = 0; j < order; ++j) acc += (int64_t)kFixed[order][j] * s[i - 1 - j];
+        for (uint32_t j = 0; j < order; ++j) acc += (int64_t)fgc::fixed_coef(order, j) * s[i - 1 - j];
         const int64_t r = s[i] - acc;
         if (r > 0x3FFFFFFFll || r < -0x40000000ll) ok = false;
         res[i] = r;
@@ -586,18 +364,9 @@ void encode_subframe(const fg_params &p, BitWriter &bw, const std::vector<int64_
     header(8 + order);
     for (uint32_t i = 0; i < order; ++i) bw.put_signed(s[i], (int)eff);
     const RicePlan rp = plan_rice(p, res, bs, order, salt);
+    tr[4] = rp.order;
     write_residual(p, bw, rp, res, bs, order);
 }
-
-void put_utf8(std::vector<uint8_t> &o, uint64_t v) {
-    if (v < 0x80) { o.push_back((uint8_t)v); return; }
-    int n = 2;
-    while (n < 7 && v >= (1ull << (5 * n + 1))) ++n;  // n bytes carry 5n+1 bits
-    o.push_back((uint8_t)((0xFF << (8 - n)) | (v >> (6 * (n - 1)))));
-    for (int i = n - 2; i >= 0; --i) o.push_back((uint8_t)(0x80 | ((v >> (6 * i)) & 0x3F)));
-}
-
-uint32_t container_of(uint32_t bps) { return bps <= 8 ? 1 : bps <= 16 ? 2 : 4; }
 
 // One whole frame -> bytes appended to `out`; PCM (container-typed, MSB aligned) -> pcm if non-null.
 void encode_frame(const fg_params &p, const FramePlan &f, std::vector<uint8_t> &out, uint8_t *pcm_base,
@@ -606,7 +375,7 @@ void encode_frame(const fg_params &p, const FramePlan &f, std::vector<uint8_t> &
     const uint32_t C = p.channels, bs = f.block_size;
     const uint32_t cb = container_of(p.bps);
     if (pcm_base) {
-        const uint32_t msb = (p.bps >= 9 && p.bps <= 15) ? 16 - p.bps : (p.bps >= 17 && p.bps <= 31) ? 32 - p.bps : 0;
+        const uint32_t msb = fgc::msb_shift_of(p.bps);
         uint8_t *dst = pcm_base + f.first_sample * C * cb;
         for (uint32_t i = 0; i < bs; ++i)
             for (uint32_t c = 0; c < C; ++c) {
@@ -617,12 +386,7 @@ void encode_frame(const fg_params &p, const FramePlan &f, std::vector<uint8_t> &
             }
     }
     // channel assignment
-    uint32_t mode = 0;
-    if (C == 2) {
-        mode = p.stereo_mode == 4 ? (uint32_t)(f.index % 4) : p.stereo_mode;
-        if (p.bps == 32) mode = 0;  // a 33-bit side channel does not fit the reference's container (Q9)
-    }
-    const uint32_t ch_code = (C == 2 && mode) ? 7 + mode : C - 1;
+    const uint32_t mode = fgc::stereo_mode_of(p, f.index);
     std::vector<int64_t> a, b;
     uint32_t side_channel = 99;
     if (mode == 1) {  // left/side
@@ -643,34 +407,8 @@ void encode_frame(const fg_params &p, const FramePlan &f, std::vector<uint8_t> &
     }
     const size_t start = out.size();
     // header
-    out.push_back(0xFF);
-    out.push_back(p.variable_blocksize ? 0xF9 : 0xF8);
-    uint32_t bs_code, bs_extra = 0;
-    if (bs == 192) bs_code = 1;
-    else if (bs == 576 || bs == 1152 || bs == 2304 || bs == 4608) bs_code = bs == 576 ? 2 : bs == 1152 ? 3 : bs == 2304 ? 4 : 5;
-    else if (bs >= 256 && bs <= 32768 && (bs & (bs - 1)) == 0) {
-        bs_code = 0;
-        while ((1u << bs_code) != bs) ++bs_code;
-    } else if (bs <= 256) { bs_code = 6; bs_extra = 1; }
-    else { bs_code = 7; bs_extra = 2; }
-    uint32_t sr_code = 0;
-    switch (p.sample_rate) {
-        case 88200: sr_code = 1; break; case 176400: sr_code = 2; break; case 192000: sr_code = 3; break;
-        case 8000: sr_code = 4; break; case 16000: sr_code = 5; break; case 22050: sr_code = 6; break;
-        case 24000: sr_code = 7; break; case 32000: sr_code = 8; break; case 44100: sr_code = 9; break;
-        case 48000: sr_code = 10; break; case 96000: sr_code = 11; break; default: sr_code = 0;
-    }
-    uint32_t bd_code = 0;
-    switch (p.bps) {
-        case 8: bd_code = 1; break; case 12: bd_code = 2; break; case 16: bd_code = 4; break;
-        case 20: bd_code = 5; break; case 24: bd_code = 6; break; case 32: bd_code = 7; break; default: bd_code = 0;
-    }
-    out.push_back((uint8_t)((bs_code << 4) | sr_code));
-    out.push_back((uint8_t)((ch_code << 4) | (bd_code << 1)));
-    put_utf8(out, p.variable_blocksize ? f.first_sample : f.index);
-    if (bs_extra == 1) out.push_back((uint8_t)(bs - 1));
-    else if (bs_extra == 2) { out.push_back((uint8_t)((bs - 1) >> 8)); out.push_back((uint8_t)(bs - 1)); }
-    out.push_back(crc8(out.data() + start, out.size() - start));
+    const fgc::FrameHeaderBytes hdr = fgc::frame_header(p, f.index, f.first_sample, bs);
+    out.insert(out.end(), hdr.b, hdr.b + hdr.n);
     // subframes
     BitWriter bw(out);
     const uint32_t acc_bits = cb == 1 ? 16 : cb == 2 ? 32 : 64;
@@ -680,7 +418,8 @@ void encode_frame(const fg_params &p, const FramePlan &f, std::vector<uint8_t> &
         if (mode == 2 && c == 0) sig = &a;
         if (mode == 3) sig = c == 0 ? &a : &b;
         const bool side = c == side_channel;
-        encode_subframe(p, bw, *sig, bs, p.bps + (side ? 1 : 0), !side, acc_bits, f.index * 8 + c + (p.seed & 7));
+        encode_subframe(p, bw, *sig, bs, p.bps + (side ? 1 : 0), !side, acc_bits, fgc::subframe_salt(p, f.index, c),
+                        (g_trace && f.index * C + c < g_trace_records) ? g_trace + 8 * (f.index * C + c) : nullptr);
     }
     bw.align();
     const uint16_t crc = crc16(out.data() + start, out.size() - start);
@@ -733,7 +472,7 @@ int generate(const fg_params &p, int want_pcm, fg_result *out, uint32_t threads)
     Md5 md5;
     {
         const uint32_t hb = (p.bps + 7) / 8;
-        const uint32_t msb = (p.bps >= 9 && p.bps <= 15) ? 16 - p.bps : (p.bps >= 17 && p.bps <= 31) ? 32 - p.bps : 0;
+        const uint32_t msb = fgc::msb_shift_of(p.bps);
         const uint64_t n = p.n_samples * p.channels;
         if (hb == cb && msb == 0) md5.update(pcm, pcm_bytes);
         else {
@@ -822,6 +561,13 @@ int fg_generate_batch(const fg_params *ps, uint32_t n, int want_pcm, fg_result *
     for (uint32_t t = 0; t < std::min(n_threads, std::max(1u, n)); ++t) ts.emplace_back(worker);
     for (auto &t : ts) t.join();
     return rc;
+}
+
+// Debug: subframe records of the NEXT single-stream fg_generate call go to buf (8 words per subframe, frame-major);
+// nullptr switches the trace off.
+void fg_set_trace(uint32_t *buf, uint64_t n_records) {
+    g_trace = buf;
+    g_trace_records = buf ? n_records : 0;
 }
 
 void fg_free(fg_result *r) {

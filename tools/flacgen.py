@@ -19,6 +19,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "_build", "libflacgen.so")
 _SRC = os.path.join(_HERE, "flacgen.cpp")
+_HDR = os.path.join(_HERE, "flacgen_common.h")
 
 
 class Params(C.Structure):
@@ -38,11 +39,12 @@ class _Result(C.Structure):
 
 
 def build(force: bool = False) -> str:
-    stale = (not os.path.exists(_LIB)) or os.path.getmtime(_SRC) > os.path.getmtime(_LIB)
+    stale = (not os.path.exists(_LIB)) or max(os.path.getmtime(_SRC), os.path.getmtime(_HDR)) > os.path.getmtime(_LIB)
     if force or stale:
         os.makedirs(os.path.dirname(_LIB), exist_ok=True)
         # x86-64-v3, not -march=native: the .so built here also runs on the GPU box's host CPU
-        subprocess.run(["g++", "-O3", "-march=x86-64-v3", "-std=c++17", "-shared", "-fPIC", "-pthread", "-Wall",
+        # -ffp-contract=off: the CUDA generator must reproduce every double of this one (flacgen_common.h)
+        subprocess.run(["g++", "-O3", "-march=x86-64-v3", "-ffp-contract=off", "-std=c++17", "-shared", "-fPIC", "-pthread", "-Wall",
                         "-o", _LIB, _SRC], check=True, capture_output=True)
     return _LIB
 
@@ -156,6 +158,131 @@ def c5_file(i: int, seconds: float = 1.0, **kw) -> Params:
     """BASELINE config 5: file i of the batch of short 16-bit stereo files (11 frames of 4096 at 1.0 s)."""
     return params(stereo_mode=4, subframe_mix=1, n_samples=int(seconds * 44100), seed=0x5EED1000 + i, n_threads=1,
                   amplitude=0.25 + 0.01 * (i % 7), noise=0.0008 + 0.0002 * (i % 5), **kw)
+
+
+# ---------------------------------------------------------------- the CUDA generator (tools/flacgen_cuda.cu)
+_CU_LIB = os.path.join(_HERE, "_build", "libflacgen_cuda.so")
+_CU_SRC = os.path.join(_HERE, "flacgen_cuda.cu")
+
+
+def build_cuda(force: bool = False) -> str:
+    """nvcc cross-compiles for sm_100a without a GPU. -fmad=false / -ffp-contract=off: see flacgen_common.h."""
+    stale = (not os.path.exists(_CU_LIB)) or max(os.path.getmtime(_CU_SRC), os.path.getmtime(_HDR)) > os.path.getmtime(_CU_LIB)
+    if force or stale:
+        os.makedirs(os.path.dirname(_CU_LIB), exist_ok=True)
+        subprocess.run(["nvcc", "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-fmad=false", "-lineinfo",
+                        "-Xcompiler", "-fPIC,-ffp-contract=off", "-shared", "-o", _CU_LIB, _CU_SRC], check=True, capture_output=True)
+    return _CU_LIB
+
+
+class _DevStream(C.Structure):
+    _fields_ = [("flac_off", C.c_uint64), ("flac_bytes", C.c_uint64), ("pcm_off", C.c_uint64), ("pcm_bytes", C.c_uint64),
+                ("n_frames", C.c_uint64), ("container_bytes", C.c_uint32), ("pad", C.c_uint32), ("md5", C.c_uint8 * 16)]
+
+
+_cu = None
+
+
+def lib_cuda():
+    global _cu
+    if _cu is None:
+        if not os.path.exists(_CU_LIB):
+            build_cuda()
+        _cu = C.CDLL(_CU_LIB)
+        _cu.fgc_generate.argtypes = [C.POINTER(Params), C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p)]
+        _cu.fgc_generate.restype = C.c_int
+        _cu.fgc_info.argtypes = [C.c_void_p, C.POINTER(_DevStream), C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
+        _cu.fgc_info.restype = C.c_int
+        _cu.fgc_copy.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        _cu.fgc_copy.restype = C.c_int
+        _cu.fgc_trace.argtypes = [C.c_void_p, C.c_void_p]
+        _cu.fgc_trace.restype = C.c_int
+        _cu.fgc_free.argtypes = [C.c_void_p]
+        _cu.fgc_free.restype = None
+        _cu.fgc_last_error.restype = C.c_char_p
+    return _cu
+
+
+class DeviceBatch:
+    """Streams generated in device memory by tools/flacgen_cuda.cu: one FLAC blob (stream i at streams[i]['flac_off'], a
+    multiple of `align`) and one PCM blob (what zflac.decode returns for every stream, at streams[i]['pcm_off']).
+    Same bytes as generate() / generate_batch() for the same parameters (tests/test_gpu_flacgen.py)."""
+
+    def __init__(self, ps: list[Params], device: int = 0, align: int = 16, keep_trace: bool = False):
+        self.params = list(ps)
+        n = len(self.params)
+        arr = (Params * n)(*self.params)
+        self._h = C.c_void_p()
+        rc = lib_cuda().fgc_generate(arr, n, device, align, 1 if keep_trace else 0, C.byref(self._h))
+        if rc != 0:
+            raise RuntimeError(f"flacgen_cuda failed with code {rc}: {lib_cuda().fgc_last_error().decode()}")
+        outs = (_DevStream * n)()
+        sizes = (C.c_uint64 * 4)()
+        secs = (C.c_double * 6)()
+        lib_cuda().fgc_info(self._h, outs, sizes, secs)
+        self.flac_bytes, self.pcm_bytes, self.n_frames, self.n_subframes = (int(x) for x in sizes)
+        self.seconds = dict(zip(("host_plan", "alloc_upload", "encode_kernels", "write_kernels", "md5", "total"), (float(x) for x in secs)))
+        self.streams = [dict(flac_off=int(o.flac_off), flac_bytes=int(o.flac_bytes), pcm_off=int(o.pcm_off), pcm_bytes=int(o.pcm_bytes),
+                             n_frames=int(o.n_frames), container_bytes=int(o.container_bytes), md5=bytes(o.md5)) for o in outs]
+        self.device = device
+
+    def copy_to(self, flac_ptr: int = 0, flac_on_device: bool = True, pcm_ptr: int = 0, pcm_on_device: bool = True, stream: int = 0):
+        """Copies the blobs to caller memory (raw pointers: a torch tensor's data_ptr() or a numpy array's ctypes.data)."""
+        rc = lib_cuda().fgc_copy(self._h, flac_ptr or None, int(flac_on_device), pcm_ptr or None, int(pcm_on_device), stream or None)
+        if rc != 0:
+            raise RuntimeError(f"fgc_copy failed with code {rc}: {lib_cuda().fgc_last_error().decode()}")
+
+    def to_host(self, want_pcm: bool = True):
+        flac = np.empty(self.flac_bytes, dtype=np.uint8)
+        pcm = np.empty(self.pcm_bytes, dtype=np.uint8) if want_pcm else None
+        self.copy_to(flac.ctypes.data, False, pcm.ctypes.data if want_pcm else 0, False)
+        return flac, pcm
+
+    def synths(self, want_pcm: bool = True) -> list[Synth]:
+        """The streams as host-side Synth objects (what generate() returns)."""
+        flac, pcm = self.to_host(want_pcm)
+        out = []
+        for p, s in zip(self.params, self.streams):
+            f = flac[s["flac_off"]: s["flac_off"] + s["flac_bytes"]].copy()
+            x = pcm[s["pcm_off"]: s["pcm_off"] + s["pcm_bytes"]].view(_DT[s["container_bytes"]]).copy() if want_pcm else None
+            out.append(Synth(f, x, s["md5"], s["n_frames"], 42, s["container_bytes"], p))
+        return out
+
+    def trace(self) -> np.ndarray:
+        t = np.zeros((self.n_subframes, 8), dtype=np.uint32)
+        rc = lib_cuda().fgc_trace(self._h, t.ctypes.data)
+        if rc != 0:
+            raise RuntimeError(f"fgc_trace failed with code {rc} (keep_trace=True?): {lib_cuda().fgc_last_error().decode()}")
+        return t
+
+    def close(self):
+        if self._h:
+            lib_cuda().fgc_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
+def generate_device(ps, device: int = 0, align: int = 16, keep_trace: bool = False) -> DeviceBatch:
+    return DeviceBatch([ps] if isinstance(ps, Params) else list(ps), device, align, keep_trace)
+
+
+def cpu_trace(p: Params) -> tuple[Synth, np.ndarray]:
+    """generate(p) plus the per-subframe debug records of the CPU generator (fg_set_trace)."""
+    bs = 16 if p.variable_blocksize else max(1, int(p.block_size))
+    n_rec = (int(p.n_samples) // bs + 8) * int(p.channels) * (8 if p.variable_blocksize else 1)
+    t = np.zeros((n_rec, 8), dtype=np.uint32)
+    lib().fg_set_trace.argtypes = [C.c_void_p, C.c_uint64]
+    lib().fg_set_trace(t.ctypes.data, n_rec)
+    try:
+        s = generate(p)
+    finally:
+        lib().fg_set_trace(None, 0)
+    return s, t[: s.n_frames * int(p.channels)]
 
 
 if __name__ == "__main__":

@@ -222,6 +222,11 @@ def stitch_ranges(rows, audio_offset: int) -> bool:
     return bool(_native.load().zflacb200_stitch(buf, len(rows), int(audio_offset)))
 
 
+def trim() -> None:
+    """Hands the library's idle device blocks back to the driver (zflacb200_trim); open handles stay valid."""
+    _native.load().zflacb200_trim()
+
+
 BLOCK_TYPES = ("STREAMINFO", "PADDING", "APPLICATION", "SEEKTABLE", "VORBIS_COMMENT", "CUESHEET", "PICTURE")
 
 

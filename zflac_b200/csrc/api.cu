@@ -281,10 +281,12 @@ int ensure_device(int device, int *resolved) {
         for (auto &l : c.lane) CU_CHECK(cudaStreamCreateWithFlags(&l, cudaStreamNonBlocking));
         CU_CHECK(cudaHostAlloc((void **)&c.mailbox, 8 * (2 + 4096), cudaHostAllocDefault));
         CU_CHECK(scan_init_constants());
-        cudaMemPool_t pool;
-        CU_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
-        uint64_t thresh = ~0ull;  // keep freed blocks cached: open() allocates the same sizes again and again
-        CU_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+        if (use_driver_pool()) {  // ZFLACB200_ALLOC=pool (A/B runs) only: the process's default pool is not ours to retune otherwise
+            cudaMemPool_t pool;
+            CU_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
+            uint64_t thresh = ~0ull;  // keep freed blocks cached: open() allocates the same sizes again and again
+            CU_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+        }
         c.ready = true;
     }
     *resolved = device;
@@ -2131,6 +2133,8 @@ void zflacb200_shutdown(void) {
     g_cache.release_all();  // after the streams are gone: every block is idle
     if (prev >= 0) cudaSetDevice(prev);
 }
+
+void zflacb200_trim(void) { g_cache.release_all(); }
 
 const char *zflacb200_status_name(int status) {
     switch (status) {

@@ -8,8 +8,8 @@
 // with an event recorded on the freeing stream; a request takes the smallest cached block that fits
 // (and is not wastefully large) and, if it was freed on another stream, makes the new stream wait
 // for that event. Only a miss calls cudaMalloc. 180 GB of HBM3e: the cache is allowed to hold on to
-// ZFLACB200_CACHE_MAX_MIB (default 64 GiB) of idle blocks; above that, and whenever cudaMalloc
-// fails, idle blocks are returned to the driver.
+// ZFLACB200_CACHE_MAX_MIB (default: a quarter of the device's memory) of idle blocks; above that, and
+// whenever cudaMalloc fails, idle blocks are returned to the driver; zflacb200_trim() returns all of them.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -131,10 +131,15 @@ class DevCache {
         if (bytes < (1u << 20)) return (bytes + 511) & ~(size_t)511;
         return (bytes + (2u << 20) - 1) & ~(size_t)((2u << 20) - 1);
     }
+    // idle blocks the cache may sit on: ZFLACB200_CACHE_MAX_MIB, else a quarter of the device's memory (45 GiB on a B200) —
+    // invisible to a co-resident allocator, so not more; zflacb200_trim() / zflacb200_shutdown() hand everything back
     static size_t limit() {
         static const size_t v = [] {
             const char *e = getenv("ZFLACB200_CACHE_MAX_MIB");
-            return (size_t)(e ? strtoull(e, nullptr, 10) : 65536ull) << 20;
+            if (e) return (size_t)strtoull(e, nullptr, 10) << 20;
+            size_t free_b = 0, total_b = 0;
+            if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || total_b == 0) return (size_t)16 << 30;
+            return total_b / 4;
         }();
         return v;
     }
