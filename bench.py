@@ -55,6 +55,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--files", type=int, default=10000, help="c5: number of files in the batch (whole job)")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling legs (strong_c2r, strong_c5) of the default line")
+    ap.add_argument("--generator", default="cuda", choices=["cuda", "cpu"],
+                    help="who builds the synthetic input: tools/flacgen_cuda.cu in HBM (default) or tools/flacgen.cpp on the host (same bytes)")
     ap.add_argument("--no-pin", action="store_true", help="do not pin the rank's threads to the GPU's NUMA node")
     return ap.parse_args()
 
@@ -308,16 +310,35 @@ def main():
     p, wl_name = workload_params(args, rank)
     p.n_threads = max(1, (os.cpu_count() or 1) // max(1, min(world, 8)))
     t0 = time.time()
-    synth = fg.generate(p, want_pcm=True)
-    t_gen = time.time() - t0
+    if args.generator == "cuda":
+        # the input is BUILT in HBM (tools/flacgen_cuda.cu, same bytes as tools/flacgen.cpp); the stream and
+        # the expected PCM stay on the device, host copies are made for the end-to-end legs only
+        dgen = fg.generate_device(p, device=local_rank)
+        gen_secs = {"generator": "cuda", **{k: round(v, 3) for k, v in dgen.seconds.items()}}
+        d_flac = torch.empty(dgen.flac_bytes, dtype=torch.uint8, device=dev)
+        d_exp = torch.empty(dgen.pcm_bytes, dtype=torch.uint8, device=dev)
+        dgen.copy_to(d_flac.data_ptr(), True, d_exp.data_ptr(), True)
+        st0 = dgen.streams[0]
+        dgen.close()
+        t_gen = time.time() - t0
+        h_flac = torch.empty(d_flac.numel(), dtype=torch.uint8).pin_memory()     # e2e input: pinned host
+        h_flac.copy_(d_flac)
+        synth = fg.Synth(h_flac.numpy(), d_exp.cpu().numpy().view(fg._DT[st0["container_bytes"]]), st0["md5"], st0["n_frames"], 42,
+                         st0["container_bytes"], p)
+        gen_secs["host_copies_s"] = round(time.time() - t0 - t_gen, 3)
+    else:
+        synth = fg.generate(p, want_pcm=True)
+        t_gen = time.time() - t0
+        gen_secs = {"generator": "cpu", "total": round(t_gen, 3)}
+        d_flac = torch.from_numpy(synth.flac).to(dev)                       # resident in HBM before the timed region
+        d_exp = torch.from_numpy(synth.pcm.view(np.uint8)).to(dev)
+        h_flac = torch.from_numpy(synth.flac).pin_memory()                   # e2e input: pinned host
     n_samples = int(synth.pcm.size)
     cb = synth.container_bytes
     pcm_bytes = n_samples * cb
     flac_bytes = int(synth.flac.size)
     audio_bytes = flac_bytes - synth.audio_offset
 
-    d_flac = torch.from_numpy(synth.flac).to(dev)                       # resident in HBM before the timed region
-    h_flac = torch.from_numpy(synth.flac).pin_memory()                   # e2e input: pinned host
     h_pcm = torch.empty(pcm_bytes, dtype=torch.uint8).pin_memory()       # e2e output: pinned host
     stream = torch.cuda.current_stream()
     sptr = stream.cuda_stream
@@ -371,14 +392,14 @@ def main():
 
     # parity of what was just timed: PCM bit-exact vs the generator's PCM, MD5 == STREAMINFO MD5
     s = z.open_device(d_flac.data_ptr(), flac_bytes, device=local_rank, stream=sptr, verify_md5=True)
-    exp = torch.from_numpy(synth.pcm.view(np.uint8)).to(dev)
+    exp = d_exp
     import ctypes as C
     got = torch.empty(pcm_bytes, dtype=torch.uint8, device=dev)
     C.cdll.LoadLibrary("libcudart.so.12").cudaMemcpy(C.c_void_p(got.data_ptr()), C.c_void_p(s.device_ptr()), C.c_size_t(pcm_bytes), 3)
     parity_ok = bool(torch.equal(got, exp)) and s.info["md5_computed"] == synth.md5 and s.n_samples == n_samples
     ms_md5_kernel = s.info["ms_md5"]
     s.close()
-    del exp, got
+    del exp, got, d_exp
     if not parity_ok:
         raise SystemExit("PARITY FAILURE: device PCM / MD5 differs from the generator's")
 
@@ -479,7 +500,7 @@ def main():
         "workload_detail": {"samples_per_step_per_gpu": n_samples, "frames": int(info0["n_frames"]),
                             "compressed_bytes": flac_bytes, "pcm_bytes": pcm_bytes, "sharding": "one stream per GPU, no collective",
                             "l2": "inputs larger than L2 (no flush needed)" if flac_bytes > 126 * 2**20 else "input smaller than L2",
-                            "generator_s": round(t_gen, 2)},
+                            "generator_s": round(t_gen, 2), "generator": gen_secs},
         "gated": gated,
         **strong,
         "compressed_gbs": round(world * flac_bytes / (ms_dev * 1e-3) / 1e9, 3),

@@ -39,3 +39,27 @@ def test_corrupted_frames_do_not_change_reference_semantics():
     bad_payload = s.flac.copy()
     bad_payload[end - 40] ^= 0x10
     assert oracle.decode(bad_payload).error != "OK"
+
+
+def test_cuda_generator_library_builds_and_exports_its_interface():
+    """tools/flacgen_cuda.cu cross-compiles for sm_100a and exports the entry points tools/flacgen.py
+    binds; without a device a call fails with a CUDA error instead of falling back to the CPU generator."""
+    import ctypes as C
+    from tools import flacgen as fg
+    lib = C.CDLL(fg.build_cuda())
+    for name in ("fgc_generate", "fgc_info", "fgc_copy", "fgc_trace", "fgc_free", "fgc_last_error"):
+        assert hasattr(lib, name), name
+    import torch
+    if not torch.cuda.is_available():
+        import pytest
+        with pytest.raises(RuntimeError, match="code 3"):
+            fg.generate_device(fg.c2(1.0))
+
+
+def test_cpu_generator_trace_describes_every_subframe():
+    from tools import flacgen as fg
+    p = fg.c4_variable(3.0)
+    s, t = fg.cpu_trace(p)
+    assert t.shape == (s.n_frames * 2, 8)
+    assert set(np.unique(t[:, 0])) <= set(range(0, 64)) and (t[:, 5] > 0).all()   # a type and a bit count each
+    assert np.array_equal(fg.generate(p).flac, s.flac)                               # tracing changes nothing

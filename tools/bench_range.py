@@ -45,7 +45,8 @@ def run(args, rank, world, local_rank, metric, ClockSampler, measured_peak):
     p = fg.c2(secs)
     p.n_threads = max(1, (os.cpu_count() or 1) // max(1, min(world, 8)))
     t0 = time.time()
-    synth = fg.generate(p, want_pcm=True)  # same seed on every rank: the same stream
+    # same seed on every rank: the same stream
+    (synth,), gen_secs = fg.generate_on(None if getattr(args, "generator", "cuda") == "cpu" else local_rank, p, want_pcm=True)
     t_gen = time.time() - t0
     C = int(p.channels)
     n_samples = int(synth.pcm.size)
@@ -125,7 +126,7 @@ def run(args, rank, world, local_rank, metric, ClockSampler, measured_peak):
                    "l2": "inputs larger than L2 (no flush needed)" if flac_bytes // world > 126 * 2**20 else
                          "a shard's compressed bytes fit L2, but they are uploaded again every step; scratch + PCM written per step exceed L2",
                    "value_is": "whole stream / slowest rank's kernel time (upload and read-back excluded); e2e is host to host",
-                   "generator_s": round(t_gen, 2)},
+                   "generator_s": round(t_gen, 2), "generator": {k: (round(v, 3) if isinstance(v, float) else v) for k, v in gen_secs.items()}},
         "kernel_ms": {f: round(v, 4) for f, v in k.items()},
         "parity": "every rank's slice bit-exact vs the generator's PCM; shards stitched by zflacb200_stitch (checked on this run)",
         "roofline": {"bound": "hbm", "kernel": "k_parse_frames", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",

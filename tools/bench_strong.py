@@ -88,7 +88,7 @@ def strong_c2r(rank, world, local_rank, dev, stream, barrier, steps=5, warmup=2,
 
     p = fg.c2(seconds)  # the same seed on every rank: the same stream (as N processes that mapped the same file would hold)
     p.n_threads = max(1, (os.cpu_count() or 1) // max(1, min(world, 8)))
-    synth = fg.generate(p, want_pcm=(rank == 0))
+    synth = fg.generate_on(local_rank, p, want_pcm=(rank == 0))[0][0]  # built in HBM by tools/flacgen_cuda.cu
     C, cb = int(p.channels), synth.container_bytes
     n_samples = int(p.n_samples) * C
     pcm_bytes, flac_bytes = n_samples * cb, int(synth.flac.size)
@@ -155,7 +155,7 @@ def strong_c5(rank, world, local_rank, dev, stream, barrier, steps=5, warmup=2, 
 
     threads = max(1, (os.cpu_count() or 1) // max(1, min(world, 8)))
     ids = sharding.round_robin(files, world)[rank]
-    mine = fg.generate_batch([fg.c5_file(i) for i in ids], want_pcm=True, n_threads=threads)
+    mine = fg.generate_on(local_rank, [fg.c5_file(i) for i in ids], want_pcm=True)[0]
     sptr = stream.cuda_stream
 
     def prepare(fs):
@@ -198,7 +198,7 @@ def strong_c5(rank, world, local_rank, dev, stream, barrier, steps=5, warmup=2, 
     n1 = None
     if world > 1:  # the whole batch on rank 0 alone, in this run
         if rank == 0:
-            rest = fg.generate_batch([fg.c5_file(i) for i in range(files) if i % world != 0], want_pcm=False, n_threads=os.cpu_count() or 1)
+            rest = fg.generate_on(local_rank, [fg.c5_file(i) for i in range(files) if i % world != 0], want_pcm=False)[0]
             allf = sorted(list(zip(ids, mine)) + list(zip([i for i in range(files) if i % world != 0], rest)), key=lambda t: t[0])
             m1_dev, m1_e2e, _, _ = legs([f for _, f in allf], lambda: None)
             n1 = (m1_dev, m1_e2e)

@@ -243,8 +243,9 @@ class DeviceBatch:
         flac, pcm = self.to_host(want_pcm)
         out = []
         for p, s in zip(self.params, self.streams):
-            f = flac[s["flac_off"]: s["flac_off"] + s["flac_bytes"]].copy()
-            x = pcm[s["pcm_off"]: s["pcm_off"] + s["pcm_bytes"]].view(_DT[s["container_bytes"]]).copy() if want_pcm else None
+            # views of the two host blobs (PCM offsets are multiples of 16): no per-stream copies
+            f = flac[s["flac_off"]: s["flac_off"] + s["flac_bytes"]]
+            x = pcm[s["pcm_off"]: s["pcm_off"] + s["pcm_bytes"]].view(_DT[s["container_bytes"]]) if want_pcm else None
             out.append(Synth(f, x, s["md5"], s["n_frames"], 42, s["container_bytes"], p))
         return out
 
@@ -269,6 +270,26 @@ class DeviceBatch:
 
 def generate_device(ps, device: int = 0, align: int = 16, keep_trace: bool = False) -> DeviceBatch:
     return DeviceBatch([ps] if isinstance(ps, Params) else list(ps), device, align, keep_trace)
+
+
+def generate_on(device, ps, want_pcm: bool = True, n_threads: int = 0):
+    """The streams ps (one Params or a list) as host Synth objects, built by the CUDA generator on `device` (an int) or,
+    with device=None, by the CPU generator. Returns (list of Synth, seconds dict) — same bytes either way."""
+    import time
+    single = isinstance(ps, Params)
+    lst = [ps] if single else list(ps)
+    t0 = time.time()
+    if device is None:
+        out = [generate(lst[0], want_pcm)] if single else generate_batch(lst, want_pcm, n_threads)
+        return out, {"generator": "cpu", "total": time.time() - t0}
+    d = DeviceBatch(lst, device)
+    try:
+        out = d.synths(want_pcm)
+        secs = dict(d.seconds)
+    finally:
+        d.close()
+    secs.update(generator="cuda", in_hbm=secs["total"], total=time.time() - t0)  # total includes the copy to the host
+    return out, secs
 
 
 def cpu_trace(p: Params) -> tuple[Synth, np.ndarray]:

@@ -884,13 +884,20 @@ int fgc_generate(const fg_params *ps, uint32_t n, int device, uint32_t align, ui
     SubInfo *d_subs;
     uint32_t *d_frame_len;
     uint8_t *d_pcm;
-    const size_t base_rows = max_bs;
+    const size_t base_rows = (max_bs + 3) & ~3u;
+    const bool timing = getenv("FLACGEN_TIMING") != nullptr;
     if (!mem.get(&d_streams, n) || !mem.get(&d_frames, n_frames) || !mem.get(&d_phases, phases.size()) ||
-        !mem.get(&d_windows, windows.size()) || !mem.get(&d_sig, sig_total) || !mem.get(&d_sub, sig_total) ||
-        !mem.get(&d_res, sig_total) || !mem.get(&d_plan, (size_t)n_subs * plan_stride) || !mem.get(&d_crc, 8 * 256) ||
+        !mem.get(&d_windows, windows.size()) || !mem.get(&d_sig, sig_total) ||
+        !mem.get(&d_plan, (size_t)n_subs * plan_stride) || !mem.get(&d_crc, 8 * 256) ||
         !mem.get(&d_subs, n_subs) || !mem.get(&d_frame_len, n_frames) || !mem.get(&d_pcm, pcm_total + 64))
         return 3;
-    if (any_stereo && !mem.get(&d_base, (size_t)((n_frames + 31) / 32) * base_rows * 32)) return 3;
+    d_res = d_sig;  // the residuals overwrite the channel samples, which nothing reads after k_channels
+    const size_t base_count = any_stereo ? (size_t)((n_frames + 31) / 32) * base_rows * 32 : 0;
+    if (any_stereo && !mem.get(&d_base, base_count)) return 3;
+    // the subframe signals take over the base buffer (dead once k_synth is through) when it is large enough
+    if (base_count * sizeof(double) >= sig_total * sizeof(int32_t)) d_sub = reinterpret_cast<int32_t *>(d_base);
+    else if (!mem.get(&d_sub, sig_total)) return 3;
+    if (timing) fprintf(stderr, "flacgen_cuda: cudaMalloc %.3f s\n", now_s() - t_plan);
     FGC_CK(cudaMemcpy(d_streams, streams.data(), n * sizeof(StreamDev), cudaMemcpyHostToDevice));
     FGC_CK(cudaMemcpy(d_frames, frames.data(), n_frames * sizeof(FrameJob), cudaMemcpyHostToDevice));
     FGC_CK(cudaMemcpy(d_phases, phases.data(), phases.size() * sizeof(ToneState), cudaMemcpyHostToDevice));
@@ -898,6 +905,7 @@ int fgc_generate(const fg_params *ps, uint32_t n, int device, uint32_t align, ui
     FGC_CK(cudaMemcpy(d_crc, crc_tables, sizeof(crc_tables), cudaMemcpyHostToDevice));
     FGC_CK(cudaMemsetAsync(d_pcm, 0, pcm_total + 64));
     const double t_up = now_s();
+    if (timing) fprintf(stderr, "flacgen_cuda: plan %.3f s, malloc + upload %.3f s\n", t_plan - t_start, t_up - t_plan);
 
     // ---- signal, channels, predictors, residuals, Rice plans
     k_synth<<<(n_frames + 63) / 64, 64>>>(d_streams, d_frames, n_frames, d_phases, d_sig, d_base, (uint32_t)base_rows);
