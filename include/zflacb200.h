@@ -336,6 +336,39 @@ typedef struct zflacb200_frame {
 } zflacb200_frame;
 int zflacb200_frames(zflacb200_stream *s, zflacb200_frame *dst, size_t capacity, size_t *n_frames);
 
+/* Frame-header scan for callers that may not allocate. NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc. It is the
+ * pipeline's first kernel (K1, k_sync_scan: every position whose bytes are a grammar-valid frame header with a matching
+ * CRC-8, in stream order) with its scratch — one look-back word per 64 KB tile and a ticket — in a file-scope device array
+ * of the library (128 KiB + 256 B, on every GPU that loads the library, until the process exits) instead of the block
+ * cache. The call makes no cudaMalloc / cudaFree and no allocating library call: it enqueues two memsets of the scratch,
+ * one of *d_count and the kernel on `stream`, and returns without synchronising.
+ *   d_stream, len   the stream's bytes IN DEVICE MEMORY, 16-byte aligned; bytes at or past len are never read
+ *   scan_begin      first byte position to test (the audio offset, or 0: a false match inside metadata is the caller's to drop)
+ *   d_headers       DEVICE array of `capacity` records, 16-byte aligned; record i = the i-th header found
+ *   d_count         DEVICE word: headers found; when it exceeds `capacity` only the first `capacity` were stored
+ *   device, stream  CUDA device ordinal (-1 = current; the caller's current device is restored) and cudaStream_t
+ * At most ZFLACB200_SCAN_NO_ALLOC_MAX_BYTES from scan_begin to len per call: beyond that ZFLACB200_INVALID_ARGUMENT (split
+ * the range, or use zflacb200_open). EVERY call on a device shares the one array, which keeps the last call's contents
+ * (the call clears what it uses): calls that overlap on the GPU — two streams, two threads — race and corrupt each
+ * other's ranks; order them on one stream or with events. Candidates are hints, as everywhere in this library: the
+ * frames of a stream are those zflacb200_frames() reports after the chain rules were checked. */
+#define ZFLACB200_SCAN_NO_ALLOC_MAX_BYTES (1ull << 30)
+typedef struct zflacb200_frame_header {
+    uint64_t offset;       /* byte offset of the sync code */
+    uint64_t number;       /* coded frame number (fixed block size) or first sample number (variable) */
+    uint32_t block_size;   /* 1..65535 */
+    uint32_t sample_rate;  /* as the frame header states it, 0 = "see STREAMINFO" */
+    uint8_t header_len;    /* bytes, CRC-8 included */
+    uint8_t channel_code;  /* 4-bit channel assignment */
+    uint8_t depth_code;    /* 3-bit sample size code */
+    uint8_t rate_code;     /* 4-bit sample rate code */
+    uint8_t variable;      /* blocking strategy bit */
+    uint8_t pad[3];
+} zflacb200_frame_header;
+int zflacb200_scan_no_alloc(const void *d_stream, uint64_t len, uint64_t scan_begin, zflacb200_frame_header *d_headers,
+                            uint32_t capacity, uint32_t *d_count, int device, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,7 +19,7 @@ MD5_ON_DEVICE = 0x100
 RANGE_INTO_WHOLE = 0x200
 
 EXPORTS = [
-    "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown", "zflacb200_trim",
+    "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown", "zflacb200_trim", "zflacb200_scan_no_alloc",
     "zflacb200_status_name", "zflacb200_last_error", "zflacb200_kernel_launches", "zflacb200_pass_a_launches", "zflacb200_open", "zflacb200_read",
     "zflacb200_device_pcm", "zflacb200_close", "zflacb200_decode", "zflacb200_pcm_bound", "zflacb200_frames", "zflacb200_batch_open",
     "zflacb200_batch_pcm_bytes", "zflacb200_batch_read_all", "zflacb200_batch_read_stream", "zflacb200_batch_device_pcm",
@@ -107,6 +107,8 @@ def load():
     lib.zflacb200_device_count.restype = C.c_int
     lib.zflacb200_shutdown.restype = None
     lib.zflacb200_trim.restype = None
+    lib.zflacb200_scan_no_alloc.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_void_p]
+    lib.zflacb200_scan_no_alloc.restype = C.c_int
     lib.zflacb200_status_name.argtypes = [C.c_int]
     lib.zflacb200_status_name.restype = C.c_char_p
     lib.zflacb200_last_error.restype = C.c_char_p

@@ -39,6 +39,14 @@ thread_local std::string g_last_error;
 // (they share its streams, pinned arena and mailbox). The reference's decode() is re-entrant; so is this.
 std::mutex g_dev_mutex[64];
 
+}  // namespace
+
+namespace zf {
+void set_last_error(const char *msg) { g_last_error = msg ? msg : ""; }  // for entry points that live in other files
+}
+
+namespace {
+
 struct DeviceCtx {
     bool ready = false;
     cudaStream_t stream = nullptr;

@@ -15,6 +15,7 @@ extern std::atomic<unsigned long long> g_pass_a_launches[kPassAVariants];
 
 // scan.cu
 cudaError_t scan_init_constants();
+void set_last_error(const char *msg);  // api.cu: what zflacb200_last_error() reports for the calling thread
 uint32_t scan_tile_count(uint64_t scan_begin, uint64_t len);
 cudaError_t launch_sync_scan(const uint8_t *d_stream, uint64_t scan_begin, uint64_t len, Cand *d_cands, uint32_t cap,
                              uint32_t *d_total, unsigned long long *d_tile_state, uint32_t *d_ticket, cudaStream_t st);

@@ -11,6 +11,10 @@
 // starts" without entropy-decoding it, which is what lets K2 decode every frame in parallel
 // with its output offset already known. A mismatch proves nothing (the reference would
 // still decode the frame, Q1): the host then probes that frame's end with K2 instead.
+#include <mutex>
+#include <string>
+
+#include "../../include/zflacb200.h"
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -580,3 +584,98 @@ cudaError_t launch_crc16_frames(const uint8_t *d_stream, const FrameRec *d_recs,
 }
 
 }  // namespace zf
+
+// ---------------------------------------------------------------------------------------------------------------
+// zflacb200_scan_no_alloc — K1 for callers that may not allocate (no counterpart in the reference; include/zflacb200.h).
+//
+// k_sync_scan needs scratch that every other path takes from the library's block cache (cudaMalloc on a miss): one
+// look-back word per 64 KB tile and a ticket counter. Here that scratch is a file-scope device array, part of the
+// library's image on every GPU that loads it (128 KiB + 256 B, held until the process exits), so the call allocates
+// nothing: two stream-ordered memsets and the launch.
+//
+// g_scan_scratch below is the DEVICE symbol. In host code the name is only a stand-in (its host address means nothing
+// to a kernel), so the device address is fetched with cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr uint32_t kNoAllocMaxTiles = 16384;  // x 64 KB = ZFLACB200_SCAN_NO_ALLOC_MAX_BYTES (1 GiB) of stream per call
+constexpr uint32_t kNoAllocWords = kNoAllocMaxTiles + 32;  // tile states, then 256 bytes of counters (word 0 of them: the ticket)
+
+static __device__ __align__(256) unsigned long long g_scan_scratch[kNoAllocWords];
+
+std::mutex g_scan_scratch_mutex;
+unsigned long long *g_scan_scratch_ptr[64];  // per device ordinal: the array's address ON THAT DEVICE (nullptr = not asked yet)
+
+// the caller's device is current again when this goes out of scope
+struct DeviceSwitch {
+    int prev = -1;
+    bool switched = false;
+    cudaError_t to(int device) {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) return e;
+        if (prev == device) return cudaSuccess;
+        e = cudaSetDevice(device);
+        switched = e == cudaSuccess;
+        return e;
+    }
+    ~DeviceSwitch() {
+        if (switched) cudaSetDevice(prev);
+    }
+};
+
+}  // namespace
+
+extern "C" int zflacb200_scan_no_alloc(const void *d_stream, uint64_t len, uint64_t scan_begin, zflacb200_frame_header *d_headers,
+                                       uint32_t capacity, uint32_t *d_count, int device, void *stream) {
+    static_assert(sizeof(zflacb200_frame_header) == sizeof(zf::Cand), "zflacb200_frame_header is the scan's candidate record");
+    static_assert(ZFLACB200_SCAN_NO_ALLOC_MAX_BYTES == (uint64_t)kNoAllocMaxTiles * zf::kScanTileBytes, "stated maximum");
+    if (!d_stream || !d_count || (!d_headers && capacity != 0)) {
+        zf::set_last_error("zflacb200_scan_no_alloc: null argument");
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    if ((reinterpret_cast<uintptr_t>(d_stream) & 15u) != 0 || (reinterpret_cast<uintptr_t>(d_headers) & 15u) != 0) {
+        zf::set_last_error("zflacb200_scan_no_alloc: d_stream and d_headers must be 16-byte aligned device pointers");
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    if (scan_begin > len) scan_begin = len;
+    if (len - (scan_begin & ~15ull) > ZFLACB200_SCAN_NO_ALLOC_MAX_BYTES) {
+        zf::set_last_error("zflacb200_scan_no_alloc: more than ZFLACB200_SCAN_NO_ALLOC_MAX_BYTES (1 GiB) to scan in one call: "
+                           "split the range or use zflacb200_open");
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    int dev = device;
+    if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) {
+        cudaGetLastError();
+        zf::set_last_error("zflacb200_scan_no_alloc: no current CUDA device");
+        return ZFLACB200_CUDA_ERROR;
+    }
+    if (dev < 0 || dev >= 64) {
+        zf::set_last_error("zflacb200_scan_no_alloc: device ordinal out of range");
+        return ZFLACB200_INVALID_ARGUMENT;
+    }
+    DeviceSwitch sw;
+    cudaError_t e = sw.to(dev);
+    unsigned long long *scratch = nullptr;
+    if (e == cudaSuccess) {
+        std::lock_guard<std::mutex> lk(g_scan_scratch_mutex);
+        if (!g_scan_scratch_ptr[dev]) {  // set-up, once per device, with that device current
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_scan_scratch);
+            if (e == cudaSuccess) g_scan_scratch_ptr[dev] = static_cast<unsigned long long *>(p);
+        }
+        scratch = g_scan_scratch_ptr[dev];
+    }
+    if (e == cudaSuccess) {
+        // the array keeps the last call's contents: launch_sync_scan_range clears the tile states it uses, the ticket
+        // and *d_count on `stream` ahead of the kernel
+        e = zf::launch_sync_scan_range(static_cast<const uint8_t *>(d_stream), scan_begin, len, len, reinterpret_cast<zf::Cand *>(d_headers),
+                                       capacity, d_count, scratch, reinterpret_cast<uint32_t *>(scratch + kNoAllocMaxTiles),
+                                       static_cast<cudaStream_t>(stream));
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        zf::set_last_error((std::string("zflacb200_scan_no_alloc: ") + cudaGetErrorString(e)).c_str());
+        return ZFLACB200_CUDA_ERROR;
+    }
+    return ZFLACB200_OK;
+}
