@@ -39,30 +39,63 @@ __device__ __forceinline__ uint32_t crc8_byte(uint32_t crc, uint32_t b) { return
 __constant__ uint32_t c_rate_table[16] = {0, 88200, 176400, 192000, 8000, 16000, 22050, 24000,
                                           32000, 44100, 48000, 96000, 0, 0, 0, 0};
 
+// The 16 stream bytes at position p as two little-endian 64-bit words (bytes at or past len read as zero). Where the
+// two 16-byte groups around p are inside the stream they come as two aligned vector loads (L1 / L2 hits: the scan has just
+// read them) and funnel shifts — the check of a filter hit used to be 33 dependent byte loads, which is what the other
+// warps of the tile waited for at the barrier (r04q).
+__device__ __forceinline__ void fetch16(const uint8_t *__restrict__ s, uint64_t p, uint64_t len, uint64_t &lo, uint64_t &hi) {
+    const uint64_t a = p & ~15ull;
+    if (a + 32 <= len) {
+        const uint4 x = __ldg(reinterpret_cast<const uint4 *>(s + a)), y = __ldg(reinterpret_cast<const uint4 *>(s + a + 16));
+        const uint32_t wi = (uint32_t)(p & 15u) >> 2, sh = (uint32_t)(p & 3u) * 8u;
+        // the five words that hold bytes p .. p + 15
+        const uint32_t w0 = wi == 0 ? x.x : wi == 1 ? x.y : wi == 2 ? x.z : x.w;
+        const uint32_t w1 = wi == 0 ? x.y : wi == 1 ? x.z : wi == 2 ? x.w : y.x;
+        const uint32_t w2 = wi == 0 ? x.z : wi == 1 ? x.w : wi == 2 ? y.x : y.y;
+        const uint32_t w3 = wi == 0 ? x.w : wi == 1 ? y.x : wi == 2 ? y.y : y.z;
+        const uint32_t w4 = wi == 0 ? y.x : wi == 1 ? y.y : wi == 2 ? y.z : y.w;
+        const uint32_t o0 = __funnelshift_r(w0, w1, sh), o1 = __funnelshift_r(w1, w2, sh);
+        const uint32_t o2 = __funnelshift_r(w2, w3, sh), o3 = __funnelshift_r(w3, w4, sh);
+        lo = (uint64_t)o0 | ((uint64_t)o1 << 32);
+        hi = (uint64_t)o2 | ((uint64_t)o3 << 32);
+        return;
+    }
+    lo = 0;
+    hi = 0;
+    for (int i = 0; i < 16 && p + i < len; ++i) {
+        const uint64_t v = s[p + i];
+        if (i < 8) lo |= v << (8 * i);
+        else hi |= v << (8 * (i - 8));
+    }
+}
+__device__ __forceinline__ uint32_t byte_of(uint64_t lo, uint64_t hi, int i) {  // i in [0, 16)
+    return (uint32_t)((i < 8 ? lo >> (8 * i) : hi >> (8 * (i - 8))) & 0xFFu);
+}
+
 // Full header check at byte position p. Returns true and fills `c` when the bytes at p are a
 // frame header the reference would accept (grammar) AND the CRC-8 matches.
 __device__ __noinline__ bool parse_header_at(const uint8_t *__restrict__ s, uint64_t p, uint64_t len, Cand &c) {
     if (p + 6 > len) return false;
-    uint8_t b[16];
     const int avail = (len - p) < 16 ? (int)(len - p) : 16;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) b[i] = (i < avail) ? s[p + i] : 0;
-    if (b[0] != 0xFF || (b[1] & 0xFE) != 0xF8) return false;
-    const uint32_t bs_code = b[2] >> 4, sr_code = b[2] & 15, ch_code = b[3] >> 4, bd_code = (b[3] >> 1) & 7;
+    uint64_t lo, hi;
+    fetch16(s, p, len, lo, hi);
+    const uint32_t b0 = (uint32_t)lo & 0xFFu, b1 = (uint32_t)(lo >> 8) & 0xFFu, b2 = (uint32_t)(lo >> 16) & 0xFFu, b3 = (uint32_t)(lo >> 24) & 0xFFu;
+    if (b0 != 0xFF || (b1 & 0xFE) != 0xF8) return false;
+    const uint32_t bs_code = b2 >> 4, sr_code = b2 & 15, ch_code = b3 >> 4, bd_code = (b3 >> 1) & 7;
     if (bs_code == 0 || sr_code == 15 || ch_code > 10 || bd_code == 3) return false;
-    const uint32_t c0 = b[4];
+    const uint32_t c0 = (uint32_t)(lo >> 32) & 0xFFu;
     const uint32_t ones = __clz((int)((~c0 & 0xFFu) << 24 | 0x00800000u));  // leading ones of c0 (0..8)
     if (c0 == 0xFF || ones == 1) return false;
     int n = 4 + (ones == 0 ? 1 : (int)ones);
     // value of the UTF-8-like number (:203-214 checks the lead byte only; continuation bytes are taken as they are)
     uint64_t number = ones == 0 ? c0 : (c0 & (0x7Fu >> ones));
-    for (int i = 5; i < n; ++i) number = (number << 6) | (b[i] & 0x3Fu);
+    for (int i = 5; i < n; ++i) number = (number << 6) | (byte_of(lo, hi, i) & 0x3Fu);
     uint32_t block_size;
     if (bs_code == 6) {
-        block_size = (uint32_t)b[n] + 1;
+        block_size = byte_of(lo, hi, n) + 1;
         n += 1;
     } else if (bs_code == 7) {
-        const uint32_t v = ((uint32_t)b[n] << 8) | b[n + 1];
+        const uint32_t v = (byte_of(lo, hi, n) << 8) | byte_of(lo, hi, n + 1);
         if (v == 0xFFFF) return false;
         block_size = v + 1;
         n += 2;
@@ -75,19 +108,19 @@ __device__ __noinline__ bool parse_header_at(const uint8_t *__restrict__ s, uint
     }
     uint32_t sr_value = c_rate_table[sr_code];
     if (sr_code == 12) {
-        sr_value = b[n];
+        sr_value = byte_of(lo, hi, n);
         n += 1;
     } else if (sr_code == 13) {
-        sr_value = ((uint32_t)b[n] << 8) | b[n + 1];
+        sr_value = (byte_of(lo, hi, n) << 8) | byte_of(lo, hi, n + 1);
         n += 2;
     } else if (sr_code == 14) {
-        sr_value = 10u * (((uint32_t)b[n] << 8) | b[n + 1]);
+        sr_value = 10u * ((byte_of(lo, hi, n) << 8) | byte_of(lo, hi, n + 1));
         n += 2;
     }
     if (n + 1 > avail) return false;
     uint32_t crc = 0;
-    for (int i = 0; i < n; ++i) crc = crc8_byte(crc, b[i]);
-    if (crc != b[n]) return false;
+    for (int i = 0; i < n; ++i) crc = crc8_byte(crc, byte_of(lo, hi, i));
+    if (crc != byte_of(lo, hi, n)) return false;
     c.offset = p;
     c.block_size = block_size;
     c.sr_value = sr_value;
@@ -96,7 +129,7 @@ __device__ __noinline__ bool parse_header_at(const uint8_t *__restrict__ s, uint
     c.bd_code = (uint8_t)bd_code;
     c.sr_code = (uint8_t)sr_code;
     c.number = number;
-    c.strategy = (uint8_t)(b[1] & 1u);
+    c.strategy = (uint8_t)(b1 & 1u);
     c.pad[0] = c.pad[1] = c.pad[2] = 0;
     return true;
 }
@@ -146,7 +179,13 @@ __device__ __forceinline__ uint32_t sync_filter4(uint32_t cur, uint32_t nxt, uin
 static __device__ __noinline__ void scan_check_chunk(const uint8_t *__restrict__ s, uint64_t pos, uint64_t tile_base, uint64_t scan_begin,
                                                      uint64_t scan_end, uint64_t len, uint32_t *bits) {
     uint32_t w[5] = {0, 0, 0, 0, 0};
-    for (int i = 0; i < 17 && pos + i < len; ++i) w[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+    if (pos + 32 <= len) {  // pos is a multiple of 16
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(s + pos));
+        w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+        w[4] = __ldg(reinterpret_cast<const uint32_t *>(s + pos + 16));
+    } else {
+        for (int i = 0; i < 17 && pos + i < len; ++i) w[i >> 2] |= (uint32_t)s[pos + i] << (8 * (i & 3));
+    }
     const uint32_t z0 = sync_hits4(w[0], __funnelshift_r(w[0], w[1], 8)), z1 = sync_hits4(w[1], __funnelshift_r(w[1], w[2], 8));
     const uint32_t z2 = sync_hits4(w[2], __funnelshift_r(w[2], w[3], 8)), z3 = sync_hits4(w[3], __funnelshift_r(w[3], w[4], 8));
     uint32_t raw = hits_to_mask4(z0) | (hits_to_mask4(z1) << 4) | (hits_to_mask4(z2) << 8) | (hits_to_mask4(z3) << 12);
