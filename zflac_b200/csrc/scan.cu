@@ -176,8 +176,17 @@ __device__ __forceinline__ uint32_t sync_filter4(uint32_t cur, uint32_t nxt, uin
 // The exact test + header check of one 16-byte chunk whose filter fired (rare): sets the bit of every validated header.
 // Chunks are queued by the scanning threads and checked afterwards, one chunk per thread, so that a hit costs the
 // scanning warp a handful of instructions instead of a header check executed for one lane of it.
+// The headers a tile validated, kept in shared memory so that writing them out in order does not parse them again
+// (the second parse was a tenth of the kernel's instructions, executed for one lane at a time).
+constexpr uint32_t kTileCands = 24;  // a 64 KB tile of audio has ~10; beyond: parsed again where they are written
+struct TileCands {
+    Cand c[kTileCands];
+    uint16_t rel[kTileCands];
+    uint32_t n;
+};
+
 static __device__ __noinline__ void scan_check_chunk(const uint8_t *__restrict__ s, uint64_t pos, uint64_t tile_base, uint64_t scan_begin,
-                                                     uint64_t scan_end, uint64_t len, uint32_t *bits) {
+                                                     uint64_t scan_end, uint64_t len, uint32_t *bits, TileCands *cache) {
     uint32_t w[5] = {0, 0, 0, 0, 0};
     if (pos + 32 <= len) {  // pos is a multiple of 16
         const uint4 v = __ldg(reinterpret_cast<const uint4 *>(s + pos));
@@ -197,6 +206,11 @@ static __device__ __noinline__ void scan_check_chunk(const uint8_t *__restrict__
         if (p >= scan_begin && p < scan_end && parse_header_at(s, p, len, c)) {
             const uint32_t rel = (uint32_t)(p - tile_base);
             atomicOr(&bits[rel >> 5], 1u << (rel & 31u));
+            const uint32_t k = atomicAdd(&cache->n, 1u);
+            if (k < kTileCands) {
+                cache->c[k] = c;
+                cache->rel[k] = (uint16_t)rel;
+            }
         }
     }
 }
@@ -212,10 +226,12 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     __shared__ unsigned long long s_base;
     __shared__ uint32_t s_nq;
     __shared__ uint16_t s_queue[kScanQueue];  // chunk index (tile byte / 16) of every chunk whose filter fired
+    __shared__ __align__(16) TileCands s_cands;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) {
         s_tile = atomicAdd(ticket, 1u);  // tiles start in order: look-back below cannot deadlock
         s_nq = 0;
+        s_cands.n = 0;
     }
     uint32_t c1, c6;  // filter constants the compiler must keep in registers (see sync_filter4)
     asm("mov.b32 %0, 0x01010101;" : "=r"(c1));
@@ -234,42 +250,35 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     auto queue_chunk = [&](uint64_t pos) {  // rare
         const uint32_t q = atomicAdd(&s_nq, 1u);
         if (q < kScanQueue) s_queue[q] = (uint16_t)((pos - tile_base) >> 4);
-        else scan_check_chunk(s, pos, tile_base, scan_begin, scan_end, len, s_bits);
+        else scan_check_chunk(s, pos, tile_base, scan_begin, scan_end, len, s_bits, &s_cands);
     };
-    if (interior) {  // the whole tile and the byte after it are inside the stream: no length checks
-        const uint4 *src = reinterpret_cast<const uint4 *>(s + tile_base) + tid;
-        const uint8_t *edge = s + tile_base + (uint64_t)tid * 16 + 16;  // lane 31: the byte after the warp's 512 (the next warp's first)
+    if (interior) {  // the whole tile and the 16 bytes after it are inside the stream: no length checks
+        // warp w scans the CONTIGUOUS 8 KB [8192 w, 8192 w + 8192) of the tile, 16 rows of 512 bytes: the byte after
+        // lane 31's sixteen is lane 0's first byte of the next row, which is in registers already (rows are
+        // prefetched four ahead) — one extra load per warp and tile instead of one per row
+        const uint64_t warp_base = tile_base + (uint64_t)warp * (kScanRows * 512);
+        const uint4 *src = reinterpret_cast<const uint4 *>(s + warp_base) + lane;
         uint4 v[4], nx[4];
-        uint32_t e[4] = {0, 0, 0, 0}, ne[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            v[r] = __ldg(src + r * kScanThreads);
-            if (lane == 31) e[r] = __ldg(edge + r * (kScanThreads * 16));
-        }
+        for (int r = 0; r < 4; ++r) v[r] = __ldg(src + r * 32);
+        const uint32_t after = __ldg(reinterpret_cast<const uint32_t *>(s + warp_base + kScanRows * 512));  // the next warp's (tile's) first bytes
 #pragma unroll 1
         for (int r0 = 0; r0 < kScanRows; r0 += 4) {
-            if (r0 + 4 < kScanRows) {  // the next four rows (and their edge bytes) are on their way while these four are tested
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    nx[r] = __ldg(src + (r0 + 4 + r) * kScanThreads);
-                    if (lane == 31) ne[r] = __ldg(edge + (r0 + 4 + r) * (kScanThreads * 16));
-                }
-            }
+            for (int r = 0; r < 4; ++r) nx[r] = (r0 + 4 < kScanRows) ? __ldg(src + (r0 + 4 + r) * 32) : make_uint4(after, 0, 0, 0);
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
+                const uint32_t next_row0 = __shfl_sync(0xFFFFFFFFu, r < 3 ? v[r + 1].x : nx[0].x, 0);
                 uint32_t nb = __shfl_down_sync(0xFFFFFFFFu, v[r].x, 1);  // the byte after my 16: the next lane's first
-                if (lane == 31) nb = e[r];
+                if (lane == 31) nb = next_row0;
                 const uint32_t w0 = v[r].x, w1 = v[r].y, w2 = v[r].z, w3 = v[r].w;
                 const uint32_t f = (sync_filter4(w0, __funnelshift_r(w0, w1, 8), c1, c6) | sync_filter4(w1, __funnelshift_r(w1, w2, 8), c1, c6) |
                                     sync_filter4(w2, __funnelshift_r(w2, w3, 8), c1, c6) | sync_filter4(w3, __funnelshift_r(w3, nb, 8), c1, c6)) &
                                    0x80808080u;
-                if (f) queue_chunk(tile_base + (uint64_t)(r0 + r) * (kScanThreads * 16) + (uint64_t)tid * 16);
+                if (f) queue_chunk(warp_base + (uint64_t)(r0 + r) * 512 + (uint64_t)lane * 16);
             }
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                v[r] = nx[r];
-                e[r] = ne[r];
-            }
+            for (int r = 0; r < 4; ++r) v[r] = nx[r];
         }
     } else {
 #pragma unroll 1
@@ -296,7 +305,7 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
     {
         const uint32_t nq = s_nq < kScanQueue ? s_nq : kScanQueue;
         for (uint32_t q = tid; q < nq; q += kScanThreads)
-            scan_check_chunk(s, tile_base + (uint64_t)s_queue[q] * 16, tile_base, scan_begin, scan_end, len, s_bits);
+            scan_check_chunk(s, tile_base + (uint64_t)s_queue[q] * 16, tile_base, scan_begin, scan_end, len, s_bits, &s_cands);
     }
     __syncthreads();
 
@@ -364,9 +373,22 @@ k_sync_scan(const uint8_t *__restrict__ s, uint64_t scan_begin, uint64_t scan_en
         while (m) {
             const int b = __ffs(m) - 1;
             m &= m - 1;
-            Cand c;
-            parse_header_at(s, tile_base + (uint64_t)tid * 256 + (uint64_t)k * 32 + b, len, c);  // validated above
-            if (slot < cap) out[slot] = c;
+            const uint32_t rel = (uint32_t)tid * 256u + (uint32_t)k * 32u + (uint32_t)b;
+            if (slot < cap) {
+                const uint32_t nc = s_cands.n < kTileCands ? s_cands.n : kTileCands;
+                uint32_t j = 0;
+                while (j < nc && s_cands.rel[j] != rel) ++j;
+                if (j < nc) {
+                    const uint4 *src = reinterpret_cast<const uint4 *>(&s_cands.c[j]);
+                    uint4 *dst = reinterpret_cast<uint4 *>(out + slot);
+                    dst[0] = src[0];
+                    dst[1] = src[1];
+                } else {
+                    Cand c;
+                    parse_header_at(s, tile_base + rel, len, c);  // validated above
+                    out[slot] = c;
+                }
+            }
             ++slot;
         }
     }
