@@ -119,6 +119,9 @@ struct PosReader {
 //   lane and TMA's per-request cost); value extraction in a second phase through a shared-memory tile +25 (+37 with two
 //   warps per scheduler): with ~21 instructions a row, most on the half-rate ALU pipe, two warps per scheduler are
 //   bound by instruction throughput, not by the chain's latency — so the work below is counted in instructions.
+//   Moving shifts to the FMA pipe as IMAD.HI (f >> 23 and f >> sh as the high word of a product with an opaque power of
+//   two: 113 -> 97 ALU-pipe instructions a body) made the kernel SLOWER, 0.575 -> 0.591 ms on C2, with either one of the
+//   two alone as well (r06j): IMAD.HI is no half-rate instruction here.
 // ---------------------------------------------------------------------------------------
 struct RiceParams {
     uint32_t C;      // 158 + k + 1: (Q - C) + exponent = Q - (zeros + 1 + k)
