@@ -173,7 +173,8 @@ def pcie_floor_ms(torch, dev, h_in, n_out_bytes, reps=5):
     return best, total / reps
 
 
-PASS_A_VARIANTS = ("k_parse_frames<StagedSrc>", "k_parse_frames<QuadSrc>", "k_parse_frames_narrow<64>", "k_parse_frames_narrow<32>")
+PASS_A_VARIANTS = ("k_parse_frames<StagedSrc>", "k_parse_frames<QuadSrc>", "k_parse_frames_narrow<64>", "k_parse_frames_narrow<32>",
+                   "k_parse_frames_narrow<64, WIDE>", "k_parse_frames_narrow<32, WIDE>")
 
 
 def pass_a_counts():

@@ -71,6 +71,8 @@ typedef enum zflacb200_status {
                                           * ignores it, :551): info.n_crc16_mismatch stays 0, zflacb200_frame.crc16_ok says 2 = not checked */
 #define ZFLACB200_NO_PIPELINE 0x40u    /* diagnostics: zflacb200_decode uploads, decodes and reads back one after the other */
 #define ZFLACB200_SINGLE_PASS 0x20u    /* diagnostics: fused single-pass subframe decoder (K2 + K3) instead of parse + predict */
+#define ZFLACB200_WORD_PIPELINE 0x400u /* diagnostics: pass A of 17..31-bit streams by the first bit reader (word pipeline, parse_core.cuh) instead of
+                                        * the position reader (parse_narrow.cuh, WIDE): the A/B of the two, and what keeps both kernels tested */
 #define ZFLACB200_MD5_ON_DEVICE 0x100u /* diagnostics: run a single stream's MD5 chain on the GPU (k_md5, 119 MB/s) instead of on a host
                                         * thread over the PCM as it lands in host memory (the default for streams >= 256 KiB of PCM;
                                         * batches always hash on the device, one chain per lane) */
@@ -122,7 +124,8 @@ const char *zflacb200_last_error(void);        /* thread-local detail for CUDA_E
 uint64_t zflacb200_kernel_launches(void);      /* kernels this library has launched since load (bench: gpu_launches) */
 /* diagnostics: launches of pass A (the frame-serial bit-chain kernel) by instantiation since load. variant 0:
  * k_parse_frames<StagedSrc> (int32 scratch, one wave), 1: k_parse_frames<QuadSrc> (int32 scratch, more frames than one
- * wave holds), 2: k_parse_frames_narrow<64> (streams of <= 16 bits), 3: k_parse_frames_narrow<32> (the same, large launches). */
+ * wave holds), 2: k_parse_frames_narrow<64> (streams of <= 16 bits), 3: k_parse_frames_narrow<32> (the same, large launches),
+ * 4 / 5: k_parse_frames_narrow<64 / 32, WIDE> (int32 rows: streams of 17..31 bits; 0 / 1 then only run with ZFLACB200_WORD_PIPELINE). */
 uint64_t zflacb200_pass_a_launches(int variant);
 
 /* Replaces the body of decode() (src/zflac.zig:217-310): signature + metadata walk,

@@ -138,8 +138,9 @@ int zf_host_parse_frame(const uint8_t *stream, const zf::FrameRec *fr, int32_t *
 // Narrow pass A (parse_narrow.cuh) on the host: int16 rows into `scratch`. layout 0: the frame's own region
 // (kLayoutFrame, scratch_base 0); layout 1: the warp-interleaved one (kLayoutWarp) as lane `lane` of a warp whose region
 // starts at scratch. Returns the unchecked-read violations (must be 0); *overflow != 0 when a value did not fit 16 bits.
+// wide != 0: int32 rows (parse_narrow.cuh, WIDE) — no overflow is ever reported.
 int zf_host_parse_frame_narrow(const uint8_t *stream, const zf::FrameRec *fr, uint16_t *scratch, zf::SubRec *subs, int write_samples,
-                               zf::FrameOut *out, uint32_t *overflow, int layout, int lane) {
+                               zf::FrameOut *out, uint32_t *overflow, int layout, int lane, int wide) {
     const uint64_t start = fr->offset + fr->header_len;
     const uint64_t origin = start & ~15ull;  // the device source starts at a 16-byte aligned address
     const uint64_t bytes = fr->stream_end > origin ? fr->stream_end - origin : 0;
@@ -151,11 +152,12 @@ int zf_host_parse_frame_narrow(const uint8_t *stream, const zf::FrameRec *fr, ui
     br.src.violations = 0;
     br.init_at((uint32_t)(start - origin));
     zf::NarrowSink sink;
-    if (layout == zf::kLayoutWarp) sink.set_warp(scratch, 0, (uint32_t)lane, fr->block_size);
-    else sink.set_frame(scratch, 0, fr->channels);
+    if (layout == zf::kLayoutWarp) sink.set_warp(scratch, 0, (uint32_t)lane, fr->block_size, wide != 0);
+    else sink.set_frame(scratch, 0, fr->channels, wide != 0);
     uint32_t max_order = 0;
     *overflow = 0;
-    zf::parse_frame_narrow(br, *fr, sink, subs, bytes * 8, write_samples != 0, origin, *out, max_order, *overflow);
+    if (wide) zf::parse_frame_narrow<HostPairSrc, true>(br, *fr, sink, subs, bytes * 8, write_samples != 0, origin, *out, max_order, *overflow);
+    else zf::parse_frame_narrow<HostPairSrc, false>(br, *fr, sink, subs, bytes * 8, write_samples != 0, origin, *out, max_order, *overflow);
     return br.src.violations;
 }
 

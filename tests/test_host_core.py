@@ -48,16 +48,17 @@ def core():
     lib.zf_host_predict_plane.restype = None
     assert lib.zf_host_subrec_size() == 80
     lib.zf_host_parse_frame_narrow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
-                                               C.c_int, C.c_int]
+                                               C.c_int, C.c_int, C.c_int]
     lib.zf_host_parse_frame_narrow.restype = C.c_int
     return lib
 
 
-def host_decode(lib, data: bytes, ref, two_pass: bool = False, narrow: bool = False, stats=None):
+def host_decode(lib, data: bytes, ref, two_pass: bool = False, narrow: bool = False, stats=None, pos_wide: bool = False):
     """Decode all frames of the oracle's frame trace with the host core; return interleaved PCM like the reference's.
     two_pass: pass A (parse_core.cuh) + a scalar restatement of pass B instead of the single-pass decoder.
     narrow: pass A is parse_narrow.cuh (PosReader, folded 16-bit scratch); a frame that reports overflow is redone with
-    parse_core.cuh, the way the host library falls back (stats["overflow_frames"] counts them)."""
+    parse_core.cuh, the way the host library falls back (stats["overflow_frames"] counts them).
+    pos_wide: pass A is parse_narrow.cuh with int32 rows (WIDE), both layouts alternating; nothing can overflow."""
     arr = np.frombuffer(data, dtype=np.uint8)
     ch, bps = ref.channels, ref.bits_per_sample
     wide = bps == 32
@@ -78,7 +79,25 @@ def host_decode(lib, data: bytes, ref, two_pass: bool = False, narrow: bool = Fa
             assert not wide
             subs = np.zeros(8 * 80, dtype=np.uint8)
             done = False
-            if narrow:
+            if pos_wide:
+                nb = pitch // 8
+                warp_layout = (int(fr["offset"]) // 7) % 2 == 1
+                lane = int(fr["offset"]) % 32
+                s32 = np.zeros(ch * nb * 2 * 32 * 4 if warp_layout else pitch * ch, dtype=np.int32)
+                ovf = np.zeros(1, dtype=np.uint32)
+                viol = lib.zf_host_parse_frame_narrow(arr.ctypes.data, rec.ctypes.data, s32.ctypes.data, subs.ctypes.data, 1,
+                                                      out.ctypes.data, ovf.ctypes.data, int(warp_layout), lane, 1)
+                assert viol == 0, "unchecked ring entry read outside the top_up guarantee"
+                assert int(ovf[0]) == 0
+                if warp_layout:  # half h of row t of channel c of lane L at (((c * nb + t) * 2 + h) * 32 + L) * 16 bytes
+                    rows = s32.reshape(ch, nb, 2, 32, 4)
+                    assert not rows[:, :, :, np.arange(32) != lane, :].any(), "wrote into another lane's rows"
+                    planes32 = rows[:, :, :, lane, :].reshape(ch, pitch)
+                    scratch = planes32.reshape(ch, pitch // 8, 8).transpose(1, 0, 2).reshape(-1).copy()  # the sub_idx() layout
+                else:
+                    scratch = s32  # the per-frame layout IS sub_idx()
+                done = True
+            elif narrow:
                 # both row layouts of parse_narrow.cuh, alternating from frame to frame: the frame's own region (groups of
                 # 16 steps x channels x 16 values) and the warp-interleaved one (row t of channel c of lane L at
                 # ((c * nb + t) * 32 + L) * 16 bytes), here as a lane that changes with the frame
@@ -88,7 +107,7 @@ def host_decode(lib, data: bytes, ref, two_pass: bool = False, narrow: bool = Fa
                 s16 = np.zeros(ch * nb * 32 * 8 if warp_layout else (bs + 15) // 16 * 16 * ch, dtype=np.uint16)
                 ovf = np.zeros(1, dtype=np.uint32)
                 viol = lib.zf_host_parse_frame_narrow(arr.ctypes.data, rec.ctypes.data, s16.ctypes.data, subs.ctypes.data, 1,
-                                                      out.ctypes.data, ovf.ctypes.data, int(warp_layout), lane)
+                                                      out.ctypes.data, ovf.ctypes.data, int(warp_layout), lane, 0)
                 assert viol == 0, "unchecked ring entry read outside the top_up guarantee"
                 if int(ovf[0]) == 0:
                     if warp_layout:
@@ -210,4 +229,32 @@ def test_host_parse_narrow_synth(core, name):
     if ref.bits_per_sample == 32:
         pytest.skip("32 bps streams stay on the single-pass int64 decoder")
     got = host_decode(core, data, ref, two_pass=True, narrow=True)
+    assert np.array_equal(got, ref.samples)
+
+
+@pytest.mark.parametrize("entry", [e for e in corpus_entries() if not e["expect_error"]],
+                         ids=[i for i, e in zip(corpus_ids(), corpus_entries()) if not e["expect_error"]])
+def test_host_parse_pos_wide_corpus(core, entry):
+    """Pass A with the position reader and int32 rows (parse_narrow.cuh, WIDE: what 17..31-bit streams take, and the
+    rerun of a narrower launch group that overflowed 16 bits) + the recurrence == the oracle, frame ends included, on
+    every stream of the corpus up to 31 bits per sample, both row layouts."""
+    data = corpus_bytes(entry)
+    ref = oracle.decode(data, trace_frames=True)
+    if ref.error != "OK":
+        pytest.skip(f"oracle: {ref.error}")
+    if ref.bits_per_sample == 32:
+        pytest.skip("32 bps streams stay on the single-pass int64 decoder")
+    got = host_decode(core, data, ref, two_pass=True, pos_wide=True)
+    assert np.array_equal(got, ref.samples)
+
+
+@pytest.mark.parametrize("name", sorted(synth_cases.CASES))
+def test_host_parse_pos_wide_synth(core, name):
+    s = synth_cases.make(name)
+    data = s.flac.tobytes()
+    ref = oracle.decode(data, trace_frames=True)
+    assert ref.error == "OK"
+    if ref.bits_per_sample == 32:
+        pytest.skip("32 bps streams stay on the single-pass int64 decoder")
+    got = host_decode(core, data, ref, two_pass=True, pos_wide=True)
     assert np.array_equal(got, ref.samples)

@@ -671,11 +671,13 @@ struct DevBuf {  // stream-ordered allocation released on scope exit
 struct SubframeStage {
     bool two_pass = false;
     bool narrow = false;  // uint16 scratch of folded residuals (parse_narrow.cuh): streams of <= 16 bits per sample
+    bool word_pipeline = false;  // diagnostics (ZFLACB200_WORD_PIPELINE): int32 rows by the first pass A (parse_core.cuh) instead of the position reader
     DevBuf b_subs, b_big;  // b_big: {some order above 12, a value did not fit the narrow scratch}
     // depth: bits per sample by STREAMINFO (largest of a batch group); 0 or allow_narrow = false keeps the int32 scratch
     int prepare(bool wide, uint32_t flags, uint32_t n_recs, cudaStream_t st, uint32_t depth = 0, bool allow_narrow = true) {
         two_pass = !wide && (flags & ZFLACB200_SINGLE_PASS) == 0;
         narrow = false;
+        word_pipeline = (flags & ZFLACB200_WORD_PIPELINE) != 0;
         if (!two_pass) return ZFLACB200_OK;
         static const bool env_no_narrow = getenv("ZFLACB200_NO_NARROW") != nullptr;  // diagnostics: A/B runs
         narrow = allow_narrow && !env_no_narrow && depth >= 1 && depth <= 16;
@@ -695,7 +697,7 @@ struct SubframeStage {
         else if (two_pass)
             CU_CHECK(launch_parse_frames(d_stream, d_recs, n, (int32_t *)d_scratch,
                                          (SubRec *)((uint8_t *)b_subs.p + kSubRecBytes * 8 * (size_t)first), d_outs, (uint32_t *)b_big.p,
-                                         write, st));
+                                         write, st, word_pipeline));
         else
             CU_CHECK(launch_decode_frames(d_stream, d_recs, n, d_scratch, wide, d_outs, write, st));
         return ZFLACB200_OK;

@@ -10,7 +10,7 @@ namespace zf {
 extern std::atomic<unsigned long long> g_kernel_launches;
 #define ZF_COUNT_LAUNCH() (::zf::g_kernel_launches.fetch_add(1, std::memory_order_relaxed))
 // which instantiation of pass A a launch took (zflacb200_pass_a_launches): the parity tests make every variant run
-enum { kPassAStaged = 0, kPassAQuad = 1, kPassANarrow64 = 2, kPassANarrow32 = 3, kPassAVariants = 4 };
+enum { kPassAStaged = 0, kPassAQuad = 1, kPassANarrow64 = 2, kPassANarrow32 = 3, kPassAWide64 = 4, kPassAWide32 = 5, kPassAVariants = 6 };
 extern std::atomic<unsigned long long> g_pass_a_launches[kPassAVariants];
 
 // scan.cu
@@ -60,7 +60,8 @@ cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_fram
 struct SubRec;  // parse_core.cuh
 constexpr size_t kSubRecBytes = 80;  // sizeof(SubRec); 8 slots per frame record
 cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, int32_t *d_scratch,
-                                SubRec *d_subs, FrameOut *d_outs, uint32_t *d_big_orders, bool write_samples, cudaStream_t st);
+                                SubRec *d_subs, FrameOut *d_outs, uint32_t *d_big_orders, bool write_samples, cudaStream_t st,
+                                bool word_pipeline = false);
 // narrow K2a (streams of <= 16 bits per sample): uint16 scratch of folded residuals; d_flags = {big orders, 16-bit overflow}
 cudaError_t launch_parse_frames_narrow(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, uint16_t *d_scratch,
                                        SubRec *d_subs, FrameOut *d_outs, uint32_t *d_flags, bool write_samples, cudaStream_t st);

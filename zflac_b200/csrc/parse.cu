@@ -44,7 +44,9 @@ k_parse_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frame
 // PairSrc ring in static shared memory; the scratch is uint16 (folded residuals as coded). flags[0]: some subframe has an
 // order above 12 (pass B then also runs its 32-tap kernel); flags[1]: a value did not fit 16 bits (the host redoes the
 // launch group on the int32 path).
-template <int RING>
+// WIDE: the same kernel with int32 rows (parse_narrow.cuh) for streams of 17..31 bits per sample, and for launch groups
+// of narrower streams that reported a value beyond 16 bits.
+template <int RING, bool WIDE = false>
 __global__ void __launch_bounds__(32, RING >= 64 ? 14 : 20)
 k_parse_frames_narrow(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frames, uint32_t n_frames,
                       uint16_t *__restrict__ scratch, SubRec *__restrict__ subs, FrameOut *__restrict__ outs,
@@ -64,11 +66,11 @@ k_parse_frames_narrow(const uint8_t *__restrict__ s, const FrameRec *__restrict_
     const uint64_t base0 = __shfl_sync(0xFFFFFFFFu, fr.scratch_base, 0);
     const uint64_t end31 = __shfl_sync(0xFFFFFFFFu, fr.scratch_base + (uint64_t)fr.channels * ((fr.block_size + 7u) & ~7u), 31);
     const bool alike = fr.block_size != 0 && fr.channels == c0 && fr.scratch_base >= base0;
-    const bool interleave = __all_sync(0xFFFFFFFFu, alike) && end31 >= base0 + 16ull * c0 * ((bs_max + 7u) & ~7u);
+    const bool interleave = __all_sync(0xFFFFFFFFu, alike) && end31 >= base0 + (WIDE ? 32ull : 16ull) * c0 * ((bs_max + 7u) & ~7u);
     if (fr.block_size == 0) return;  // dropped candidate slot / past the end
     NarrowSink sink;
-    if (interleave) sink.set_warp(scratch, base0, threadIdx.x, bs_max);
-    else sink.set_frame(scratch, fr.scratch_base, fr.channels);
+    if (interleave) sink.set_warp(scratch, base0, threadIdx.x, bs_max, WIDE);
+    else sink.set_frame(scratch, fr.scratch_base, fr.channels, WIDE);
     const uint64_t start = fr.offset + fr.header_len;  // first subframe header
     const uint32_t lead = (uint32_t)(reinterpret_cast<uintptr_t>(s + start) & 15u);
     const uint64_t origin = start - lead;
@@ -79,7 +81,7 @@ k_parse_frames_narrow(const uint8_t *__restrict__ s, const FrameRec *__restrict_
     const uint64_t len_bits = span * 8;
     FrameOut o;
     uint32_t max_order = 0, overflow = 0;
-    parse_frame_narrow(br, fr, sink, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order, overflow);
+    parse_frame_narrow<PairSrc<RING>, WIDE>(br, fr, sink, subs + (size_t)f * 8, len_bits, write_samples != 0, origin, o, max_order, overflow);
     if (max_order > 12 && write_samples) flags[0] = 1u;
     if (overflow && write_samples) flags[1] = 1u;
     outs[f] = o;
@@ -107,7 +109,8 @@ cudaError_t launch_parse_frames_narrow(const uint8_t *d_stream, const FrameRec *
 }
 
 cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, int32_t *d_scratch,
-                                SubRec *d_subs, FrameOut *d_outs, uint32_t *d_big_orders, bool write_samples, cudaStream_t st) {
+                                SubRec *d_subs, FrameOut *d_outs, uint32_t *d_big_orders, bool write_samples, cudaStream_t st,
+                                bool word_pipeline) {
     if (n_frames == 0) return cudaSuccess;
     const uint32_t blocks = (n_frames + kDecodeThreads - 1) / kDecodeThreads;
     ZF_COUNT_LAUNCH();
@@ -117,6 +120,18 @@ cudaError_t launch_parse_frames(const uint8_t *d_stream, const FrameRec *d_frame
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (sms <= 0) sms = 148;
+    }
+    if (!word_pipeline) {  // the position reader with int32 rows (parse_narrow.cuh, WIDE): the default
+        const uint32_t warps = (n_frames + 31u) / 32u;
+        const bool deep = warps <= (uint32_t)sms * 14u;
+        g_pass_a_launches[deep ? kPassAWide64 : kPassAWide32].fetch_add(1, std::memory_order_relaxed);
+        if (deep)
+            k_parse_frames_narrow<64, true><<<warps, 32, 0, st>>>(d_stream, d_frames, n_frames, reinterpret_cast<uint16_t *>(d_scratch), d_subs,
+                                                                  d_outs, d_big_orders, write_samples ? 1 : 0);
+        else
+            k_parse_frames_narrow<32, true><<<warps, 32, 0, st>>>(d_stream, d_frames, n_frames, reinterpret_cast<uint16_t *>(d_scratch), d_subs,
+                                                                  d_outs, d_big_orders, write_samples ? 1 : 0);
+        return cudaGetLastError();
     }
     // One-warp CTAs for the StagedSrc kernel: with 128-thread CTAs a 1-hour stream is 303 CTAs on 148 SMs, seven SMs
     // carry three CTAs (3 warps per scheduler instead of 2) and the whole launch waits 26 % longer for them

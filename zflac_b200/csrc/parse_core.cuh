@@ -223,6 +223,9 @@ ZF_HDI void parse_frame(BitReader<Src> &br, const FrameRec &fr, int32_t *__restr
             sub->shift = (uint8_t)shift;
             sub->wasted = (uint8_t)wasted;
             sub->wide_acc = (uint8_t)wide_acc;
+            sub->pad[0] = 0;  // kLayoutFrame (parse_narrow.cuh): pass B finds the rows in the frame's own region, sub_idx()
+            sub->pad[1] = 0;
+            sub->pad[2] = 0;
             sub->constant = constant;
         }
     }

@@ -38,6 +38,12 @@ ZF_HD uint32_t pack16(int32_t lo, int32_t hi) {  // two int16 in one word (PRMT)
 //                32-byte sector per channel and group, written by the same lane in two halves):
 //                frame_base + (t / 2) * 32 * C + c * 32 + (t % 2) * 16.
 // Both live inside the region the int32 layout would use (scratch_base counts 4-byte elements): room to spare.
+//
+// WIDE = true: the same pass A for streams of 17..31 bits per sample. Rows are eight int32 = two 16-byte halves, no
+// value can overflow, bodies are accepted for k <= 23 on the window fit alone. kLayoutFrame is then exactly the int32
+// layout of parse_core.cuh (sub_idx(): 32 bytes per channel and row, channels one after another); kLayoutWarp keeps the
+// two halves of a row 512 bytes apart so that each of a body's two store instructions writes 512 contiguous bytes:
+// half h of row t of channel c of lane L at warp_base + (((c * nb + t) * 2 + h) * 32 + L) * 16.
 enum : uint8_t { kLayoutFrame = 0, kLayoutWarp = 1 };
 
 struct NarrowSink {
@@ -46,38 +52,61 @@ struct NarrowSink {
     uint32_t row_shift;  // row t lives at (t >> row_shift) * row_stride + (t & row_mask) * 16
     uint32_t row_mask;
     uint32_t row_stride;
+    uint32_t half_off;   // WIDE: bytes from the first half of a row (values 0..3) to the second (values 4..7)
     uint16_t rows;       // kLayoutWarp: rows per channel of the warp's columns = ceil(longest block / 8), in SubRec.pad[1..2]
     uint8_t layout;
-    ZF_HD void set_frame(void *scratch, uint64_t scratch_base, uint32_t channels) {
+    ZF_HD void set_frame(void *scratch, uint64_t scratch_base, uint32_t channels, bool wide = false) {
         base = reinterpret_cast<uint8_t *>(scratch) + 4u * scratch_base;
         rows = 0;
         ch_stride = 32u;
-        row_shift = 1u;
-        row_mask = 1u;
+        row_shift = wide ? 0u : 1u;
+        row_mask = wide ? 0u : 1u;
         row_stride = 32u * channels;
+        half_off = 16u;
         layout = kLayoutFrame;
     }
-    ZF_HD void set_warp(void *scratch, uint64_t warp_scratch_base, uint32_t lane, uint32_t max_block_size) {
+    ZF_HD void set_warp(void *scratch, uint64_t warp_scratch_base, uint32_t lane, uint32_t max_block_size, bool wide = false) {
         base = reinterpret_cast<uint8_t *>(scratch) + 4u * warp_scratch_base + 16u * lane;
         rows = (uint16_t)((max_block_size + 7u) >> 3);  // <= 8192
-        ch_stride = rows * 512u;
+        row_stride = wide ? 1024u : 512u;
+        ch_stride = rows * row_stride;
         row_shift = 0u;
         row_mask = 0u;
-        row_stride = 512u;
+        half_off = 512u;
         layout = kLayoutWarp;
     }
 };
 struct NarrowOut {  // one channel's rows
     uint8_t *base;
-    uint32_t row_shift, row_mask, row_stride;
-    ZF_HD uint8_t *row(uint32_t i) const {  // the 16-byte row that holds step i
+    uint32_t row_shift, row_mask, row_stride, half_off;
+    ZF_HD uint8_t *row(uint32_t i) const {  // the row that holds step i (WIDE: its first half)
         const uint32_t t = i >> 3;
         return base + (size_t)(t >> row_shift) * row_stride + (t & row_mask) * 16u;
     }
-    ZF_HD void put(uint32_t i, int32_t v) const { reinterpret_cast<uint16_t *>(row(i))[i & 7u] = (uint16_t)v; }
+    template <bool WIDE>
+    ZF_HD void put(uint32_t i, int32_t v) const {
+        if (WIDE) reinterpret_cast<int32_t *>(row(i) + ((i >> 2) & 1u) * half_off)[i & 3u] = v;
+        else reinterpret_cast<uint16_t *>(row(i))[i & 7u] = (uint16_t)v;
+    }
+    // the eight values of a body, i a multiple of 8
+    template <bool WIDE>
+    ZF_HD void put8(uint32_t i, const int32_t (&r)[8]) const {
+        uint8_t *p = row(i);
+        if (WIDE) {
+            *reinterpret_cast<int4 *>(p) = make_int4(r[0], r[1], r[2], r[3]);
+            *reinterpret_cast<int4 *>(p + half_off) = make_int4(r[4], r[5], r[6], r[7]);
+        } else {
+            uint4 v;
+            v.x = pack16(r[0], r[1]);
+            v.y = pack16(r[2], r[3]);
+            v.z = pack16(r[4], r[5]);
+            v.w = pack16(r[6], r[7]);
+            *reinterpret_cast<uint4 *>(p) = v;
+        }
+    }
 };
 
-template <class Src>
+template <class Src, bool WIDE>
 ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, const NarrowOut &out, uint32_t order,
                                       uint32_t block_size, uint64_t len_bits, bool wr, uint32_t &overflow) {
     const uint32_t method = br.read(2);
@@ -122,14 +151,7 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, const NarrowOut &out, 
                 int32_t r[8];
 #pragma unroll
                 for (int u = 0; u < 8; ++u) r[u] = rice_value(fp[u], rp);
-                if (pend && wr) {
-                    uint4 v;
-                    v.x = pack16(r[0], r[1]);
-                    v.y = pack16(r[2], r[3]);
-                    v.z = pack16(r[4], r[5]);
-                    v.w = pack16(r[6], r[7]);
-                    *reinterpret_cast<uint4 *>(out.row(ip)) = v;  // ip is a multiple of 8
-                }
+                if (pend && wr) out.template put8<WIDE>(ip, r);  // ip is a multiple of 8
             }
 #pragma unroll
             for (int u = 0; u < 8; ++u) fp[u] = fn[u];
@@ -143,12 +165,10 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, const NarrowOut &out, 
         }
         if (pend) {  // leaving the run of bodies: finish the last one (k is still its partition's)
             if (wr) {
-                uint4 v;
-                v.x = pack16(rice_value(fp[0], rp), rice_value(fp[1], rp));
-                v.y = pack16(rice_value(fp[2], rp), rice_value(fp[3], rp));
-                v.z = pack16(rice_value(fp[4], rp), rice_value(fp[5], rp));
-                v.w = pack16(rice_value(fp[6], rp), rice_value(fp[7], rp));
-                *reinterpret_cast<uint4 *>(out.row(ip)) = v;
+                int32_t r[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) r[u] = rice_value(fp[u], rp);
+                out.template put8<WIDE>(ip, r);
             }
             pend = false;
         }
@@ -163,15 +183,15 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, const NarrowOut &out, 
 #pragma unroll 1
                 for (; i < end; ++i) {
                     const int32_t r = esc ? br.read_signed(esc) : 0;
-                    overflow |= misfit16(r);
-                    if (wr) out.put(i, r);
+                    if (!WIDE) overflow |= misfit16(r);
+                    if (wr) out.template put<WIDE>(i, r);
                     if ((i & 255u) == 255u && br.pos_bits() > len_bits) return ST_END_OF_STREAM;
                 }
                 continue;
             }
             k = param;
-            body_ok = k <= 16;
-            if (body_ok) rp.set(k);
+            body_ok = k <= (WIDE ? 23u : 16u);
+            if (body_ok) rp.set(k, WIDE);
         } else {  // one row
             const uint32_t win = br.peek();
             const uint32_t z = clz32(win);
@@ -185,10 +205,10 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, const NarrowOut &out, 
                 if (q == 0xFFFFFFFFu) return ST_END_OF_STREAM;
                 const uint32_t r = br.read(k);
                 cw = (q << k) + r;
-                if ((q >> 16) != 0) overflow |= 1u;  // q << k wrapped or is far beyond 16 bits either way
+                if (!WIDE && (q >> 16) != 0) overflow |= 1u;  // q << k wrapped or is far beyond 16 bits either way
             }
-            overflow |= cw >> 16;
-            if (wr) out.put(i, zigzag(cw));
+            if (!WIDE) overflow |= cw >> 16;
+            if (wr) out.template put<WIDE>(i, zigzag(cw));
             ++i;
             if (force_single) --force_single;
         }
@@ -199,7 +219,7 @@ ZF_HDI uint32_t parse_residual_narrow(PosReader<Src> &br, const NarrowOut &out, 
 }
 
 // One whole frame, subframes in channel order, then align + CRC-16 (:425-551). `sink` says where the frame's rows go.
-template <class Src>
+template <class Src, bool WIDE = false>
 ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const NarrowSink &sink, SubRec *__restrict__ subs,
                                uint64_t len_bits, bool wr, uint64_t origin_byte, FrameOut &o, uint32_t &max_order, uint32_t &overflow) {
     uint32_t status = ST_OK;
@@ -227,6 +247,7 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const Nar
         out.row_shift = sink.row_shift;
         out.row_mask = sink.row_mask;
         out.row_stride = sink.row_stride;
+        out.half_off = sink.half_off;
         SubRec *sub = subs + ch;
         uint32_t kind = kSubRaw, order = 0, shift = 0, wide_acc = 0;
         int32_t constant = 0;
@@ -241,8 +262,8 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const Nar
 #pragma unroll 1
             for (uint32_t i = 0; i < bs; ++i) {
                 const int32_t v = br.read_signed(n);
-                overflow |= misfit16(v);
-                if (wr) out.put(i, v);
+                if (!WIDE) overflow |= misfit16(v);
+                if (wr) out.template put<WIDE>(i, v);
                 if ((i & 255u) == 255u && br.pos_bits() > len_bits) break;  // ran off the stream
             }
         } else if ((type >= 8 && type <= 12) || type >= 32) {  // FIXED (:466-498) / LPC (:499-541)
@@ -255,8 +276,8 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const Nar
 #pragma unroll 1
             for (uint32_t t = 0; t < order; ++t) {  // warm-up samples (:473-479, :501-507)
                 const int32_t v = br.read_signed(eff);
-                overflow |= misfit16(v);
-                if (wr) out.put(t, v);
+                if (!WIDE) overflow |= misfit16(v);
+                if (wr) out.template put<WIDE>(t, v);
             }
             if (is_lpc) {
                 const uint32_t precision = br.read(4) + 1;  // :508 (0b1111 is not rejected by the reference)
@@ -274,7 +295,7 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const Nar
                     for (int j = 0; j < 4; ++j) sub->coef[j] = (int16_t)fixed_coef(order, j);
                 }
             }
-            status = parse_residual_narrow(br, out, order, bs, len_bits, wr, overflow);
+            status = parse_residual_narrow<Src, WIDE>(br, out, order, bs, len_bits, wr, overflow);
         } else {  // reserved (:542)
             status = ST_INVALID_SUBFRAME_HEADER;
         }

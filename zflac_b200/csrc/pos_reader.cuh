@@ -129,14 +129,16 @@ struct RiceParams {
     uint32_t nmask;  // ~(2^k - 1)
     uint32_t C2;     // 158 << k
     uint32_t fmin;   // smallest float pattern a body accepts: window fit (zeros <= 31 - k) and cw < 65536 guaranteed
-    ZF_HD void set(uint32_t k) {  // k <= 16
+    // k <= 16 for int16 rows; k <= 23 for int32 rows (`wide`: the mantissa of a float holds 23 bits after the stop bit, and
+    // a body is accepted on the window fit alone)
+    ZF_HD void set(uint32_t k, bool wide = false) {
         C = 159u + k;
         sh = 23u - k;
         nmask = ~((1u << k) - 1u);
         C2 = 158u << k;
         // window: zeros <= 31 - k.  16 bits: (zeros + 1) << k <= 65536  <=>  zeros <= (65536 >> k) - 1
         const uint32_t zfit = 31u - k;
-        const uint32_t z16 = (65536u >> k) - 1u;
+        const uint32_t z16 = wide ? zfit : (65536u >> k) - 1u;
         const uint32_t zlim = zfit < z16 ? zfit : z16;
         fmin = (158u - zlim) << 23;
     }

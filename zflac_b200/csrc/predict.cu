@@ -74,9 +74,8 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
     const uint64_t f64 = (uint64_t)warp * G + g;
 
     // ---- the lane's subframe
-    const int32_t *src = scratch;
     const uint8_t *row0 = reinterpret_cast<const uint8_t *>(scratch);  // NARROW: row t at row0 + (t >> row_shift) * row_stride + (t & row_mask) * 16
-    uint32_t row_shift = 0, row_mask = 0, row_stride = 0;
+    uint32_t row_shift = 0, row_mask = 0, row_stride = 0, half_off = 16;
     uint32_t bs = 0, order = 0, shift = 0, wasted = 0, kind = kSubRaw, C = 1, wide_acc = 0, bps = 0, mode = 0;
     int32_t constant = 0;
     uint64_t elem_base = 0, frame_byte_base = 0;
@@ -98,20 +97,21 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             bs = fr.block_size;
             C = fr.channels;
             // sub_idx() layout: 8 values of this channel per group of 8 * C (elements: int32, or uint16 when NARROW)
-            src = scratch + fr.scratch_base + c * 8u;
-            if (NARROW) {  // rows of eight int16, laid out per warp of pass A or per frame (parse_narrow.cuh, flag in SubRec.pad[0])
-                if (((hd.y >> 8) & 0xFFu) == kLayoutWarp) {
-                    const uint64_t base0 = frames[f & ~31u].scratch_base;
-                    row0 = reinterpret_cast<const uint8_t *>(scratch + base0) + ((size_t)c * (hd.y >> 16) * 32u + (f & 31u)) * 16u;
-                    row_shift = 0u;
-                    row_mask = 0u;
-                    row_stride = 512u;
-                } else {
-                    row0 = reinterpret_cast<const uint8_t *>(scratch + fr.scratch_base) + c * 32u;
-                    row_shift = 1u;
-                    row_mask = 1u;
-                    row_stride = 32u * fr.channels;
-                }
+            // rows of eight values, laid out per warp of pass A or per frame (parse_narrow.cuh, flag in SubRec.pad[0]): int16
+            // rows when NARROW, else int32 rows in two 16-byte halves `half_off` apart (the per-frame layout is sub_idx()'s)
+            if (((hd.y >> 8) & 0xFFu) == kLayoutWarp) {
+                const uint64_t base0 = frames[f & ~31u].scratch_base;
+                row_stride = NARROW ? 512u : 1024u;
+                row0 = reinterpret_cast<const uint8_t *>(scratch + base0) + (size_t)c * (hd.y >> 16) * row_stride + (f & 31u) * 16u;
+                row_shift = 0u;
+                row_mask = 0u;
+                half_off = 512u;
+            } else {
+                row0 = reinterpret_cast<const uint8_t *>(scratch + fr.scratch_base) + c * 32u;
+                row_shift = NARROW ? 1u : 0u;
+                row_mask = NARROW ? 1u : 0u;
+                row_stride = 32u * fr.channels;
+                half_off = 16u;
             }
             elem_base = fr.sample_base + c;
             bps = fr.bps;
@@ -176,11 +176,10 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
                                   : any_wide ? (order_max <= 8 ? 3u : 4u) : (order_max <= 4 ? 0u : order_max <= 8 ? 1u : 2u);
 
     const bool loads = bs != 0 && kind != kSubConst;
-    const uint32_t c8 = 8 * C;
     int4 na = make_int4(constant, constant, constant, constant), nb = na;
     if (loads) {
-        na = *reinterpret_cast<const int4 *>(NARROW ? reinterpret_cast<const int32_t *>(row0) : src);
-        if (!NARROW) nb = *reinterpret_cast<const int4 *>(src + 4);
+        na = *reinterpret_cast<const int4 *>(row0);
+        if (!NARROW) nb = *reinterpret_cast<const int4 *>(row0 + half_off);
     }
     const bool folded = NARROW && loads;  // na = eight int16 values (constant subframes keep the value itself)
     uint32_t lossy = 0, buf = 0;
@@ -195,14 +194,10 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             for (int u = 0; u < 8; ++u) r[u] = (u & 1) ? ((int32_t)w[u >> 1] >> 16) : (int32_t)(int16_t)w[u >> 1];
         }
         if (loads && i0 + 8 < bs) {  // next group (whole groups are in bounds: the frame's scratch covers roundup8(bs) steps)
-            if (NARROW) {
-                const uint32_t t = (i0 >> 3) + 1;
-                na = *reinterpret_cast<const int4 *>(row0 + (size_t)(t >> row_shift) * row_stride + (t & row_mask) * 16u);
-            } else {
-                const int32_t *nx = src + (size_t)((i0 >> 3) + 1) * c8;
-                na = *reinterpret_cast<const int4 *>(nx);
-                nb = *reinterpret_cast<const int4 *>(nx + 4);
-            }
+            const uint32_t t = (i0 >> 3) + 1;
+            const uint8_t *nx = row0 + (size_t)(t >> row_shift) * row_stride + (t & row_mask) * 16u;
+            na = *reinterpret_cast<const int4 *>(nx);
+            if (!NARROW) nb = *reinterpret_cast<const int4 *>(nx + half_off);
         }
         int32_t y[8];
         if (i0 < order_max) {  // warm-up steps present (first one or two iterations; four in the LARGE kernel)
