@@ -47,8 +47,11 @@ __device__ __forceinline__ void lpc_chunk(int32_t (&h)[HMAX], const int32_t (&cf
         x[P + u] = r[u] + (WARM ? (i0 + u >= order ? pred : 0) : pred);
         y[u] = x[P + u];
     }
+    if (P > 8 || WARM) {  // a window of <= 8 taps is the last eight samples: the older slots are never read again (the warm-up chunk, which
+                          // reads all of them, only runs while they are still zero)
 #pragma unroll
-    for (int j = 0; j < HMAX - 8; ++j) h[j] = h[j + 8];
+        for (int j = 0; j < HMAX - 8; ++j) h[j] = h[j + 8];
+    }
 #pragma unroll
     for (int u = 0; u < 8; ++u) h[HMAX - 8 + u] = y[u];
 }
@@ -175,6 +178,7 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
     const uint32_t pclass = LARGE ? (any_wide ? 1u : 0u)
                                   : any_wide ? (order_max <= 8 ? 3u : 4u) : (order_max <= 4 ? 0u : order_max <= 8 ? 1u : 2u);
 
+    const bool any_wasted = __any_sync(0xFFFFFFFFu, wasted != 0);
     const bool loads = bs != 0 && kind != kSubConst;
     int4 na = make_int4(constant, constant, constant, constant), nb = na;
     if (loads) {
@@ -222,7 +226,11 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
         // ---- wasted bits, decorrelation, narrowing, MSB-align shift
         int32_t o[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) o[u] = (int32_t)((uint32_t)y[u] << wasted);
+        for (int u = 0; u < 8; ++u) o[u] = y[u];
+        if (LARGE || any_wasted) {  // warp-uniform: streams without wasted bits skip the shifts (the 32-tap kernel is faster without the branch)
+#pragma unroll
+            for (int u = 0; u < 8; ++u) o[u] = (int32_t)((uint32_t)y[u] << wasted);
+        }
         if (stereo) {  // warp-uniform: every lane takes part in the shuffles
             int32_t p[8];
 #pragma unroll
