@@ -148,12 +148,12 @@ struct RiceParams {
 // header) into f[], the position after the eighth into q_out. Returns whether every codeword fitted the window and is
 // known to fit 16 bits; br itself is not moved. Nothing here depends on anything but Q: the caller overlaps the
 // value extraction of the PREVIOUS body with this chain.
-template <class Src>
-ZF_HDI bool rice_chain8(PosReader<Src> &br, const RiceParams &rp, uint32_t (&f)[8], uint32_t &q_out) {
+template <int N, class Src>
+ZF_HDI bool rice_chain(PosReader<Src> &br, const RiceParams &rp, uint32_t (&f)[N], uint32_t &q_out) {
     uint32_t Q = br.Q;
     uint32_t fmin = 0xFFFFFFFFu;
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
+    for (int u = 0; u < N; ++u) {
         const uint2 e = br.src.entry_at(Q);
         const uint32_t win = funnel_r_wrap(e.y, e.x, Q);
         f[u] = float_bits_rz(win);
@@ -168,6 +168,11 @@ ZF_HDI bool rice_chain8(PosReader<Src> &br, const RiceParams &rp, uint32_t (&f)[
     br.src.body_done(ok);
     q_out = Q;
     return ok;
+}
+
+template <class Src>
+ZF_HDI bool rice_chain8(PosReader<Src> &br, const RiceParams &rp, uint32_t (&f)[8], uint32_t &q_out) {
+    return rice_chain<8>(br, rp, f, q_out);
 }
 
 // The residual a float pattern stands for: x = f >> (23 - k) = exponent * 2^k + r, codeword (158 - exponent) * 2^k + r,
