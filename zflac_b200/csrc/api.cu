@@ -1654,11 +1654,32 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     // ---- chunks: >= 8 MiB (a frame is < 2.1 MB: one that starts in chunk i ends inside chunk i + 1), about 24 of them
     uint64_t chunk = std::max<uint64_t>(8ull << 20, (len / (on_device ? dev_chunks : 24) + 0xFFFF) & ~0xFFFFull);
     if (env_chunk >= 4096) chunk = (env_chunk + 15) & ~15ull;  // a frame longer than a chunk only costs the fallback
-    if (audio_offset >= chunk) return kNotPipelined;
-    const uint32_t K = (uint32_t)((len + chunk - 1) / chunk);
-    std::vector<uint64_t> b(K + 1);
-    for (uint32_t i = 0; i <= K; ++i) b[i] = std::min<uint64_t>(len, (uint64_t)i * chunk);
-    b[0] = audio_offset;
+    // The first chunks are smaller (1/8, 1/8, 1/4, 1/2 of a chunk): nothing travels back until the first chunk is uploaded
+    // AND decoded, and a chunk's kernels take ~0.9 ms whatever its size (they are latency-bound) — with full-size chunks the
+    // read-back, the long pole of the call, started 1.3 ms late. No chunk is smaller than the largest frame the format
+    // allows (65535 samples x 8 channels x 33 bits < 2.25 MiB), so "a frame that starts in chunk i ends inside chunk i + 1"
+    // holds whatever STREAMINFO claims. Only for host streams (the device form has no copies to overlap), not under the test knob.
+    static const bool no_ramp = getenv("ZFLACB200_PIPELINE_NO_RAMP") != nullptr;  // diagnostics: A/B runs
+    const uint64_t small = std::max<uint64_t>((chunk / 8 + 0xFFFF) & ~0xFFFFull, 0x240000ull);
+    const bool ramp = !no_ramp && !on_device && env_chunk < 4096 && audio_offset < small && 2 * small <= chunk && len > 4 * chunk;
+    std::vector<uint64_t> b;
+    b.push_back(audio_offset);
+    {
+        uint64_t at = 0;
+        if (ramp) {
+            const uint64_t steps[4] = {small, small, 2 * small, 4 * small};
+            for (uint64_t sz : steps) {
+                at += sz;
+                b.push_back(at);
+            }
+        }
+        while (at < len) {
+            at = std::min<uint64_t>(len, at + chunk);
+            b.push_back(at);
+        }
+    }
+    if (audio_offset >= b[1]) return kNotPipelined;
+    const uint32_t K = (uint32_t)b.size() - 1;
 
     // ---- device buffers for the whole stream
     const uint32_t min_bs = std::max<uint32_t>(si.min_block, 16);
