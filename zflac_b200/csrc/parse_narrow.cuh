@@ -285,8 +285,30 @@ ZF_HDI void parse_frame_narrow(PosReader<Src> &br, const FrameRec &fr, const Nar
         } else if (type == 1) {  // VERBATIM (:455-465)
             if (wasted >= depth) { status = ST_UNDEFINED_IN_REFERENCE; break; }
             const uint32_t n = depth - wasted;
+            uint32_t i = 0;
+            // rows of eight: fixed-width fields have no chain — eight independent windows, one row store (a sample at a
+            // time is ~50 dependent cycles each, and the lanes of a warp that hold Rice-coded subframes wait meanwhile)
 #pragma unroll 1
-            for (uint32_t i = 0; i < bs; ++i) {
+            for (; i + 8u <= bs; i += 8u) {
+                if (Src::kStaleCursor) br.src.top_up_stale(br.entry_index());
+                else br.src.top_up(br.entry_index(), 0u);
+                int32_t r[8];
+                uint32_t bad = 0;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const uint32_t q = br.Q - (uint32_t)u * n;
+                    const uint2 e = br.src.entry_at(q);
+                    r[u] = (int32_t)funnel_r_wrap(e.y, e.x, q) >> (32u - n);
+                    if (!WIDE) bad |= misfit16(r[u]);
+                }
+                br.src.body_done(true);
+                overflow |= bad;
+                if (wr) out.template put8<WIDE>(i, r);
+                br.Q -= 8u * n;
+                if ((i & 255u) == 248u && br.pos_bits() > len_bits) break;  // ran off the stream
+            }
+#pragma unroll 1
+            for (; i < bs; ++i) {
                 const int32_t v = br.read_signed(n);
                 if (!WIDE) overflow |= misfit16(v);
                 if (wr) out.template put<WIDE>(i, v);
