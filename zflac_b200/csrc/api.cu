@@ -1362,6 +1362,56 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
     std::vector<Item> items(n);
     uint64_t blob_len = 0, scan_begin = ~0ull;
     std::vector<uint32_t> keys;  // distinct (channels, wide, container, shift) classes
+
+    // ---- K1 ahead of the metadata walk. The scan needs nothing the walk finds (it starts at the first stream's first byte:
+    // the metadata of every later stream was always scanned, a chance match in there is no frame of any chain), and the
+    // walk of 10 000 streams is a millisecond of host time the GPU used to wait out (r07d). Only when some stream looks
+    // like a fast-path candidate (signature + a stated total), so that a batch of other streams uploads nothing twice.
+    Events ev;
+    DevBuf b_blob, b_cands, b_total, b_tiles, b_ticket;
+    const uint8_t *d_blob = device_blob;
+    uint32_t scan_cap = 0;
+    const void *h_total_early = nullptr;
+    bool early = false;
+    {
+        uint64_t first_off = ~0ull, len_pre = 0;
+        bool maybe_fast = false;
+        for (size_t i = 0; i < n; ++i) {
+            len_pre = std::max(len_pre, offsets[i] + lens[i]);
+            first_off = std::min(first_off, offsets[i]);
+            if (!maybe_fast && lens[i] >= 42) {
+                const uint8_t *p = blob + offsets[i];  // STREAMINFO is the first block: its 36-bit total is at bytes 21..25
+                maybe_fast = p[0] == 0x66 && p[1] == 0x4C && p[2] == 0x61 && p[3] == 0x43 && ((p[21] & 0x0F) | p[22] | p[23] | p[24] | p[25]) != 0;
+            }
+        }
+        early = maybe_fast && n > 0 && (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0;
+        if (early) {
+            if (ev.init() != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+            CU_CHECK(cudaEventRecord(ev.e[0], st));
+            if (!d_blob) {
+                if (b_blob.alloc(((len_pre + 15) & ~15ull) + 64, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+                CU_CHECK(cudaMemcpyAsync(b_blob.p, blob, len_pre, cudaMemcpyHostToDevice, st));
+                d_blob = (const uint8_t *)b_blob.p;
+            }
+            CU_CHECK(cudaEventRecord(ev.e[1], st));
+            scan_begin = first_off;
+            scan_cap = (uint32_t)std::min<uint64_t>(len_pre / 256 + 4096 + 4 * n, 0x7FFFFFFFull);
+            if (b_total.alloc(sizeof(uint32_t), st) || b_ticket.alloc(sizeof(uint32_t), st) ||
+                b_tiles.alloc(sizeof(unsigned long long) * std::max<uint32_t>(scan_tile_count(scan_begin, len_pre), 1), st) ||
+                b_cands.alloc(sizeof(Cand) * (size_t)scan_cap, st))
+                return ZFLACB200_CUDA_ERROR;
+            CU_CHECK(launch_sync_scan(d_blob, scan_begin, len_pre, (Cand *)b_cands.p, scan_cap, (uint32_t *)b_total.p,
+                                      (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
+            h_total_early = get_small(g_ctx[device], b_total.p, sizeof(uint32_t), st);
+            if (!h_total_early) {
+                g_last_error = "small device->host transfer failed (candidate count)";
+                return ZFLACB200_CUDA_ERROR;
+            }
+            CU_CHECK(cudaEventRecord(ev.e[2], st));  // ms_scan stays the scan's time, not the walk's
+            tr.mark("scan_enqueue");
+        }
+    }
+    const uint64_t early_scan_begin = scan_begin;
     for (size_t i = 0; i < n; ++i) {
         memset(&infos[i], 0, sizeof(zflacb200_info));
         blob_len = std::max(blob_len, offsets[i] + lens[i]);
@@ -1413,43 +1463,54 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         }
     } cleanup{b};
 
+    if (early) scan_begin = early_scan_begin;  // what the scan that is already running covers
+    if (early && keys.empty()) CU_CHECK(cudaStreamSynchronize(st));  // nothing will use the scan: let it finish before its buffers go
     if (!keys.empty()) {
-        Events ev;
-        if (ev.init() != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
-        CU_CHECK(cudaEventRecord(ev.e[0], st));
-        DevBuf b_blob;
-        const uint8_t *d_blob = device_blob;
-        if (!d_blob) {
-            if (b_blob.alloc(((blob_len + 15) & ~15ull) + 64, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
-            tr.mark("blob_alloc");
-            CU_CHECK(cudaMemcpyAsync(b_blob.p, blob, blob_len, cudaMemcpyHostToDevice, st));
-            tr.mark("h2d_enqueue");
-            if (tr.on) { cudaStreamSynchronize(st); tr.mark("h2d_wait"); }
-            d_blob = (const uint8_t *)b_blob.p;
+        if (!early) {
+            if (ev.init() != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+            CU_CHECK(cudaEventRecord(ev.e[0], st));
+            if (!d_blob) {
+                if (b_blob.alloc(((blob_len + 15) & ~15ull) + 64, st) != ZFLACB200_OK) return ZFLACB200_CUDA_ERROR;
+                tr.mark("blob_alloc");
+                CU_CHECK(cudaMemcpyAsync(b_blob.p, blob, blob_len, cudaMemcpyHostToDevice, st));
+                tr.mark("h2d_enqueue");
+                if (tr.on) { cudaStreamSynchronize(st); tr.mark("h2d_wait"); }
+                d_blob = (const uint8_t *)b_blob.p;
+            }
+            CU_CHECK(cudaEventRecord(ev.e[1], st));
         }
-        // ---- K1 once over the packed bytes
-        CU_CHECK(cudaEventRecord(ev.e[1], st));
+        // ---- K1 once over the packed bytes (already on its way when `early`)
         uint32_t n_cand = 0;
-        DevBuf b_cands, b_total, b_tiles, b_ticket;
         {
-            const uint32_t n_tiles = scan_tile_count(scan_begin, blob_len);
-            uint32_t cap = (uint32_t)std::min<uint64_t>(blob_len / 256 + 4096 + 4 * n, 0x7FFFFFFFull);
-            if (b_total.alloc(sizeof(uint32_t), st) || b_ticket.alloc(sizeof(uint32_t), st) ||
-                b_tiles.alloc(sizeof(unsigned long long) * std::max<uint32_t>(n_tiles, 1), st))
-                return ZFLACB200_CUDA_ERROR;
+            uint32_t cap = early ? scan_cap : (uint32_t)std::min<uint64_t>(blob_len / 256 + 4096 + 4 * n, 0x7FFFFFFFull);
+            if (!early) {
+                const uint32_t n_tiles = scan_tile_count(scan_begin, blob_len);
+                if (b_total.alloc(sizeof(uint32_t), st) || b_ticket.alloc(sizeof(uint32_t), st) ||
+                    b_tiles.alloc(sizeof(unsigned long long) * std::max<uint32_t>(n_tiles, 1), st))
+                    return ZFLACB200_CUDA_ERROR;
+            }
+            bool rescanned = false;
             for (int attempt = 0; attempt < 2; ++attempt) {
-                if (b_cands.p) { dev_free(b_cands.p, st); b_cands.p = nullptr; }
-                if (b_cands.alloc(sizeof(Cand) * (size_t)cap, st)) return ZFLACB200_CUDA_ERROR;
-                CU_CHECK(launch_sync_scan(d_blob, scan_begin, blob_len, (Cand *)b_cands.p, cap, (uint32_t *)b_total.p,
-                                          (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
-                GET_SMALL(h_total, g_ctx[device], b_total.p, sizeof(uint32_t), st);
+                const void *h_total = h_total_early;
+                if (!(early && attempt == 0)) {
+                    rescanned = true;
+                    if (b_cands.p) { dev_free(b_cands.p, st); b_cands.p = nullptr; }
+                    if (b_cands.alloc(sizeof(Cand) * (size_t)cap, st)) return ZFLACB200_CUDA_ERROR;
+                    CU_CHECK(launch_sync_scan(d_blob, scan_begin, blob_len, (Cand *)b_cands.p, cap, (uint32_t *)b_total.p,
+                                              (unsigned long long *)b_tiles.p, (uint32_t *)b_ticket.p, st));
+                    h_total = get_small(g_ctx[device], b_total.p, sizeof(uint32_t), st);
+                    if (!h_total) {
+                        g_last_error = "small device->host transfer failed (candidate count)";
+                        return ZFLACB200_CUDA_ERROR;
+                    }
+                }
                 CU_CHECK(cudaStreamSynchronize(st));
                 n_cand = *(const uint32_t *)h_total;
                 if (n_cand <= cap) break;
                 cap = n_cand;
             }
+            if (!early || rescanned) CU_CHECK(cudaEventRecord(ev.e[2], st));
         }
-        CU_CHECK(cudaEventRecord(ev.e[2], st));
         tr.mark("h2d+scan");
 
         // ---- one launch group per class
