@@ -194,8 +194,20 @@ def decode_range(data, byte_lo: int, byte_hi: int, dst: np.ndarray | None = None
     info, rng = _native.Info(), _native.Range()
     rng.struct_size = C.sizeof(_native.Range)
     own = dst is None
-    if own:
+    if own:  # the byte range's share of the PCM STREAMINFO promises, plus two maximum blocks; if that is short the call says how much
         dst = np.empty(0, dtype=np.uint8)
+        try:
+            if arr.size >= 42 and bytes(arr[:4]) == b"fLaC" and (int(arr[4]) & 0x7F) == 0:  # STREAMINFO, the first block
+                si = arr[8:42]
+                max_block = (int(si[2]) << 8) | int(si[3])
+                packed = int.from_bytes(bytes(si[10:18]), "big")
+                channels, depth, total = ((packed >> 41) & 7) + 1, ((packed >> 36) & 31) + 1, packed & 0xFFFFFFFFF
+                cb = 1 if depth <= 8 else 2 if depth <= 16 else 4
+                if total and total <= 65535 * (arr.size // 10 + 1):  # a total the bytes could hold
+                    share = min(1.0, max(0, int(byte_hi) - int(byte_lo)) / max(1, arr.size - 42))
+                    dst = np.empty((int(total * share) + 2 * max_block + 16) * channels * cb, dtype=np.uint8)
+        except Exception:  # noqa: BLE001 - no stated total, a broken head: the first call reports the size (or the error)
+            pass
     for attempt in range(2):
         d8 = dst.view(np.uint8).reshape(-1)
         st = lib.zflacb200_decode_range(arr.ctypes.data, arr.size, C.byref(opt), int(byte_lo), int(byte_hi),

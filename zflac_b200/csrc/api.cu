@@ -1454,6 +1454,7 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         bool armed = true;
         ~Cleanup() {
             if (armed) {
+                cudaDeviceSynchronize();  // error path: nothing may still be writing the blocks released below
                 for (auto &it : b->items)
                     if (it.solo) { dev_free(it.solo->d_pcm, nullptr); delete it.solo; }
                 for (auto &g : b->groups)
@@ -1760,6 +1761,18 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
         b_flag.alloc(sizeof(uint32_t), st) || b_hi.alloc(sizeof(unsigned long long) * K, st) || b_jobs.alloc(sizeof(Md5Job), st) ||
         b_digest.alloc(16, st) || stage.prepare(wide, flags, cap, st, depth) != ZFLACB200_OK)
         return ZFLACB200_CUDA_ERROR;
+    // Declared after the buffers, so it runs before they are released: an early return (a CUDA error, a bail-out) must not
+    // hand blocks back to the cache while a lane still decodes into them or a copy still reads them.
+    struct Quiesce {
+        DeviceCtx &ctx;
+        bool armed = true;
+        ~Quiesce() {
+            if (!armed) return;
+            for (auto &l : ctx.lane) cudaStreamSynchronize(l);
+            cudaStreamSynchronize(ctx.copy_in);
+            cudaStreamSynchronize(ctx.copy_out);
+        }
+    } quiesce{ctx};
     StreamDesc sd;
     memset(&sd, 0, sizeof(sd));
     sd.begin = 0;
@@ -1931,6 +1944,7 @@ int decode_pipelined(const uint8_t *data, size_t len, const zflacb200_options *o
     }
     CU_CHECK(cudaStreamSynchronize(ctx.copy_out));
     CU_CHECK(cudaStreamSynchronize(ctx.copy_in));
+    quiesce.armed = false;  // every lane was joined into `st` above and the copies are through
     tr.mark("tail");
     if (!accepted) return kNotPipelined;
     info->ms_total = ev_ms(ev.e[0], ev.e[7]);
@@ -2461,10 +2475,11 @@ int zflacb200_batch_decode(const uint8_t *blob, const uint64_t *offsets, const u
         pcm_offsets[i] = ~0ull;
     }
     // ---- sub-batches: a sub-batch pays the fixed latency of the frame-serial kernels and of the per-file MD5 chain
-    // once (C5: 6.7 ms for an eighth of the batch, 11 ms for all of it), so few and large ones: 4, at least 8 MiB each
+    // once (C5: 3.5 ms for an eighth of the batch, 6.3 ms for all of it), so few and large ones: 8, at least 8 MiB each
+    // (r07e, C5 end to end: 4 parts 46.5 ms, 6 45.0, 8 44.3, 12 48.3, 16 61.6; with the slower kernels of round 1 it was 4)
     static const uint64_t max_parts = [] {
         const char *e = getenv("ZFLACB200_BATCH_PARTS");
-        const uint64_t v = e ? strtoull(e, nullptr, 10) : 4;
+        const uint64_t v = e ? strtoull(e, nullptr, 10) : 8;
         return std::min<uint64_t>(std::max<uint64_t>(v, 1), 64);
     }();
     size_t parts = ordered ? (size_t)std::min<uint64_t>(max_parts, std::max<uint64_t>(1, blob_len / (8ull << 20))) : 1;
