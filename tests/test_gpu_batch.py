@@ -115,3 +115,20 @@ def test_batch_decode_one_call_pipelined(z):
     assert 12 in res.statuses  # ZFLACB200_OUT_OF_MEMORY for the streams that no longer fitted
     ok = [i for i in range(len(streams)) if res.statuses[i] == 0]
     assert ok and all(np.array_equal(res.samples(i), oracle.decode(streams[i]).samples) for i in ok[:4])
+
+
+def test_batch_decode_in_eight_sub_batches(z, monkeypatch):
+    """The one-call batch really cut into sub-batches (ZFLACB200_BATCH_PART_MIN_BYTES lowers the size below which a batch
+    stays whole): 8 parts of ~12 files, every file == the generator's PCM, offsets in blob order, MD5 gate on."""
+    files = fg.generate_batch([fg.c5_file(300 + i) for i in range(96)], want_pcm=True)
+    blob, offs, lens = z.pack_streams([f.flac for f in files])
+    dst = np.zeros(z.batch_pcm_bound(blob, offs, lens) + 4096, dtype=np.uint8)
+    monkeypatch.setenv("ZFLACB200_BATCH_PART_MIN_BYTES", str(1 << 20))
+    res = z.decode_batch_into(blob, offs, lens, dst)
+    monkeypatch.delenv("ZFLACB200_BATCH_PART_MIN_BYTES")
+    whole = z.decode_batch_into(blob, offs, lens, np.zeros_like(dst))
+    assert res.statuses == [0] * len(files) == whole.statuses
+    for i, f in enumerate(files):
+        assert np.array_equal(res.samples(i), f.pcm), i
+        assert res.infos[i]["md5_checked"] == 1 and res.infos[i]["md5_computed"] == f.md5
+        assert np.array_equal(whole.samples(i), f.pcm), i

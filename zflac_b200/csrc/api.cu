@@ -2475,14 +2475,17 @@ int zflacb200_batch_decode(const uint8_t *blob, const uint64_t *offsets, const u
         pcm_offsets[i] = ~0ull;
     }
     // ---- sub-batches: a sub-batch pays the fixed latency of the frame-serial kernels and of the per-file MD5 chain
-    // once (C5: 3.5 ms for an eighth of the batch, 6.3 ms for all of it), so few and large ones: 8, at least 8 MiB each
+    // once (C5: 3.5 ms for an eighth of the batch, 6.3 ms for all of it), so few and large ones: at most 8
     // (r07e, C5 end to end: 4 parts 46.5 ms, 6 45.0, 8 44.3, 12 48.3, 16 61.6; with the slower kernels of round 1 it was 4)
     static const uint64_t max_parts = [] {
         const char *e = getenv("ZFLACB200_BATCH_PARTS");
         const uint64_t v = e ? strtoull(e, nullptr, 10) : 8;
         return std::min<uint64_t>(std::max<uint64_t>(v, 1), 64);
     }();
-    size_t parts = ordered ? (size_t)std::min<uint64_t>(max_parts, std::max<uint64_t>(1, blob_len / (8ull << 20))) : 1;
+    // ... and no part below ~96 MiB of stream: a rank's eighth of C5 (150 MB) in 8 parts was 8 x 3.5 ms of fixed latency (r08 N = 8)
+    uint64_t part_min = 96ull << 20;
+    if (const char *e = getenv("ZFLACB200_BATCH_PART_MIN_BYTES")) part_min = std::max<uint64_t>(strtoull(e, nullptr, 0), 4096);  // test knob, read per call
+    size_t parts = ordered ? (size_t)std::min<uint64_t>(max_parts, std::max<uint64_t>(1, blob_len / part_min)) : 1;
     if (parts > n) parts = n ? n : 1;
     std::vector<size_t> first(parts + 1, n);
     first[0] = 0;
