@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <thread>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -1412,15 +1413,16 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         }
     }
     const uint64_t early_scan_begin = scan_begin;
-    for (size_t i = 0; i < n; ++i) {
+    // The walk of one stream touches nothing but that stream's slots, so a large batch is walked by a few host threads
+    // (10 000 streams: ~1.0 ms on one core); what orders the streams — the class list and the scan start — follows serially.
+    auto walk = [&](size_t i) {
         memset(&infos[i], 0, sizeof(zflacb200_info));
-        blob_len = std::max(blob_len, offsets[i] + lens[i]);
         Item &it = items[i];
         ByteSource src;
         src.host = blob + offsets[i];
         src.len = lens[i];
         statuses[i] = parse_metadata(src, it.si, it.audio_offset);
-        if (statuses[i] != ZFLACB200_OK) continue;
+        if (statuses[i] != ZFLACB200_OK) return;
         it.depth = it.si.depth_m1 + 1;
         it.aligned = (it.depth + 7u) & ~7u;
         it.container = it.aligned == 8 ? 1 : it.aligned == 16 ? 2 : 4;
@@ -1435,14 +1437,30 @@ int batch_open_impl(const uint8_t *blob, const uint8_t *device_blob, const uint6
         it.eligible = it.si.total > 0 && it.si.total * (it.si.channels_m1 + 1) < (1ull << 40) &&
                       plausible_total(it.si.total, lens[i] - std::min<uint64_t>(lens[i], it.audio_offset)) &&
                       (flags & (ZFLACB200_NO_FAST_PATH | ZFLACB200_NO_CRC_ACCEL)) == 0;
-        if (it.eligible) {
-            const uint32_t key = ((uint32_t)it.si.channels_m1 << 20) | (it.wide ? 1u << 16 : 0u) | (it.container << 8) | it.msb_shift;
-            size_t g = 0;
-            while (g < keys.size() && keys[g] != key) ++g;
-            if (g == keys.size()) keys.push_back(key);
-            it.group = (int)g;
-            scan_begin = std::min(scan_begin, offsets[i] + it.audio_offset);
+    };
+    {
+        const unsigned hw = std::thread::hardware_concurrency();
+        const size_t n_threads = n >= 4096 ? std::min<size_t>(4, hw > 1 ? hw : 1) : 1;
+        if (n_threads <= 1) {
+            for (size_t i = 0; i < n; ++i) walk(i);
+        } else {
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < n_threads; ++t)
+                pool.emplace_back([&, t] { for (size_t i = n * t / n_threads; i < n * (t + 1) / n_threads; ++i) walk(i); });
+            for (size_t i = 0; i < n / n_threads; ++i) walk(i);
+            for (auto &th : pool) th.join();
         }
+    }
+    for (size_t i = 0; i < n; ++i) {
+        blob_len = std::max(blob_len, offsets[i] + lens[i]);
+        Item &it = items[i];
+        if (statuses[i] != ZFLACB200_OK || !it.eligible) continue;
+        const uint32_t key = ((uint32_t)it.si.channels_m1 << 20) | (it.wide ? 1u << 16 : 0u) | (it.container << 8) | it.msb_shift;
+        size_t g = 0;
+        while (g < keys.size() && keys[g] != key) ++g;
+        if (g == keys.size()) keys.push_back(key);
+        it.group = (int)g;
+        scan_begin = std::min(scan_begin, offsets[i] + it.audio_offset);
     }
 
     tr.mark("metadata");
