@@ -189,6 +189,11 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
     uint32_t lossy = 0, buf = 0;
     uint8_t *const slot0 = tile + g * (chunk_bytes + 16) + c * CB;
     const uint32_t rs = C * CB;
+    // The loop exists once per predictor class (the class is warp-uniform and fixed for the launch's warp): with one loop
+    // and a dispatch inside it, the register window had one layout for all classes and every iteration paid the branches
+    // and ~20 moves to and from it (r06l).
+    auto run = [&](auto pc_tag) {
+    constexpr uint32_t PC = decltype(pc_tag)::value;
 #pragma unroll 1
     for (uint32_t i0 = 0; i0 < bs_max; i0 += 8) {
         int32_t r[8] = {na.x, na.y, na.z, na.w, nb.x, nb.y, nb.z, nb.w};
@@ -206,20 +211,20 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
         int32_t y[8];
         if (i0 < order_max) {  // warm-up steps present (first one or two iterations; four in the LARGE kernel)
             if (LARGE) {
-                if (pclass == 0) lpc_chunk<HMAX, 32, int32_t, true>(h, cf, r, shift, order, i0, y);
+                if (PC == 0) lpc_chunk<HMAX, 32, int32_t, true>(h, cf, r, shift, order, i0, y);
                 else lpc_chunk<HMAX, 32, int64_t, true>(h, cf, r, shift, order, i0, y);
             } else {
-                if (pclass <= 2) lpc_chunk<HMAX, 12, int32_t, true>(h, cf, r, shift, order, i0, y);
+                if (PC <= 2) lpc_chunk<HMAX, 12, int32_t, true>(h, cf, r, shift, order, i0, y);
                 else lpc_chunk<HMAX, 12, int64_t, true>(h, cf, r, shift, order, i0, y);
             }
         } else if (LARGE) {
-            if (pclass == 0) lpc_chunk<HMAX, 32, int32_t, false>(h, cf, r, shift, order, i0, y);
+            if (PC == 0) lpc_chunk<HMAX, 32, int32_t, false>(h, cf, r, shift, order, i0, y);
             else lpc_chunk<HMAX, 32, int64_t, false>(h, cf, r, shift, order, i0, y);
         } else {
-            if (pclass == 0) lpc_chunk<HMAX, 4, int32_t, false>(h, cf, r, shift, order, i0, y);
-            else if (pclass == 1) lpc_chunk<HMAX, 8, int32_t, false>(h, cf, r, shift, order, i0, y);
-            else if (pclass == 2) lpc_chunk<HMAX, 12, int32_t, false>(h, cf, r, shift, order, i0, y);
-            else if (pclass == 3) lpc_chunk<HMAX, 8, int64_t, false>(h, cf, r, shift, order, i0, y);
+            if (PC == 0) lpc_chunk<HMAX, 4, int32_t, false>(h, cf, r, shift, order, i0, y);
+            else if (PC == 1) lpc_chunk<HMAX, 8, int32_t, false>(h, cf, r, shift, order, i0, y);
+            else if (PC == 2) lpc_chunk<HMAX, 12, int32_t, false>(h, cf, r, shift, order, i0, y);
+            else if (PC == 3) lpc_chunk<HMAX, 8, int64_t, false>(h, cf, r, shift, order, i0, y);
             else lpc_chunk<HMAX, 12, int64_t, false>(h, cf, r, shift, order, i0, y);
         }
 
@@ -289,6 +294,17 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             rd_ptr[1] += chunk_bytes;
         }
         buf ^= 1u;  // the next iteration's stores go to the other half: one __syncwarp per iteration is enough
+    }
+    };
+    if (LARGE) {
+        if (pclass == 0) run(std::integral_constant<uint32_t, 0>{});
+        else run(std::integral_constant<uint32_t, 1>{});
+    } else {
+        if (pclass == 0) run(std::integral_constant<uint32_t, 0>{});
+        else if (pclass == 1) run(std::integral_constant<uint32_t, 1>{});
+        else if (pclass == 2) run(std::integral_constant<uint32_t, 2>{});
+        else if (pclass == 3) run(std::integral_constant<uint32_t, 3>{});
+        else run(std::integral_constant<uint32_t, 4>{});
     }
     if (lossy) atomicOr(lossy_flag, 1u);
 }
