@@ -93,10 +93,10 @@ static long long *g_rollbacks = nullptr;
 
 extern "C" {
 
-// Decodes one frame on the host. scratch: int32 (wide == 0) or int64 planes. Returns the number of
-// unchecked-read violations (must be 0).
+// Decodes one frame on the host. scratch: int32 (wide == 0) or int64 planes; inter64: the stream's container is wider than
+// 16 bits (decode_core.cuh, "Arithmetic"). Returns the number of unchecked-read violations (must be 0).
 int zf_host_decode_frame(const uint8_t *stream, const zf::FrameRec *fr, void *scratch, int wide, int write_samples,
-                         zf::FrameOut *out) {
+                         zf::FrameOut *out, int inter64) {
     const uint64_t start = fr->offset + fr->header_len;
     const uint64_t origin = start & ~3ull;
     const uint64_t bytes = fr->stream_end > origin ? fr->stream_end - origin : 0;
@@ -109,7 +109,7 @@ int zf_host_decode_frame(const uint8_t *stream, const zf::FrameRec *fr, void *sc
     br.src.rollbacks = 0;
     br.init((uint32_t)(start & 3));
     if (wide) zf::decode_frame<int64_t>(br, *fr, (int64_t *)scratch, bytes * 8, write_samples != 0, origin, *out);
-    else zf::decode_frame<int32_t>(br, *fr, (int32_t *)scratch, bytes * 8, write_samples != 0, origin, *out);
+    else zf::decode_frame<int32_t>(br, *fr, (int32_t *)scratch, bytes * 8, write_samples != 0, origin, *out, inter64 != 0);
     if (g_rollbacks) *g_rollbacks += br.src.rollbacks;
     return br.src.violations;
 }

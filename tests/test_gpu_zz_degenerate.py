@@ -95,3 +95,22 @@ def test_overstated_total_in_a_batch(z):
             assert isinstance(r, (z.EndOfStream, z.OutOfMemory)), r
         else:
             assert np.array_equal(r.samples, f.pcm)
+
+
+def test_samples_wider_than_the_frame_depth(z):
+    """A malformed but defined 24-bit stream: samples of 30 bits, so that the LPC sum leaves int32 where the frame's depth
+    says it cannot (bitcraft.wide_sample_stream). The reference sums in i64 in a 32-bit container (src/zflac.zig:314-319);
+    pass B and the single-pass decoder must too — every path against the oracle, alone and in a batch."""
+    from oracle import oracle
+    from bitcraft import wide_sample_stream
+    data = wide_sample_stream()
+    ref = oracle.decode(data)
+    assert ref.error == "OK" and ref.container_bytes == 4
+    assert _same_as_oracle(z, data) == "OK"
+    for kw in (dict(use_fast_path=False), dict(verify_md5=False), dict(word_pipeline=True), dict(md5_on_device=True),
+               dict(single_pass=True), dict(single_pass=True, use_fast_path=False)):
+        got = z.decode(data, **kw)
+        assert np.array_equal(got.samples, ref.samples), kw
+    from test_gpu_batch import check_against_oracle
+    cases = [data, make("c5_file_0").flac, data]
+    check_against_oracle(z, cases, z.decode_batch(cases))

@@ -39,7 +39,7 @@ def core():
         subprocess.run([nvcc, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC",
                         "--expt-relaxed-constexpr", "-o", LIB, SRC], check=True, capture_output=True)
     lib = C.CDLL(LIB)
-    lib.zf_host_decode_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.zf_host_decode_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
     lib.zf_host_decode_frame.restype = C.c_int
     assert lib.zf_host_framerec_size() == FRAME_REC.itemsize
     lib.zf_host_parse_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -129,7 +129,7 @@ def host_decode(lib, data: bytes, ref, two_pass: bool = False, narrow: bool = Fa
                     lib.zf_host_predict_plane(subs.ctypes.data + 80 * c, scratch.ctypes.data, c, ch, bs, planar.ctypes.data + 4 * pitch * c)
                 scratch = planar
         else:
-            viol = lib.zf_host_decode_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, int(wide), 1, out.ctypes.data)
+            viol = lib.zf_host_decode_frame(arr.ctypes.data, rec.ctypes.data, scratch.ctypes.data, int(wide), 1, out.ctypes.data, int(cb == 4))
         assert viol == 0, "unchecked word read beyond the top_up guarantee"
         assert int(out["status"][0]) == 0, (int(fr["offset"]), int(out["status"][0]))
         assert int(out["end_offset"][0]) == int(fr["end_offset"]), int(fr["offset"])
@@ -258,3 +258,15 @@ def test_host_parse_pos_wide_synth(core, name):
         pytest.skip("32 bps streams stay on the single-pass int64 decoder")
     got = host_decode(core, data, ref, two_pass=True, pos_wide=True)
     assert np.array_equal(got, ref.samples)
+
+
+def test_host_core_samples_wider_than_the_frame_depth(core):
+    """decode_core.cuh's `inter64` and the scalar pass B against the oracle's i64 sums (bitcraft.wide_sample_stream)."""
+    from bitcraft import wide_sample_stream
+    data = wide_sample_stream()
+    ref = oracle.decode(data, trace_frames=True)
+    assert ref.error == "OK" and len(ref.frames) == 40
+    s1 = (1 << 29) + 12345 + ((127 * 100) >> 15)
+    assert int(ref.samples[2]) == (((7 + ((127 * s1) >> 15)) << 8) & 0xFFFFFFFF)  # the i64 sum, MSB-aligned (:287-306)
+    for two_pass in (False, True):
+        assert np.array_equal(host_decode(core, data.tobytes(), ref, two_pass=two_pass), ref.samples)

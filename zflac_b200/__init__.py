@@ -98,15 +98,18 @@ FORMATS = {"native": 0, "f32": 1, "s24": 2, "u8": 3}  # zflacb200_format
 
 
 def decode(data, *, device: int = -1, verify_md5: bool = True, use_crc_links: bool = True,
-           use_fast_path: bool = True, md5_on_device: bool = False, word_pipeline: bool = False) -> DecodedFLAC:
+           use_fast_path: bool = True, md5_on_device: bool = False, word_pipeline: bool = False,
+           single_pass: bool = False) -> DecodedFLAC:
     """Drop-in for `zflac.decode(allocator, reader)`: `data` is bytes / ndarray / a readable object
     holding the whole stream. Raises the ZflacError subclass named like the Zig error.
-    word_pipeline (diagnostics, ZFLACB200_WORD_PIPELINE): pass A of 17..31-bit streams by the first bit reader."""
+    word_pipeline (diagnostics, ZFLACB200_WORD_PIPELINE): pass A of 17..31-bit streams by the first bit reader.
+    single_pass (diagnostics, ZFLACB200_SINGLE_PASS): the fused subframe decoder instead of parse + predict."""
     lib = _native.load()
     arr = _as_u8(data)
     flags = (0 if verify_md5 else SKIP_MD5) | (0 if use_crc_links else NO_CRC_ACCEL) | (0 if use_fast_path else NO_FAST_PATH)
     flags |= MD5_ON_DEVICE if md5_on_device else 0
     flags |= _native.WORD_PIPELINE if word_pipeline else 0
+    flags |= _native.SINGLE_PASS if single_pass else 0
     opt = _options(flags, device)
     handle = C.c_void_p()
     info = _native.Info()

@@ -18,6 +18,7 @@ NO_FAST_PATH = 0x10
 MD5_ON_DEVICE = 0x100
 RANGE_INTO_WHOLE = 0x200
 WORD_PIPELINE = 0x400
+SINGLE_PASS = 0x20
 
 EXPORTS = [
     "zflacb200_abi_version", "zflacb200_init", "zflacb200_device_count", "zflacb200_shutdown", "zflacb200_trim", "zflacb200_scan_no_alloc",

@@ -466,7 +466,7 @@ struct Pipeline {
 
     int probe(const FrameRec &rec, FrameOut &out) {
         CU_CHECK(cudaMemcpyAsync(d_probe_rec, &rec, sizeof(rec), cudaMemcpyHostToDevice, st));
-        CU_CHECK(launch_decode_frames(d_stream, d_probe_rec, 1, nullptr, wide, d_probe_out, false, st));
+        CU_CHECK(launch_decode_frames(d_stream, d_probe_rec, 1, nullptr, wide, d_probe_out, false, false, st));
         CU_CHECK(cudaMemcpyAsync(&out, d_probe_out, sizeof(out), cudaMemcpyDeviceToHost, st));
         CU_CHECK(cudaStreamSynchronize(st));
         return ZFLACB200_OK;
@@ -673,12 +673,14 @@ struct SubframeStage {
     bool two_pass = false;
     bool narrow = false;  // uint16 scratch of folded residuals (parse_narrow.cuh): streams of <= 16 bits per sample
     bool word_pipeline = false;  // diagnostics (ZFLACB200_WORD_PIPELINE): int32 rows by the first pass A (parse_core.cuh) instead of the position reader
+    bool inter64 = false;  // container wider than 16 bits: the reference's sums are i64 (decode_core.cuh, "Arithmetic")
     DevBuf b_subs, b_big;  // b_big: {some order above 12, a value did not fit the narrow scratch}
     // depth: bits per sample by STREAMINFO (largest of a batch group); 0 or allow_narrow = false keeps the int32 scratch
     int prepare(bool wide, uint32_t flags, uint32_t n_recs, cudaStream_t st, uint32_t depth = 0, bool allow_narrow = true) {
         two_pass = !wide && (flags & ZFLACB200_SINGLE_PASS) == 0;
         narrow = false;
         word_pipeline = (flags & ZFLACB200_WORD_PIPELINE) != 0;
+        inter64 = depth > 16;
         if (!two_pass) return ZFLACB200_OK;
         static const bool env_no_narrow = getenv("ZFLACB200_NO_NARROW") != nullptr;  // diagnostics: A/B runs
         narrow = allow_narrow && !env_no_narrow && depth >= 1 && depth <= 16;
@@ -700,7 +702,7 @@ struct SubframeStage {
                                          (SubRec *)((uint8_t *)b_subs.p + kSubRecBytes * 8 * (size_t)first), d_outs, (uint32_t *)b_big.p,
                                          write, st, word_pipeline));
         else
-            CU_CHECK(launch_decode_frames(d_stream, d_recs, n, d_scratch, wide, d_outs, write, st));
+            CU_CHECK(launch_decode_frames(d_stream, d_recs, n, d_scratch, wide, d_outs, write, inter64, st));
         return ZFLACB200_OK;
     }
     int epilogue(const EpilogueParams &ep, const FrameOut *d_outs, uint32_t max_channels, cudaStream_t st, uint32_t first = 0) {

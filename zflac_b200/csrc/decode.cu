@@ -24,7 +24,7 @@ namespace zf {
 template <typename ST>
 __global__ void __launch_bounds__(kDecodeThreads)
 k_decode_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ frames, uint32_t n_frames,
-                ST *__restrict__ scratch, FrameOut *__restrict__ outs, int write_samples) {
+                ST *__restrict__ scratch, FrameOut *__restrict__ outs, int write_samples, int inter64) {
     const uint32_t f = blockIdx.x * kDecodeThreads + threadIdx.x;
     if (f >= n_frames) return;
     const FrameRec fr = frames[f];
@@ -36,22 +36,22 @@ k_decode_frames(const uint8_t *__restrict__ s, const FrameRec *__restrict__ fram
     br.init((uint32_t)(start & 3));
     const uint64_t len_bits = (fr.stream_end > origin ? fr.stream_end - origin : 0) * 8;
     FrameOut o;
-    decode_frame<ST>(br, fr, scratch, len_bits, write_samples != 0, origin, o);
+    decode_frame<ST>(br, fr, scratch, len_bits, write_samples != 0, origin, o, inter64 != 0);
     asm volatile("cp.async.wait_group 0;" ::: "memory");  // nothing may land in the ring after the CTA retires
     outs[f] = o;
 }
 
 cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, void *d_scratch,
-                                 bool wide_scratch, FrameOut *d_outs, bool write_samples, cudaStream_t st) {
+                                 bool wide_scratch, FrameOut *d_outs, bool write_samples, bool inter64, cudaStream_t st) {
     if (n_frames == 0) return cudaSuccess;
     const uint32_t blocks = (n_frames + kDecodeThreads - 1) / kDecodeThreads;
     ZF_COUNT_LAUNCH();
     if (wide_scratch)
         k_decode_frames<int64_t><<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(d_stream, d_frames, n_frames, (int64_t *)d_scratch, d_outs,
-                                                                    write_samples ? 1 : 0);
+                                                                    write_samples ? 1 : 0, inter64 ? 1 : 0);
     else
         k_decode_frames<int32_t><<<blocks, kDecodeThreads, kRingWords * kDecodeThreads * sizeof(uint32_t), st>>>(d_stream, d_frames, n_frames, (int32_t *)d_scratch, d_outs,
-                                                                    write_samples ? 1 : 0);
+                                                                    write_samples ? 1 : 0, inter64 ? 1 : 0);
     return cudaGetLastError();
 }
 

@@ -23,7 +23,9 @@
 //
 // Arithmetic: the reference accumulates in i16/i32/i64 depending on the container (Q10). Here a
 // subframe runs in int32 when depth + precision + ceil(log2(order)) <= 32 proves the sum cannot
-// overflow, else in int64 — both are exact wherever the reference is defined.
+// overflow for samples of `depth` bits, else in int64; in a 32-bit container (`inter64`: the reference's
+// i64) every shifted sum runs in int64, because a malformed stream may carry samples wider than `depth`
+// there without leaving the reference's defined range — exact wherever the reference is defined.
 #pragma once
 #include "common.cuh"
 
@@ -399,7 +401,7 @@ ZF_HDI uint32_t predicted_subframe(BitReader<Src> &br, int32_t *__restrict__ out
 template <class Src>
 ZF_HDI uint32_t decode_predicted32(BitReader<Src> &br, int32_t *__restrict__ out, uint32_t order, bool is_lpc,
                                    uint32_t depth, uint32_t eff_bits, uint32_t block_size, uint32_t wasted,
-                                   uint64_t len_bits, bool wr) {
+                                   uint64_t len_bits, bool wr, bool inter64) {
     int32_t warm[32];
 #pragma unroll 1
     for (uint32_t t = 0; t < order; ++t) {
@@ -414,7 +416,11 @@ ZF_HDI uint32_t decode_predicted32(BitReader<Src> &br, int32_t *__restrict__ out
     }
     const uint32_t precision = br.read(4) + 1;  // :508 (0b1111 is not rejected by the reference)
     const uint32_t shift = br.read(5);          // :510 unsigned (Q17)
-    const bool wide = depth + precision + ceil_log2(order) > 32;
+    // int32 sums are the reference's own arithmetic in a 16-bit container (InterType i32, :314-319) and cannot overflow
+    // while the samples keep to `depth` bits. In a 32-bit container the reference sums in i64 and stays defined when a
+    // malformed stream drives samples past `depth` bits (still inside i32): there a shifted sum is always taken in int64
+    // (without a shift the low 32 bits are all that is kept, and those are exact either way).
+    const bool wide = depth + precision + ceil_log2(order) > 32 || (inter64 && shift != 0);
 #define ZF_RUN(PP)                                                                                                                  \
     return wide ? predicted_subframe<PP, int64_t>(br, out, warm, order, true, precision, shift, block_size, wasted, len_bits, wr) \
                 : predicted_subframe<PP, int32_t>(br, out, warm, order, true, precision, shift, block_size, wasted, len_bits, wr)
@@ -478,10 +484,11 @@ template <> struct IsWide<int64_t> { static constexpr bool value = true; };
 
 // One whole frame: subframes in channel order, then align + CRC-16 (:425-551). `br` is positioned
 // on the first subframe header. ST = int32_t: frames with <= 31 bits per sample (subframe depth
-// <= 32); ST = int64_t: 32 bps streams. len_bits is relative to the source origin.
+// <= 32); ST = int64_t: 32 bps streams. len_bits is relative to the source origin. inter64: the stream's
+// container is wider than 16 bits (see "Arithmetic" above).
 template <typename ST, class Src>
 ZF_HDI void decode_frame(BitReader<Src> &br, const FrameRec &fr, ST *__restrict__ scratch, uint64_t len_bits, bool wr,
-                         uint64_t origin_byte, FrameOut &o) {
+                         uint64_t origin_byte, FrameOut &o, bool inter64 = false) {
     uint32_t status = ST_OK;
     const uint32_t bs = fr.block_size;
     const uint32_t bps = fr.bps;
@@ -531,7 +538,7 @@ ZF_HDI void decode_frame(BitReader<Src> &br, const FrameRec &fr, ST *__restrict_
             if (IsWide<ST>::value)
                 status = decode_predicted64(br, (int64_t *)out, order, is_lpc, eff, bs, wasted, len_bits, wr);
             else
-                status = decode_predicted32(br, (int32_t *)out, order, is_lpc, eff, eff, bs, wasted, len_bits, wr);
+                status = decode_predicted32(br, (int32_t *)out, order, is_lpc, eff, eff, bs, wasted, len_bits, wr, inter64);
         } else {  // reserved (:542)
             status = ST_INVALID_SUBFRAME_HEADER;
         }

@@ -54,7 +54,7 @@ cudaError_t launch_verify_chain(const Cand *d_cands, uint32_t n, const StreamDes
 
 // decode.cu
 cudaError_t launch_decode_frames(const uint8_t *d_stream, const FrameRec *d_frames, uint32_t n_frames, void *d_scratch,
-                                 bool wide_scratch, FrameOut *d_outs, bool write_samples, cudaStream_t st);
+                                 bool wide_scratch, FrameOut *d_outs, bool write_samples, bool inter64, cudaStream_t st);
 
 // parse.cu + predict.cu: the two-pass decoder for streams with <= 31 bits per sample
 struct SubRec;  // parse_core.cuh

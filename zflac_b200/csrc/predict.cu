@@ -94,6 +94,10 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
             shift = (hd.x >> 16) & 0xFFu;
             wasted = (hd.x >> 24) & 0xFFu;
             wide_acc = hd.y & 0xFFu;
+            // a 32-bit container: the reference sums in i64 (src/zflac.zig:314-319) and stays defined when a malformed stream
+            // carries samples wider than the frame's depth, which pass A's rule (depth + precision + log2(order) <= 32)
+            // assumes they are not; without a shift the low 32 bits of the sum are exact either way
+            if (CB == 4 && kind == kSubPred && shift != 0) wide_acc = 1;
             constant = (int32_t)hd.z;
             if (order > 32) order = 32;
             if (kind != kSubPred) order = 0;
