@@ -114,3 +114,27 @@ def test_samples_wider_than_the_frame_depth(z):
     from test_gpu_batch import check_against_oracle
     cases = [data, make("c5_file_0").flac, data]
     check_against_oracle(z, cases, z.decode_batch(cases))
+
+
+def test_random_streams(z):
+    """tests/bitcraft.py's random encoder (any legal field combination, PCM known by construction): every stream the
+    reference is defined on — one batch (mixed depths and channel counts: several launch groups), then each path alone on
+    a sample of them. Where a quirk of the reference changes the PCM (fuzz_case: not exact) the gate must say
+    InvalidChecksum, and without the gate the samples are the oracle's."""
+    from bitcraft import fuzz_case
+    from test_gpu_batch import check_against_oracle
+    cases = [c for c in (fuzz_case(seed) for seed in range(1000, 1400)) if c is not None]
+    assert len(cases) >= 250
+    streams = [c[0] for c in cases]
+    check_against_oracle(z, streams, z.decode_batch(streams))
+    paths = [dict(), dict(use_fast_path=False), dict(word_pipeline=True), dict(single_pass=True), dict(md5_on_device=True)]
+    for k, (data, ref, exact) in enumerate(cases[:150]):
+        kw = dict(paths[k % 5])
+        if not exact:
+            with pytest.raises(z.ZflacError) as ei:
+                z.decode(data, **kw)
+            assert type(ei.value).__name__ == "InvalidChecksum"
+            kw["verify_md5"] = False
+        got = z.decode(data, **kw)
+        assert got.samples.dtype == ref.samples.dtype and np.array_equal(got.samples, ref.samples), (k, kw)
+        assert (got.channels, got.sample_rate, got.bits_per_sample) == (ref.channels, ref.sample_rate, ref.bits_per_sample)

@@ -70,6 +70,10 @@ __device__ __forceinline__ void epilogue_frame(const FrameRec &fr, const ST *__r
         uint32_t ignored = 0;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
+            // the subframe's value went into the container type and took its wasted-bits shift THERE (:494, :537; `<<=` drops
+            // what leaves the type): the decorrelation reads it back from the container
+#pragma unroll
+            for (int c = 0; c < C; ++c) v[c][k] = (int64_t)(CT)(UT)(uint64_t)v[c][k];
             if (C == 2) decorrelate(fr.ch_code, v[0][k], v[C - 1][k]);
 #pragma unroll
             for (int c = 0; c < C; ++c) o[k * C + c] = narrow_shift<CT>(v[c][k], shift, t + k < bs ? lossy : ignored);  // plane padding is garbage

@@ -81,6 +81,7 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
     uint32_t row_shift = 0, row_mask = 0, row_stride = 0, half_off = 16;
     uint32_t bs = 0, order = 0, shift = 0, wasted = 0, kind = kSubRaw, C = 1, wide_acc = 0, bps = 0, mode = 0;
     int32_t constant = 0;
+    uint32_t pair_code = 1;  // channel assignment of a two-channel frame (1: independent)
     uint64_t elem_base = 0, frame_byte_base = 0;
     const SubRec *sub = nullptr;
     if (f64 < n_frames) {
@@ -128,6 +129,7 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
                 else if (fr.ch_code == 10) mode = c == 0 ? 3 : 4;
             }
             frame_byte_base = fr.sample_base * CB;
+            if (fr.channels == 2) pair_code = fr.ch_code;
         }
     }
     // ---- warp-uniform shape
@@ -171,6 +173,22 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
         }
     }
     const bool two_pieces = n_pieces > 32;
+
+    // ---- 16-bit two-channel frames (CB == 2, every frame of the warp, PCM 16-byte aligned): no shared memory at all. The
+    // two lanes of a frame trade HALF a group — the even lane takes time steps 0..3 of both channels, the odd lane 4..7 —
+    // and each one undoes the channel assignment for its four steps as (left, right) pairs, which are then exactly the
+    // 16 bytes it stores: four shuffles, four packs and one store instead of eight shuffles, eight 16-bit shared stores,
+    // a warp barrier and a shared load (r12: 122 -> ~50 of the loop's ~265 instructions).
+    //   left = (al * a + bl * b + (b & pm)) >> dsh, right = (ar * a + br * b + (b & pm)) >> dsh, a / b = channel 0 / 1 (:553-578)
+    const bool odd = (lane & 1u) != 0;
+    const bool pair16 = CB == 2 && cp_shift == 1 && uniform_c && c_max == 2 &&
+                        __all_sync(0xFFFFFFFFu, bs == 0 || ((reinterpret_cast<uintptr_t>(pcm) + frame_byte_base) & 15u) == 0);
+    const int32_t al = pair_code == 10 ? 2 : 1, bl = pair_code == 9 || pair_code == 10 ? 1 : 0;
+    const int32_t ar = pair_code == 10 ? 2 : pair_code == 8 ? 1 : 0, br = pair_code == 8 || pair_code == 10 ? -1 : 1;
+    const int32_t kxl = odd ? bl : al, kyl = odd ? al : bl, kxr = odd ? br : ar, kyr = odd ? ar : br;  // x: own value, y: the partner's
+    const int32_t pm = pair_code == 10 ? 1 : 0;
+    const uint32_t psh = pair_code == 10 ? 1u : 0u;
+    uint8_t *const pair_ptr = pcm + frame_byte_base + (odd ? 16u : 0u);
 
     // ---- coefficients and history
     int32_t cf[HMAX], h[HMAX];
@@ -238,7 +256,36 @@ k_predict_epilogue(const FrameRec *__restrict__ frames, const FrameOut *__restri
         for (int u = 0; u < 8; ++u) o[u] = y[u];
         if (LARGE || any_wasted) {  // warp-uniform: streams without wasted bits skip the shifts (the 32-tap kernel is faster without the branch)
 #pragma unroll
-            for (int u = 0; u < 8; ++u) o[u] = (int32_t)((uint32_t)y[u] << wasted);
+            for (int u = 0; u < 8; ++u) o[u] = narrow<CB>((int32_t)((uint32_t)y[u] << wasted));  // `<<=` on the container type (:494, :537): wraps
+        }
+        if (CB == 2 && pair16) {
+            const bool whole = i0 + 8 <= bs;  // the same for both lanes of a frame
+            if (__all_sync(0xFFFFFFFFu, whole || i0 >= bs)) {  // no frame of the warp is in its last, partial group
+                int32_t x[4], snd[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    x[j] = odd ? o[j + 4] : o[j];
+                    snd[j] = odd ? o[j] : o[j + 4];
+                }
+                uint32_t w[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int32_t yv = __shfl_xor_sync(0xFFFFFFFFu, snd[j], 1);
+                    const int32_t lsb = (odd ? x[j] : yv) & pm;
+                    int32_t left = (kxl * x[j] + kyl * yv + lsb) >> psh;
+                    int32_t right = (kxr * x[j] + kyr * yv + lsb) >> psh;
+                    if (msb_shift != 0) {
+                        const int32_t cl = narrow<CB>(left), cr = narrow<CB>(right);
+                        left = narrow<CB>((int32_t)((uint32_t)cl << msb_shift));  // `<<=` discards the bits shifted out
+                        right = narrow<CB>((int32_t)((uint32_t)cr << msb_shift));
+                        if (((left >> msb_shift) != cl || (right >> msb_shift) != cr) && whole) lossy = 1;
+                    }
+                    w[j] = __byte_perm((uint32_t)left, (uint32_t)right, 0x5410);
+                }
+                if (whole) *reinterpret_cast<uint4 *>(pair_ptr + (size_t)i0 * 4u) = make_uint4(w[0], w[1], w[2], w[3]);
+                rd_ptr[0] += chunk_bytes;  // the staged path's cursor (a later, partial group of some frame uses it)
+                continue;
+            }
         }
         if (stereo) {  // warp-uniform: every lane takes part in the shuffles
             int32_t p[8];
