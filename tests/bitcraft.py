@@ -224,8 +224,8 @@ def _put_subframe(b: Bits, rng, x, depth, exact=False, bps=None):
         b.put(v, eff)
     coefs, shift = FIXED.get(order, []), 0
     if kind == 3:
-        precision = int(rng.integers(2, 16))
-        shift = int(rng.integers(0, precision))
+        precision = int(rng.integers(1, 16))
+        shift = int(rng.integers(0, precision)) if rng.random() < 0.9 else int(rng.integers(0, 32))
         w = rng.normal(size=order)
         w = w / max(1e-9, abs(w).sum()) * rng.uniform(0.2, 1.6)
         lim = (1 << (precision - 1)) - 1
@@ -250,6 +250,9 @@ def random_stream(seed: int):
     bs = int(rng.choice(sizes))
     n_frames = int(rng.integers(1, 6))
     last = int(rng.integers(1, bs + 1))
+    # the sample rate as one of the table codes or spelled out after the frame number, in kHz, Hz or tens of Hz (:343-374)
+    rate, rate_code, rate_tail = [(44100, 9, b""), (48000, 10, b""), (48000, 12, bytes([48])), (44100, 13, (44100).to_bytes(2, "big")),
+                                  (48000, 14, (4800).to_bytes(2, "big")), (44100, 0, b"")][int(rng.integers(0, 6))]
     variable = rng.random() < 0.3  # blocking strategy bit: every frame its own size, numbered by its first sample (:343-374)
     depth_in_header = rng.random() < 0.8  # else code 0: "as STREAMINFO says" (:381-384)
     frames, pcm, used = [], [], []
@@ -258,9 +261,10 @@ def random_stream(seed: int):
         used.append(n)
         code = {192: 1, 576: 2, 1152: 3, 256: 8, 1024: 10}.get(n, 6 if n <= 256 else 7) if rng.random() < 0.7 else (6 if n <= 256 else 7)
         number = len(pcm) // channels if variable else f
-        head = bytes([0xFF, 0xF9 if variable else 0xF8, (code << 4) | 9,
+        head = bytes([0xFF, 0xF9 if variable else 0xF8, (code << 4) | rate_code,
                       (ch_code << 4) | ((DEPTH_CODE[depth] if depth_in_header else 0) << 1)]) + utf8_number(number)
         head += bytes([n - 1]) if code == 6 else (n - 1).to_bytes(2, "big") if code == 7 else b""
+        head += rate_tail
         head += bytes([crc8(head)])
         sig = [_signal(rng, n, depth) for _ in range(channels)]
         if ch_code >= 8 and rng.random() < 0.3:  # both channels full scale with the same low bits clear: a side channel with wasted bits
@@ -290,7 +294,7 @@ def random_stream(seed: int):
     nbytes = (depth + 7) // 8
     md5 = hashlib.md5(b"".join(int(v).to_bytes(nbytes, "little", signed=True) for v in pcm)).digest()
     total = len(pcm) // channels
-    data = stream(frames, depth, channels, total, max(used), md5=md5, min_block_size=min(used))
+    data = stream(frames, depth, channels, total, max(used), sample_rate=rate, md5=md5, min_block_size=min(used))
     return np.frombuffer(data, dtype=np.uint8).copy(), np.array(pcm, dtype=np.int64), channels, depth
 
 
@@ -304,7 +308,7 @@ def fuzz_case(seed):
     from oracle import oracle
     data, pcm, channels, depth = random_stream(seed)
     ref = oracle.decode(data, trace_frames=True, keep_on_md5_mismatch=True)
-    if ref.overflow_flag:
+    if ref.overflow_flag or ref.error == "UndefinedInReference":  # the latter: a predictor shift as wide as the InterType (:531)
         return None
     assert ref.error in ("OK", "InvalidChecksum"), (seed, ref.error)
     shift = 16 - depth if 9 <= depth <= 15 else 32 - depth if 17 <= depth <= 31 else 0

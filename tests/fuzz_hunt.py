@@ -1,0 +1,97 @@
+"""Parity hunt with tests/bitcraft.py's random encoder, beyond what the test suite runs every time.
+
+  python tests/fuzz_hunt.py make FIRST COUNT OUT.npz     # CPU: build the streams (slow, pure Python)
+  python tests/fuzz_hunt.py run  OUT.npz                  # GPU: every stream through the batch call and each single-stream
+                                                          # path, against the oracle
+
+Test infrastructure (not collected by pytest): the suite runs a few hundred seeds every time, this runs thousands once."""
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def _one(seed):
+    import bitcraft
+    try:
+        return seed, bitcraft.random_stream(seed)[0]
+    except Exception as e:  # a generator bug is a finding too
+        return seed, repr(e)
+
+
+def make(first, count, out):
+    from multiprocessing import Pool
+    with Pool(min(16, os.cpu_count() or 1)) as pool:
+        res = pool.map(_one, range(first, first + count), chunksize=16)
+    bad = [(s, d) for s, d in res if isinstance(d, str)]
+    if bad:
+        print("generator failures:", bad[:10])
+    good = [(s, d) for s, d in res if not isinstance(d, str)]
+    lens = np.array([d.size for _, d in good], dtype=np.int64)
+    np.savez(out, seeds=np.array([s for s, _ in good]), lens=lens, blob=np.concatenate([d for _, d in good]))
+    print(f"{len(good)} streams, {lens.sum() / 1e6:.1f} MB -> {out}")
+
+
+def run(path):
+    from oracle import oracle as chk
+    import zflac_b200 as z
+    f = np.load(path)
+    seeds, lens, blob = f["seeds"], f["lens"], f["blob"]
+    offs = np.concatenate([[0], np.cumsum(lens)])
+    streams = [blob[offs[i]:offs[i + 1]].copy() for i in range(len(seeds))]
+    t0 = time.time()
+    refs = [chk.decode(d, keep_on_md5_mismatch=True) for d in streams]
+    keep = [i for i, r in enumerate(refs) if not r.overflow_flag and r.error in ("OK", "InvalidChecksum")]
+    print(f"{len(keep)} of {len(streams)} streams are defined in the reference ({time.time() - t0:.1f} s)")
+    bad = []
+
+    def same(got, ref):
+        return (not isinstance(got, Exception) and got.samples.dtype == ref.samples.dtype and np.array_equal(got.samples, ref.samples)
+                and (got.channels, got.sample_rate, got.bits_per_sample) == (ref.channels, ref.sample_rate, ref.bits_per_sample))
+
+    t0 = time.time()
+    for lo in range(0, len(keep), 512):
+        idx = keep[lo:lo + 512]
+        res = z.decode_batch([streams[i] for i in idx])
+        for i, got in zip(idx, res):
+            ref = refs[i]
+            if ref.error != "OK":
+                if not (isinstance(got, z.ZflacError) and type(got).__name__ == ref.error):
+                    bad.append((int(seeds[i]), "batch", "expected " + ref.error))
+            elif not same(got, ref):
+                bad.append((int(seeds[i]), "batch", repr(got)[:60]))
+    print(f"batch: {time.time() - t0:.1f} s, {len(bad)} findings")
+    paths = [dict(), dict(use_fast_path=False), dict(word_pipeline=True), dict(single_pass=True), dict(md5_on_device=True)]
+    t0 = time.time()
+    for n, i in enumerate(keep):
+        ref = refs[i]
+        for kw in (paths[0], paths[1 + n % 4]):
+            kw = dict(kw)
+            try:
+                if ref.error != "OK":
+                    try:
+                        z.decode(streams[i], **kw)
+                        bad.append((int(seeds[i]), str(kw), "no " + ref.error))
+                    except z.ZflacError as e:
+                        if type(e).__name__ != ref.error:
+                            bad.append((int(seeds[i]), str(kw), type(e).__name__))
+                    kw["verify_md5"] = False
+                if not same(z.decode(streams[i], **kw), ref):
+                    bad.append((int(seeds[i]), str(kw), "samples"))
+            except z.ZflacError as e:
+                bad.append((int(seeds[i]), str(kw), type(e).__name__))
+    print(f"single: {time.time() - t0:.1f} s")
+    print("FINDINGS", len(bad), bad[:40])
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "make":
+        make(int(sys.argv[2]), int(sys.argv[3]), sys.argv[4])
+    else:
+        sys.exit(run(sys.argv[2]))
