@@ -5,6 +5,7 @@
                                                           # path, against the oracle
   python tests/fuzz_hunt.py damaged OUT.npz               # the same with one defect per stream (bit flip, cut, repeat):
                                                           # same error name, or the same samples where it still decodes
+  python tests/fuzz_hunt.py damaged synth                 # twelve defects for each of tests/synth_cases.py's streams
 
 Test infrastructure (not collected by pytest): the suite runs a few hundred seeds every time, this runs thousands once."""
 import os
@@ -39,11 +40,10 @@ def make(first, count, out):
     print(f"{len(good)} streams, {lens.sum() / 1e6:.1f} MB -> {out}")
 
 
-def damage(data, seed):
+def damage(data, seed, lo=42):
     """One defect per stream: a flipped bit, a zeroed or 0xFF byte, a cut, or a few bytes repeated — all after the metadata."""
     rng = np.random.default_rng(seed ^ 0x5EED)
     d = data.copy()
-    lo = 42
     if d.size <= lo + 2:
         return d
     at = int(rng.integers(lo, d.size))
@@ -65,10 +65,22 @@ def damage(data, seed):
 def run(path, damaged=False):
     from oracle import oracle as chk
     import zflac_b200 as z
-    f = np.load(path)
-    seeds, lens, blob = f["seeds"], f["lens"], f["blob"]
-    offs = np.concatenate([[0], np.cumsum(lens)])
-    streams = [blob[offs[i]:offs[i + 1]].copy() for i in range(len(seeds))]
+    if path == "synth":  # the generator's presets (long frames, many of them: the sync scan and the frame chain), `damaged` x 12
+        import synth_cases
+        seeds, streams = [], []
+        for k, name in enumerate(sorted(synth_cases.CASES)):
+            flac = synth_cases.make(name).flac
+            lo = int(chk.decode(flac).audio_offset)
+            for j in range(12):
+                seeds.append(1000 * k + j)
+                streams.append(damage(flac, 1000 * k + j, lo))
+        seeds = np.array(seeds)
+        damaged = False
+    else:
+        f = np.load(path)
+        seeds, lens, blob = f["seeds"], f["lens"], f["blob"]
+        offs = np.concatenate([[0], np.cumsum(lens)])
+        streams = [blob[offs[i]:offs[i + 1]].copy() for i in range(len(seeds))]
     if damaged:
         streams = [damage(d, int(s)) for d, s in zip(streams, seeds)]
     t0 = time.time()
