@@ -157,6 +157,8 @@ def _signal(rng, n, bits):
 def _put_residual(b: Bits, rng, res, order, bs):
     """Residual section (:614-666): coding method, partition order, per partition a Rice parameter or the escape code."""
     method = int(rng.integers(0, 2))
+    if max([abs(r) for r in res], default=0).bit_length() > 26:
+        method = 1  # 4-bit parameters stop at 14: unary runs of 2^13 zeros and more per residual make Python's big integers crawl
     pbits, kmax = (4, 14) if method == 0 else (5, 30)
     orders = [po for po in range(0, 9) if bs % (1 << po) == 0 and (bs >> po) >= order and (bs >> po) > 0]
     po = int(rng.choice(orders))
@@ -238,12 +240,13 @@ def _put_subframe(b: Bits, rng, x, depth, exact=False, bps=None):
     return x
 
 
-def random_stream(seed: int):
-    """(flac bytes as uint8 array, expected interleaved PCM before the MSB-align shift, channels, depth)."""
+def random_stream(seed: int, depths=(8, 12, 16, 16, 20, 24, 24)):
+    """(flac bytes as uint8 array, expected interleaved PCM before the MSB-align shift, channels, depth). depths: what the
+    stream's depth is drawn from (the suite's seeds use the default; fuzz_hunt.py also runs 32)."""
     import hashlib
     import numpy as np
     rng = np.random.default_rng(seed)
-    depth = int(rng.choice([8, 12, 16, 16, 20, 24, 24]))
+    depth = int(rng.choice(list(depths)))
     ch_code = int(rng.choice([0, 1, 1, 2, 5, 7, 8, 9, 10, 10]))
     channels = 2 if ch_code >= 8 else ch_code + 1
     sizes = [16, 32, 33, 64, 100, 192, 255, 256, 576, 1024, 1152]
@@ -298,15 +301,15 @@ def random_stream(seed: int):
     return np.frombuffer(data, dtype=np.uint8).copy(), np.array(pcm, dtype=np.int64), channels, depth
 
 
-def fuzz_case(seed):
-    """(stream, oracle result, exact) of random_stream(seed), or None where the reference is undefined (the oracle's overflow
+def fuzz_case(seed, depths=None):
+    """(stream, oracle result, exact) of random_stream(seed) — of random_stream(seed, depths) if given —, or None where the reference is undefined (the oracle's overflow
     flag: a side-channel value beyond the container, a sum beyond the reference's InterType). exact: the reference
     reproduces the PCM the stream was coded from; else one of its defined quirks changed it (a side channel's wasted-bits
     shift wraps in the container type, :494 / :537) — the stream's MD5 then does not match, and the oracle's samples
     (keep_on_md5_mismatch) are what a decoder without the gate must produce."""
     import numpy as np
     from oracle import oracle
-    data, pcm, channels, depth = random_stream(seed)
+    data, pcm, channels, depth = random_stream(seed, depths) if depths else random_stream(seed)
     ref = oracle.decode(data, trace_frames=True, keep_on_md5_mismatch=True)
     if ref.overflow_flag or ref.error == "UndefinedInReference":  # the latter: a predictor shift as wide as the InterType (:531)
         return None

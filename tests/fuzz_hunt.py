@@ -19,10 +19,13 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
+DEPTHS = None  # make32: (32,)
+
+
 def _one(seed):
     import bitcraft
     try:
-        return seed, bitcraft.random_stream(seed)[0]
+        return seed, (bitcraft.random_stream(seed, DEPTHS)[0] if DEPTHS else bitcraft.random_stream(seed)[0])
     except Exception as e:  # a generator bug is a finding too
         return seed, repr(e)
 
@@ -137,7 +140,9 @@ def run(path, damaged=False):
 
 
 if __name__ == "__main__":
-    if sys.argv[1] == "make":
+    if sys.argv[1] in ("make", "make32"):  # make32: 32 bits per sample only (int64 scratch, the single-pass decoder)
+        if sys.argv[1] == "make32":
+            DEPTHS = (32,)
         make(int(sys.argv[2]), int(sys.argv[3]), sys.argv[4])
     else:
         sys.exit(run(sys.argv[2], damaged=sys.argv[1] == "damaged"))

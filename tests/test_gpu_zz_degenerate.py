@@ -138,3 +138,20 @@ def test_random_streams(z):
         got = z.decode(data, **kw)
         assert got.samples.dtype == ref.samples.dtype and np.array_equal(got.samples, ref.samples), (k, kw)
         assert (got.channels, got.sample_rate, got.bits_per_sample) == (ref.channels, ref.sample_rate, ref.bits_per_sample)
+
+
+def test_random_streams_32bit(z):
+    """The same at 32 bits per sample (int64 scratch, the single-pass decoder): full-scale signals, whose residuals need 33
+    bits and whose Rice codewords pass 2^32 (the reference reads them into an i64, src/zflac.zig:614-666)."""
+    from bitcraft import fuzz_case
+    from test_gpu_batch import check_against_oracle
+    cases = [c for c in (fuzz_case(seed, (32,)) for seed in range(40000, 40120)) if c is not None]
+    assert len(cases) >= 60
+    streams = [c[0] for c in cases]
+    check_against_oracle(z, streams, z.decode_batch(streams))
+    for k, (data, ref, exact) in enumerate(cases):
+        kw = [dict(), dict(use_fast_path=False), dict(md5_on_device=True)][k % 3]
+        if not exact:
+            kw["verify_md5"] = False
+        got = z.decode(data, **kw)
+        assert got.samples.dtype == ref.samples.dtype and np.array_equal(got.samples, ref.samples), (k, kw)

@@ -296,3 +296,19 @@ def test_host_core_random_streams(core):
             assert np.array_equal(host_decode(core, raw, ref, two_pass=True, narrow=True), ref.samples), seed
         done += 1
     assert done >= len(FUZZ_SEEDS) * 2 // 3
+
+
+def test_host_core_random_streams_32bit(core):
+    """32 bits per sample (int64 scratch, decode_predicted64): a full-scale signal has residuals of 33 bits — Rice codewords
+    beyond 2^32, which the reference reads into its i64 (src/zflac.zig:614-666) whatever RFC 9639 allows an encoder."""
+    from bitcraft import fuzz_case
+    done = big = 0
+    for seed in range(40000, 40120):
+        case = fuzz_case(seed, (32,))
+        if case is None:
+            continue
+        data, ref, _ = case
+        assert np.array_equal(host_decode(core, data.tobytes(), ref), ref.samples), seed
+        done += 1
+        big += int(np.abs(ref.samples.astype(np.int64)).max() >= (1 << 31) - 1)
+    assert done >= 60 and big >= 10

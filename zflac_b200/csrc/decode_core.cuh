@@ -241,6 +241,18 @@ __host__ __device__ ZF_NOINLINE uint32_t rice_slow_outlined(BitReader<Src> *br, 
     const uint32_t r = br->read(k);
     return (q << k) + r;
 }
+// The same with a 64-bit codeword: in a 32-bit container the reference's residuals are i64 (the InterType, :614-666), and a
+// full-scale 32 bps signal has residuals of 33 bits whatever RFC 9639 says about encoders.
+template <class Src>
+__host__ __device__ ZF_NOINLINE uint64_t rice_slow64_outlined(BitReader<Src> *br, uint32_t k, uint64_t len_bits, uint32_t *err) {
+    const uint32_t q = br->read_unary(len_bits);
+    if (q == 0xFFFFFFFFu) {
+        *err = ST_END_OF_STREAM;
+        return 0;
+    }
+    const uint32_t r = br->read(k);
+    return ((uint64_t)q << k) + r;
+}
 template <class Src>
 ZF_HDI uint32_t rice_slow(BitReader<Src> &br, uint32_t k, uint64_t len_bits, uint32_t &err) {
     BitReader<Src> t = br;
@@ -463,14 +475,19 @@ ZF_HDI uint32_t decode_predicted64(BitReader<Src> &br, int64_t *__restrict__ out
         const bool escaped = param == (1u << pbits) - 1u;
         const uint32_t esc = escaped ? br.read(5) : 0;
         for (; i < end; ++i) {  // hist is a ring: sample i lives at hist[i & 31]
-            int32_t r;
-            // Rice residuals are decoded in 32 bits (RFC 9639 limits them to int32); escape codes too
-            if (escaped) r = esc ? br.read_signed(esc) : 0;
-            else r = zigzag(rice_slow(br, param, len_bits, err));
+            int64_t r;
+            if (escaped) {
+                r = esc ? br.read_signed(esc) : 0;  // at most 31 bits (:646-654)
+            } else {  // 64-bit codeword: see rice_slow64_outlined
+                BitReader<Src> t = br;
+                const uint64_t cw = rice_slow64_outlined(&t, param, len_bits, &err);
+                br = t;
+                r = (int64_t)(cw >> 1) ^ -(int64_t)(cw & 1u);
+            }
             if (err != ST_OK) return err;
             int64_t acc = 0;
             for (uint32_t t = 0; t < order; ++t) acc += (int64_t)coef[t] * hist[(i - 1 - t) & 31];
-            const int64_t v = (int64_t)r + (acc >> shift);
+            const int64_t v = r + (acc >> shift);
             hist[i & 31] = v;
             if (wr) out[i] = (int64_t)((uint64_t)v << wasted);
         }
