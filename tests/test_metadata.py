@@ -177,3 +177,54 @@ def test_pcm_bound(z):
             assert b.value == 0
         elif not e["expect_error"] and b.value:
             assert b.value <= e["n_samples"] * e["container_bytes"]  # never more than what decodes (faulty/05 decodes more)
+
+
+def _random_head(rng, stream: bytes) -> bytes:
+    """`stream` = fLaC + one STREAMINFO + frames (tests/bitcraft.py). The head is rebuilt at random: block order, types
+    (reserved and invalid ones too), lengths, last-block flags, a damaged signature, a cut anywhere in the head."""
+    sig, si, frames = stream[:4], stream[8:42], stream[42:]
+    blocks = []
+    for _ in range(int(rng.integers(0, 5))):
+        typ = int(rng.choice([1, 1, 2, 3, 4, 5, 6, 7, 50, 126, 127, 0]))
+        n = int(rng.choice([0, 1, 4, 17, 34, 300]))
+        blocks.append((typ, bytes(rng.integers(0, 256, n, dtype=np.uint8)) if typ else si))
+    at = int(rng.integers(0, len(blocks) + 1)) if rng.random() < 0.2 else 0  # STREAMINFO first, mostly
+    if rng.random() < 0.9:
+        blocks.insert(at, (0, si))
+    last = len(blocks) - 1 if rng.random() < 0.85 else int(rng.integers(-1, len(blocks)))  # -1: no block says it is the last
+    head = bytearray(sig)
+    for k, (typ, body) in enumerate(blocks):
+        length = len(body) if rng.random() < 0.9 else int(rng.integers(0, 400))  # the length field may lie
+        head += bytes([(0x80 if k == last else 0) | typ]) + length.to_bytes(3, "big") + body
+    if rng.random() < 0.05:
+        head[int(rng.integers(0, 4))] ^= 0x20
+    data = bytes(head) + frames
+    if rng.random() < 0.15:
+        data = data[:int(rng.integers(0, len(head) + 8))]
+    return data
+
+
+def test_random_heads_against_the_oracle(z):
+    """The host-only metadata walk (the one `decode()` starts with) on 600 random heads: where the oracle's decode fails in
+    the head, the same error; where it gets past the head, the same audio offset."""
+    import bitcraft
+    from oracle import oracle
+    rng = np.random.default_rng(0xFEED)
+    base = [bitcraft.random_stream(seed)[0].tobytes() for seed in (3, 4, 5, 6)]
+    seen = {}
+    for k in range(600):
+        data = _random_head(rng, base[k % len(base)])
+        ref = oracle.decode(np.frombuffer(data, dtype=np.uint8), keep_on_md5_mismatch=True, copy_samples=False)
+        try:
+            m = z.metadata(data)
+        except z.ZflacError as e:
+            name = type(e).__name__
+            assert ref.error == name, (k, name, ref.error, data[:64].hex())
+            seen[name] = seen.get(name, 0) + 1
+            continue
+        seen["walked"] = seen.get("walked", 0) + 1
+        # the oracle got past the head as well: whatever it says afterwards is about the frames
+        assert ref.error not in ("InvalidSignature", "InvalidMetadataHeader", "MissingStreaminfo"), (k, ref.error, data[:64].hex())
+        if ref.audio_offset:
+            assert m["audio_offset"] == ref.audio_offset, (k, m["audio_offset"], ref.audio_offset)
+    assert seen.get("walked", 0) > 100 and len(seen) >= 4, seen
