@@ -240,7 +240,7 @@ def _put_subframe(b: Bits, rng, x, depth, exact=False, bps=None):
     return x
 
 
-def random_stream(seed: int, depths=(8, 12, 16, 16, 20, 24, 24)):
+def random_stream(seed: int, depths=(8, 12, 16, 16, 20, 24, 24), sizes=(16, 32, 33, 64, 100, 192, 255, 256, 576, 1024, 1152)):
     """(flac bytes as uint8 array, expected interleaved PCM before the MSB-align shift, channels, depth). depths: what the
     stream's depth is drawn from (the suite's seeds use the default; fuzz_hunt.py also runs 32)."""
     import hashlib
@@ -249,7 +249,7 @@ def random_stream(seed: int, depths=(8, 12, 16, 16, 20, 24, 24)):
     depth = int(rng.choice(list(depths)))
     ch_code = int(rng.choice([0, 1, 1, 2, 5, 7, 8, 9, 10, 10]))
     channels = 2 if ch_code >= 8 else ch_code + 1
-    sizes = [16, 32, 33, 64, 100, 192, 255, 256, 576, 1024, 1152]
+    sizes = list(sizes)
     bs = int(rng.choice(sizes))
     n_frames = int(rng.integers(1, 6))
     last = int(rng.integers(1, bs + 1))
@@ -262,7 +262,8 @@ def random_stream(seed: int, depths=(8, 12, 16, 16, 20, 24, 24)):
     for f in range(n_frames):
         n = int(rng.choice(sizes)) if variable else last if (f == n_frames - 1 and n_frames > 1) else bs
         used.append(n)
-        code = {192: 1, 576: 2, 1152: 3, 256: 8, 1024: 10}.get(n, 6 if n <= 256 else 7) if rng.random() < 0.7 else (6 if n <= 256 else 7)
+        code = {192: 1, 576: 2, 1152: 3, 2304: 4, 4608: 5, 256: 8, 512: 9, 1024: 10, 2048: 11, 4096: 12, 8192: 13, 16384: 14,
+                32768: 15}.get(n, 6 if n <= 256 else 7) if rng.random() < 0.7 else (6 if n <= 256 else 7)
         number = len(pcm) // channels if variable else f
         head = bytes([0xFF, 0xF9 if variable else 0xF8, (code << 4) | rate_code,
                       (ch_code << 4) | ((DEPTH_CODE[depth] if depth_in_header else 0) << 1)]) + utf8_number(number)
@@ -301,7 +302,7 @@ def random_stream(seed: int, depths=(8, 12, 16, 16, 20, 24, 24)):
     return np.frombuffer(data, dtype=np.uint8).copy(), np.array(pcm, dtype=np.int64), channels, depth
 
 
-def fuzz_case(seed, depths=None):
+def fuzz_case(seed, depths=None, sizes=None):
     """(stream, oracle result, exact) of random_stream(seed) — of random_stream(seed, depths) if given —, or None where the reference is undefined (the oracle's overflow
     flag: a side-channel value beyond the container, a sum beyond the reference's InterType). exact: the reference
     reproduces the PCM the stream was coded from; else one of its defined quirks changed it (a side channel's wasted-bits
@@ -309,7 +310,10 @@ def fuzz_case(seed, depths=None):
     (keep_on_md5_mismatch) are what a decoder without the gate must produce."""
     import numpy as np
     from oracle import oracle
-    data, pcm, channels, depth = random_stream(seed, depths) if depths else random_stream(seed)
+    kw = dict(depths=depths) if depths else {}
+    if sizes:
+        kw["sizes"] = sizes
+    data, pcm, channels, depth = random_stream(seed, **kw)
     ref = oracle.decode(data, trace_frames=True, keep_on_md5_mismatch=True)
     if ref.overflow_flag or ref.error == "UndefinedInReference":  # the latter: a predictor shift as wide as the InterType (:531)
         return None
